@@ -1,0 +1,165 @@
+/* gmr_b200.h - C ABI of the B200-native batched retargeting engine.
+ *
+ * Drop-in boundary for the hot path of Zudva/GMR (pure Python reference):
+ *   GeneralMotionRetargeting(src_human, tgt_robot).retarget(human_data)
+ *       general_motion_retargeting/motion_retarget.py:13-21 (ctor), :139-185 (retarget)
+ *   scripts/bvh_to_robot_dataset.py:84-124 and scripts/smplx_to_robot_dataset.py:79-112
+ *       (per-file construct -> per-frame retarget -> FK tail)
+ * The reference has no FFI of its own (it calls mink / mujoco / daqp from Python); these
+ * entry points are what a ctypes binding inside the reference's class would call
+ * (INTEGRATION.md shows that binding).
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 on error (gmr_last_error() has the text);
+ *     nothing throws, nothing is printed;
+ *   - the caller owns every buffer; the library owns only the opaque handles;
+ *   - pointers named *_dev are CUDA device pointers on the handle's device, pointers in
+ *     gmr_model_desc are host pointers (copied at create time);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream); all work of a
+ *     batch is enqueued on its stream, calls return without synchronising unless stated;
+ *   - quaternions are wxyz (scalar first) as in the reference; human frames are
+ *     [pos xyz, quat wxyz] = 7 numbers per body;
+ *   - a handle is bound to one device and one stream and is not thread-safe (the
+ *     reference's object is not either: one object per worker, smplx_to_robot_dataset.py:79).
+ */
+#ifndef GMR_B200_H
+#define GMR_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GMR_ABI_VERSION 1
+
+/* hard limits of the kernels (largest shipped robot: nv = 49, nbody = 53, 15 tasks) */
+#define GMR_MAX_NV     64
+#define GMR_MAX_NBODY  64     /* including world */
+#define GMR_MAX_TASKS  32     /* per stage */
+#define GMR_MAX_SCALED 32
+
+/* joint types = MuJoCo mjtJoint */
+#define GMR_JNT_FREE  0
+#define GMR_JNT_SLIDE 2
+#define GMR_JNT_HINGE 3
+
+/* dtype of the human stream */
+#define GMR_F32 0
+#define GMR_F64 1
+
+/* Flattened (source, robot) description: kinematic tree + IK-config tables.
+ * Replaces mj.MjModel.from_xml_path (motion_retarget.py:27) and the JSON handling of
+ * __init__/setup_retarget_configuration (motion_retarget.py:29-114).  Host pointers. */
+typedef struct gmr_model_desc {
+  int32_t abi_version;              /* GMR_ABI_VERSION */
+  /* kinematic tree, MuJoCo naming; body 0 = world */
+  int32_t nbody, njnt, nq, nv;
+  const int32_t* body_parentid;     /* [nbody] */
+  const double*  body_pos;          /* [nbody,3] */
+  const double*  body_quat;         /* [nbody,4] unit wxyz */
+  const int32_t* body_jntadr;       /* [nbody] first joint or -1 */
+  const int32_t* body_jntnum;       /* [nbody] */
+  const int32_t* jnt_type;          /* [njnt] */
+  const int32_t* jnt_qposadr;       /* [njnt] */
+  const int32_t* jnt_dofadr;        /* [njnt] */
+  const double*  jnt_axis;          /* [njnt,3] unit, body frame */
+  const double*  jnt_pos;           /* [njnt,3] must be 0 for the CUDA path */
+  const int32_t* jnt_limited;       /* [njnt] */
+  const double*  jnt_range;         /* [njnt,2] */
+  const double*  qpos0;             /* [nq] cold-start state (mink.Configuration(model), :75) */
+  double         timestep;          /* model.opt.timestep (:146) */
+  /* target preparation (motion_retarget.py:117-136, 209-270) */
+  int32_t n_human;                  /* h: bodies per frame in the human stream */
+  int32_t n_scaled;                 /* s: bodies of human_scale_table, entry 0 = human root */
+  const int32_t* scaled_human_index;/* [s] index into the h bodies of a frame */
+  const double*  scale;             /* [s] human_scale_table (ratio not folded in) */
+  const double*  pos_off;           /* [s,3] table-1 pos offset - ground_height*z (:91) */
+  const double*  rot_off;           /* [s,4] table-1 rot offset wxyz unit (:92) */
+  const int32_t* is_foot;           /* [s] name contains "Foot"/"foot" (:261) */
+  /* tasks of stage 1 and 2 (ik_match_table1/2, :78-114) */
+  int32_t use_table[2];
+  int32_t n_task[2];
+  const int32_t* task_body[2];      /* [m] robot body id (FrameTask frame_name) */
+  const int32_t* task_src[2];       /* [m] index into the scaled list */
+  const double*  task_wpos[2];      /* [m] position_cost */
+  const double*  task_wrot[2];      /* [m] orientation_cost */
+  /* solver constants */
+  double  damping;                  /* ctor damping, default 0.5 (:19) */
+  int32_t max_iter;                 /* 10 (:56) */
+  double  converge_eps;             /* 0.001 (:153,172) */
+  double  limit_gain;               /* mink ConfigurationLimit gain 0.95 */
+  double  lm_damping;               /* FrameTask lm_damping = 1 (:88,106) */
+} gmr_model_desc;
+
+/* per-frame diagnostics (reference: error1()/error2() :188-200, loop counters :152,171) */
+typedef struct gmr_diag {
+  double*  err_dev;      /* [B,T,2] final error1/error2 of the frame, or NULL */
+  int32_t* iters_dev;    /* [B,T,2] QP solves per stage (1..max_iter+1), or NULL */
+  int32_t* nfact_dev;    /* [B,T]   Cholesky factorisations in the frame, or NULL */
+} gmr_diag;
+
+typedef struct gmr_model gmr_model;
+typedef struct gmr_batch gmr_batch;
+
+const char* gmr_last_error(void);
+int gmr_abi_version(void);
+
+int gmr_model_create(const gmr_model_desc* desc, int device, gmr_model** out);
+int gmr_model_destroy(gmr_model* m);
+
+/* B independent IK instances (clip x robot).  n_models > 1 = heterogeneous launch;
+ * model_of_instance (host, [B]) may be NULL when n_models == 1.  State starts at qpos0. */
+int gmr_batch_create(gmr_model* const* models, int n_models, const int32_t* model_of_instance,
+                     int B, void* stream, gmr_batch** out);
+int gmr_batch_destroy(gmr_batch* b);
+/* q0_dev: [B,nq_max] or NULL for qpos0 (the reference's cold start; it has no reset). */
+int gmr_batch_reset(gmr_batch* b, const double* q0_dev);
+/* per-instance scale table [B,s_max] (human_scale_table * actual_height/assumption, :36-43);
+ * NULL restores the model's table. */
+int gmr_batch_set_scale(gmr_batch* b, const double* scale_dev);
+int gmr_batch_get_state(gmr_batch* b, double* q_dev /* [B,nq_max] */);
+int gmr_batch_dims(const gmr_batch* b, int32_t* B, int32_t* nq_max, int32_t* s_max,
+                   int32_t* h_max, int32_t* nbody_max);
+
+/* retarget(): one frame for every instance, warm-started from the batch state.
+ * human_dev [B,h,7]; qpos_out_dev [B,nq_max]; scaled_out_dev [B,s_max,7] or NULL
+ * (= .scaled_human_data, :124). */
+int gmr_batch_step(gmr_batch* b, const void* human_dev, int human_dtype, int offset_to_ground,
+                   double* qpos_out_dev, double* scaled_out_dev, const gmr_diag* diag);
+
+/* whole clips in one launch: instance i retargets frames 0..T_of_instance[i]-1 in order.
+ * human_dev [B,T_max,h,7]; T_of_instance_dev [B] or NULL (= T_max for all);
+ * qpos_out_dev [B,T_max,nq_max]. */
+int gmr_batch_run(gmr_batch* b, const void* human_dev, int human_dtype,
+                  const int32_t* T_of_instance_dev, int T_max, int offset_to_ground,
+                  double* qpos_out_dev, const gmr_diag* diag);
+
+/* --- stage entry points (same device code as the fused path; used for per-stage parity) --- */
+/* Kernel 1: scale + offset (+ground) -> scaled_out_dev [B,s,7] */
+int gmr_target_prep(gmr_batch* b, const void* human_dev, int human_dtype, int offset_to_ground,
+                    double* scaled_out_dev);
+/* Kernel 2 (FK half) on the batch state or on q_dev if not NULL:
+ * xpos_out_dev [B,nbody_max,3], xquat_out_dev [B,nbody_max,4] */
+int gmr_fk(gmr_batch* b, const double* q_dev, double* xpos_out_dev, double* xquat_out_dev);
+/* Kernel 2+3 (assembly): task errors e [B,m_max,6] and the QP of one solve_ik call:
+ * H [B,nv_max,nv_max] (full symmetric), c, lo, hi [B,nv_max]; targets = scaled_dev [B,s,7] */
+int gmr_build_qp(gmr_batch* b, int stage, const double* scaled_dev, double* e_out_dev,
+                 double* H_out_dev, double* c_out_dev, double* lo_out_dev, double* hi_out_dev);
+/* Kernel 3 (solve): box QP for arbitrary SPD H: dq [n_qp,n] ; nfact [n_qp] or NULL */
+int gmr_qp_solve(int device, void* stream, int n_qp, int n, const double* H_dev,
+                 const double* c_dev, const double* lo_dev, const double* hi_dev,
+                 double* x_out_dev, int32_t* nfact_out_dev);
+
+/* FK tail of the dataset drivers (KinematicsModel.forward_kinematics,
+ * kinematics_model.py:213-246): float32, xyzw root quaternion, bodies 1..nbody-1.
+ * root_pos_dev [N,3], root_rot_xyzw_dev [N,4], dof_pos_dev [N,ndof] ->
+ * body_pos_out_dev [N,nbody-1,3], body_rot_out_dev [N,nbody-1,4] (xyzw) or NULL. */
+int gmr_fk_bodies_f32(gmr_model* m, void* stream, int N, const float* root_pos_dev,
+                      const float* root_rot_xyzw_dev, const float* dof_pos_dev,
+                      float* body_pos_out_dev, float* body_rot_out_dev);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GMR_B200_H */
