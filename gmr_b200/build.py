@@ -1,0 +1,32 @@
+"""In-tree build of the CUDA engine:  python -m gmr_b200.build
+
+nvcc cross-compiles for sm_100a without a GPU; the .so travels to the GPU box with the repo.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "csrc", "gmr_abi.cu")
+OUT = os.path.join(HERE, "libgmr_b200.so")
+DEPS = [SRC] + [os.path.join(HERE, "csrc", f) for f in ("gmr_device.cuh", "gmr_stages.cuh", "gmr_clip.cuh")] + [
+    os.path.join(HERE, "..", "include", "gmr_b200.h")]
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared"]
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    stale = not os.path.exists(OUT) or any(os.path.getmtime(d) > os.path.getmtime(OUT) for d in DEPS if os.path.exists(d))
+    if not (force or stale):
+        return OUT
+    nvcc = os.environ.get("NVCC", "nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, SRC]
+    subprocess.check_call(cmd)
+    return OUT
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

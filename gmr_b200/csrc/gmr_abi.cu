@@ -1,0 +1,515 @@
+// gmr_abi.cu - C ABI of include/gmr_b200.h: model flattening to device tables, batch state,
+// kernel launches.  No torch types, no exceptions across the boundary.
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+#include "../../include/gmr_b200.h"
+#include "gmr_clip.cuh"
+
+using namespace gmr;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return fail(-100, std::string(#x) + ": " + cudaGetErrorString(e_)); } while (0)
+
+struct gmr_model {
+  int device = 0;
+  DevModel host{};           // device pointers inside
+  char* blob = nullptr;      // one device allocation holding every table
+  size_t blob_bytes = 0;
+  int max_task = 0;
+  // FK tail tables
+  FkTailModel tail{};
+  char* tail_blob = nullptr;
+};
+
+struct gmr_batch {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  int B = 0, n_models = 0;
+  std::vector<gmr_model*> models;
+  DevModel* d_models = nullptr;
+  int* d_model_of = nullptr;
+  double* d_q = nullptr;        // [B, nq_max]
+  double* d_scale = nullptr;    // [B, s_max]
+  int* d_counter = nullptr;
+  int* d_order = nullptr;
+  int nq_max = 0, s_max = 0, h_max = 0, nbody_max = 0, nv_max = 0, m_max = 0;
+  Lay lay{};
+  int warps_per_cta = 4, grid = 0;
+  size_t smem_bytes = 0;
+};
+
+extern "C" const char* gmr_last_error(void) { return g_err.c_str(); }
+extern "C" int gmr_abi_version(void) { return GMR_ABI_VERSION; }
+
+namespace {
+struct Blob {
+  std::vector<char> bytes;
+  template <typename T> size_t push(const std::vector<T>& v) {
+    size_t off = (bytes.size() + 15) & ~size_t(15);
+    bytes.resize(off + std::max<size_t>(v.size(), 1) * sizeof(T));
+    if (!v.empty()) memcpy(bytes.data() + off, v.data(), v.size() * sizeof(T));
+    return off;
+  }
+};
+template <typename T> std::vector<T> vec(const T* p, size_t n) { return std::vector<T>(p, p + n); }
+}  // namespace
+
+extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model** out) {
+  if (!d || !out) return fail(-1, "null argument");
+  if (d->abi_version != GMR_ABI_VERSION) return fail(-2, "abi_version mismatch");
+  if (d->nbody < 2 || d->nbody > GMR_MAX_NBODY || d->nv < 1 || d->nv > GMR_MAX_NV || d->nq > GMR_MAX_NV + 1)
+    return fail(-3, "model exceeds kernel limits (nbody<=64, nv<=64)");
+  if (d->n_scaled < 1 || d->n_scaled > GMR_MAX_SCALED) return fail(-3, "n_scaled out of range (1..32)");
+  for (int k = 0; k < 2; k++)
+    if (d->n_task[k] < 0 || d->n_task[k] > GMR_MAX_TASKS) return fail(-3, "n_task out of range (0..32)");
+  if (!(d->timestep > 0)) return fail(-3, "timestep must be > 0");
+  const int nb = d->nbody, nj = d->njnt, nv = d->nv;
+
+  // ---- validate the tree and derive dof tables
+  std::vector<int> depth(nb, 0), dof_kind(nv, 0), dof_qadr(nv, -1), dof_parent(nv, -1), dof_limited(nv, 0), dof_body(nv, 0);
+  std::vector<double> dof_lo(nv, 0.0), dof_hi(nv, 0.0);
+  std::vector<int> body_lastdof(nb, -1);   // last dof of the nearest ancestor-or-self with dofs
+  int ref_body = 0, nlevel = 0;
+  for (int b = 1; b < nb; b++) {
+    int p = d->body_parentid[b];
+    if (p < 0 || p >= b) return fail(-4, "bodies must be ordered parent-before-child");
+    depth[b] = depth[p] + 1;
+    nlevel = std::max(nlevel, depth[b]);
+    int last = body_lastdof[p];
+    int jadr = d->body_jntadr[b], jnum = d->body_jntnum[b];
+    bool seen_hinge = false;
+    for (int j = jadr; j < jadr + jnum; j++) {
+      if (j < 0 || j >= nj) return fail(-4, "body_jntadr out of range");
+      int type = d->jnt_type[j], da = d->jnt_dofadr[j], qa = d->jnt_qposadr[j];
+      if (type == GMR_JNT_FREE) {
+        if (jnum != 1 || p != 0) return fail(-4, "free joint must be the only joint of a top-level body");
+        if (ref_body == 0) ref_body = b;
+        for (int i = 0; i < 6; i++) {
+          dof_kind[da + i] = i < 3 ? DOF_FREE_T : DOF_FREE_R;
+          dof_qadr[da + i] = i < 3 ? qa + i : (i == 3 ? qa + 3 : -1);
+          dof_parent[da + i] = i == 0 ? last : da + i - 1;
+          dof_body[da + i] = b;
+        }
+        last = da + 5;
+      } else if (type == GMR_JNT_SLIDE || type == GMR_JNT_HINGE) {
+        if (type == GMR_JNT_SLIDE && seen_hinge) return fail(-4, "slide after hinge in one body is unsupported");
+        if (type == GMR_JNT_HINGE) {
+          seen_hinge = true;
+          const double* jp = d->jnt_pos + 3 * j;
+          if (jp[0] != 0 || jp[1] != 0 || jp[2] != 0) return fail(-4, "hinge joints with pos != 0 are unsupported");
+        }
+        dof_kind[da] = type == GMR_JNT_SLIDE ? DOF_SLIDE : DOF_HINGE;
+        dof_qadr[da] = qa;
+        dof_parent[da] = last;
+        dof_body[da] = b;
+        dof_limited[da] = d->jnt_limited[j] ? 1 : 0;
+        dof_lo[da] = d->jnt_range[2 * j];
+        dof_hi[da] = d->jnt_range[2 * j + 1];
+        last = da;
+      } else {
+        return fail(-4, "unsupported joint type");
+      }
+    }
+    body_lastdof[b] = last;
+  }
+  for (int i = 0; i < nv; i++)
+    if (dof_parent[i] >= i) return fail(-4, "dofs must be ordered parent-before-child");
+  // levels (level 1 first)
+  std::vector<int> level_start(nlevel + 1, 0), level_body;
+  for (int lv = 1; lv <= nlevel; lv++) {
+    level_start[lv - 1] = (int)level_body.size();
+    for (int b = 1; b < nb; b++) if (depth[b] == lv) level_body.push_back(b);
+  }
+  level_start[nlevel] = (int)level_body.size();
+
+  // ---- tasks, stage-major with stride GMR_MAX_TASKS, and per-dof subtree masks
+  const int MT = GMR_MAX_TASKS;
+  std::vector<int> task_body(2 * MT, 0), task_src(2 * MT, 0);
+  std::vector<double> task_wpos(2 * MT, 0.0), task_wrot(2 * MT, 0.0);
+  std::vector<unsigned> taskmask(2 * nv, 0u);
+  for (int k = 0; k < 2; k++) {
+    if (!d->use_table[k]) continue;
+    for (int t = 0; t < d->n_task[k]; t++) {
+      int body = d->task_body[k][t], src = d->task_src[k][t];
+      if (body < 1 || body >= nb) return fail(-5, "task body id out of range");
+      if (src < 0 || src >= d->n_scaled) return fail(-5, "task source index out of range");
+      task_body[k * MT + t] = body; task_src[k * MT + t] = src;
+      task_wpos[k * MT + t] = d->task_wpos[k][t]; task_wrot[k * MT + t] = d->task_wrot[k][t];
+      for (int i = body_lastdof[body]; i >= 0; i = dof_parent[i]) taskmask[k * nv + i] |= 1u << t;
+    }
+  }
+  for (int i = 0; i < d->n_scaled; i++)
+    if (d->scaled_human_index[i] < 0 || d->scaled_human_index[i] >= d->n_human) return fail(-5, "scaled_human_index out of range");
+
+  // ---- pack and upload
+  Blob bl;
+  size_t o_parent = bl.push(vec(d->body_parentid, nb)), o_bpos = bl.push(vec(d->body_pos, 3 * nb)),
+         o_bquat = bl.push(vec(d->body_quat, 4 * nb)), o_jadr = bl.push(vec(d->body_jntadr, nb)),
+         o_jnum = bl.push(vec(d->body_jntnum, nb)), o_lstart = bl.push(level_start), o_lbody = bl.push(level_body),
+         o_jtype = bl.push(vec(d->jnt_type, nj)), o_jq = bl.push(vec(d->jnt_qposadr, nj)),
+         o_jd = bl.push(vec(d->jnt_dofadr, nj)), o_jaxis = bl.push(vec(d->jnt_axis, 3 * nj)),
+         o_q0 = bl.push(vec(d->qpos0, d->nq)), o_dk = bl.push(dof_kind), o_dq = bl.push(dof_qadr),
+         o_dp = bl.push(dof_parent), o_dl = bl.push(dof_limited), o_dlo = bl.push(dof_lo), o_dhi = bl.push(dof_hi),
+         o_tm = bl.push(taskmask), o_si = bl.push(vec(d->scaled_human_index, d->n_scaled)),
+         o_sc = bl.push(vec(d->scale, d->n_scaled)), o_po = bl.push(vec(d->pos_off, 3 * d->n_scaled)),
+         o_ro = bl.push(vec(d->rot_off, 4 * d->n_scaled)), o_ft = bl.push(vec(d->is_foot, d->n_scaled)),
+         o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot);
+
+  // FK tail tables (KinematicsModel semantics: bodies under the first top-level body, float32, xyzw)
+  const int nbt = nb - 1;
+  std::vector<int> t_parent(nbt, -1), t_dof(nbt, -1);
+  std::vector<float> t_trans(3 * nbt, 0.f), t_rot(4 * nbt, 0.f), t_axis(3 * nbt, 0.f);
+  int root_dofs = 0;
+  if (nb > 1) {
+    int jadr = d->body_jntadr[1], jnum = d->body_jntnum[1];
+    for (int j = jadr; j < jadr + jnum; j++) root_dofs += d->jnt_type[j] == GMR_JNT_FREE ? 6 : 1;
+  }
+  for (int b = 1; b < nb; b++) {
+    int k = b - 1;
+    t_parent[k] = d->body_parentid[b] - 1;
+    for (int i = 0; i < 3; i++) t_trans[3 * k + i] = (float)d->body_pos[3 * b + i];
+    t_rot[4 * k + 0] = (float)d->body_quat[4 * b + 1]; t_rot[4 * k + 1] = (float)d->body_quat[4 * b + 2];
+    t_rot[4 * k + 2] = (float)d->body_quat[4 * b + 3]; t_rot[4 * k + 3] = (float)d->body_quat[4 * b + 0];
+    if (b > 1 && d->body_jntnum[b] == 1) {
+      int j = d->body_jntadr[b];
+      t_dof[k] = d->jnt_dofadr[j] - root_dofs;
+      for (int i = 0; i < 3; i++) t_axis[3 * k + i] = (float)d->jnt_axis[3 * j + i];
+    }
+  }
+
+  gmr_model* m = new gmr_model();
+  m->device = device;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  cudaError_t e = cudaSetDevice(device);
+  if (e == cudaSuccess) e = cudaMalloc(&m->blob, bl.bytes.size());
+  if (e == cudaSuccess) e = cudaMemcpy(m->blob, bl.bytes.data(), bl.bytes.size(), cudaMemcpyHostToDevice);
+  Blob tb;
+  size_t t_p = tb.push(t_parent), t_t = tb.push(t_trans), t_r = tb.push(t_rot), t_a = tb.push(t_axis), t_d = tb.push(t_dof);
+  if (e == cudaSuccess) e = cudaMalloc(&m->tail_blob, tb.bytes.size());
+  if (e == cudaSuccess) e = cudaMemcpy(m->tail_blob, tb.bytes.data(), tb.bytes.size(), cudaMemcpyHostToDevice);
+  cudaSetDevice(prev);
+  if (e != cudaSuccess) {
+    if (m->blob) cudaFree(m->blob);
+    if (m->tail_blob) cudaFree(m->tail_blob);
+    delete m;
+    return fail(-100, std::string("model upload: ") + cudaGetErrorString(e));
+  }
+  m->blob_bytes = bl.bytes.size();
+  DevModel& h = m->host;
+  h.nbody = nb; h.njnt = nj; h.nq = d->nq; h.nv = nv; h.n_human = d->n_human; h.n_scaled = d->n_scaled;
+  h.nlevel = nlevel; h.ref_body = ref_body;
+  for (int k = 0; k < 2; k++) { h.use[k] = d->use_table[k] ? 1 : 0; h.n_task[k] = d->use_table[k] ? d->n_task[k] : 0; }
+  h.max_iter = d->max_iter; h.damping = d->damping; h.converge_eps = d->converge_eps;
+  h.limit_gain = d->limit_gain; h.lm_damping = d->lm_damping; h.timestep = d->timestep;
+  char* B0 = m->blob;
+  h.body_parent = (const int*)(B0 + o_parent); h.body_pos = (const double*)(B0 + o_bpos);
+  h.body_quat = (const double*)(B0 + o_bquat); h.body_jntadr = (const int*)(B0 + o_jadr);
+  h.body_jntnum = (const int*)(B0 + o_jnum); h.level_start = (const int*)(B0 + o_lstart);
+  h.level_body = (const int*)(B0 + o_lbody); h.jnt_type = (const int*)(B0 + o_jtype);
+  h.jnt_qposadr = (const int*)(B0 + o_jq); h.jnt_dofadr = (const int*)(B0 + o_jd);
+  h.jnt_axis = (const double*)(B0 + o_jaxis); h.qpos0 = (const double*)(B0 + o_q0);
+  h.dof_kind = (const int*)(B0 + o_dk); h.dof_qadr = (const int*)(B0 + o_dq); h.dof_parent = (const int*)(B0 + o_dp);
+  h.dof_limited = (const int*)(B0 + o_dl); h.dof_lo = (const double*)(B0 + o_dlo); h.dof_hi = (const double*)(B0 + o_dhi);
+  h.dof_taskmask = (const unsigned*)(B0 + o_tm); h.scaled_index = (const int*)(B0 + o_si);
+  h.scale = (const double*)(B0 + o_sc); h.pos_off = (const double*)(B0 + o_po); h.rot_off = (const double*)(B0 + o_ro);
+  h.is_foot = (const int*)(B0 + o_ft); h.task_body = (const int*)(B0 + o_tb); h.task_src = (const int*)(B0 + o_ts);
+  h.task_wpos = (const double*)(B0 + o_wp); h.task_wrot = (const double*)(B0 + o_wr);
+  m->max_task = std::max(h.n_task[0], h.n_task[1]);
+  char* T0 = m->tail_blob;
+  m->tail.nbody = nbt; m->tail.parent = (const int*)(T0 + t_p); m->tail.trans = (const float*)(T0 + t_t);
+  m->tail.rot_xyzw = (const float*)(T0 + t_r); m->tail.axis = (const float*)(T0 + t_a); m->tail.dof = (const int*)(T0 + t_d);
+  m->tail.ndof = nv - root_dofs;
+  *out = m;
+  return 0;
+}
+
+extern "C" int gmr_model_destroy(gmr_model* m) {
+  if (!m) return 0;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  cudaSetDevice(m->device);
+  if (m->blob) cudaFree(m->blob);
+  if (m->tail_blob) cudaFree(m->tail_blob);
+  cudaSetDevice(prev);
+  delete m;
+  return 0;
+}
+
+// ---------------------------------------------------------------- batch
+static Lay make_layout(int nq, int s, int nv, int nbody, int m) {
+  Lay L{};
+  int o = 0;
+  auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };   // keep 16-byte alignment
+  L.q = take(nq); L.scaled = take(7 * s); L.c = take(nv); L.x = take(nv); L.lo = take(nv); L.hi = take(nv);
+  L.rhs = take(nv); L.H = take(nv * (nv + 1) / 2);
+  const int region = o;
+  L.xpos = take(3 * nbody); L.xquat = take(4 * nbody); L.S = take(6 * nv); L.e = take(6 * m);
+  L.K = take(21 * m); L.g = take(6 * m);
+  L.L = region;                                  // Cholesky factor overlays the kinematics scratch
+  o = std::max(o, region + ((nv * (nv + 1) / 2 + 1) & ~1));
+  L.total = o;
+  L.maxt = GMR_MAX_TASKS;
+  return L;
+}
+
+extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const int32_t* model_of_instance,
+                                int B, void* stream, gmr_batch** out) {
+  if (!models || n_models < 1 || B < 1 || !out) return fail(-1, "bad argument");
+  if (n_models > 1 && !model_of_instance) return fail(-1, "model_of_instance required for n_models > 1");
+  gmr_batch* b = new gmr_batch();
+  b->device = models[0]->device;
+  b->stream = (cudaStream_t)stream;
+  b->B = B; b->n_models = n_models;
+  std::vector<DevModel> hm;
+  for (int i = 0; i < n_models; i++) {
+    gmr_model* m = models[i];
+    if (!m || m->device != b->device) { delete b; return fail(-1, "models must live on one device"); }
+    b->models.push_back(m);
+    hm.push_back(m->host);
+    b->nq_max = std::max(b->nq_max, m->host.nq); b->s_max = std::max(b->s_max, m->host.n_scaled);
+    b->h_max = std::max(b->h_max, m->host.n_human); b->nbody_max = std::max(b->nbody_max, m->host.nbody);
+    b->nv_max = std::max(b->nv_max, m->host.nv); b->m_max = std::max(b->m_max, m->max_task);
+  }
+  if (model_of_instance)
+    for (int i = 0; i < B; i++)
+      if (model_of_instance[i] < 0 || model_of_instance[i] >= n_models) { delete b; return fail(-1, "model_of_instance out of range"); }
+  b->lay = make_layout(b->nq_max, b->s_max, b->nv_max, b->nbody_max, std::max(b->m_max, 1));
+  int prev = 0;
+  cudaGetDevice(&prev);
+  cudaError_t e = cudaSetDevice(b->device);
+  auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
+  alloc((void**)&b->d_models, sizeof(DevModel) * n_models);
+  alloc((void**)&b->d_q, sizeof(double) * (size_t)B * b->nq_max);
+  alloc((void**)&b->d_scale, sizeof(double) * (size_t)B * b->s_max);
+  alloc((void**)&b->d_counter, sizeof(int));
+  if (model_of_instance) alloc((void**)&b->d_model_of, sizeof(int) * (size_t)B);
+  if (e == cudaSuccess) e = cudaMemcpy(b->d_models, hm.data(), sizeof(DevModel) * n_models, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && model_of_instance)
+    e = cudaMemcpy(b->d_model_of, model_of_instance, sizeof(int) * (size_t)B, cudaMemcpyHostToDevice);
+  // launch geometry: as many resident warps as shared memory allows, one instance per warp
+  const size_t per_warp = sizeof(double) * (size_t)b->lay.total;
+  int dev_smem = 0, sms = 0;
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, b->device);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device);
+  if (e == cudaSuccess) {
+    b->warps_per_cta = 4;
+    while (b->warps_per_cta > 1 && per_warp * b->warps_per_cta > (size_t)dev_smem) b->warps_per_cta >>= 1;
+    b->smem_bytes = per_warp * b->warps_per_cta;
+    if (b->smem_bytes > (size_t)dev_smem) e = cudaErrorInvalidConfiguration;
+  }
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(clip_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(clip_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes);
+  int per_sm = 0;
+  if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, clip_kernel<float>, 32 * b->warps_per_cta, b->smem_bytes);
+  if (e == cudaSuccess) {
+    if (per_sm < 1) per_sm = 1;
+    const int need = (B + b->warps_per_cta - 1) / b->warps_per_cta;
+    b->grid = std::min(need, per_sm * sms);
+  }
+  cudaSetDevice(prev);
+  if (e != cudaSuccess) {
+    std::string msg = std::string("batch create: ") + cudaGetErrorString(e);
+    gmr_batch_destroy(b);
+    return fail(-100, msg);
+  }
+  *out = b;
+  int rc = gmr_batch_reset(b, nullptr);
+  if (rc == 0) rc = gmr_batch_set_scale(b, nullptr);
+  if (rc) { std::string msg = g_err; gmr_batch_destroy(b); *out = nullptr; return fail(rc, msg); }
+  return 0;
+}
+
+extern "C" int gmr_batch_destroy(gmr_batch* b) {
+  if (!b) return 0;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  cudaSetDevice(b->device);
+  cudaFree(b->d_models); cudaFree(b->d_q); cudaFree(b->d_scale); cudaFree(b->d_counter);
+  cudaFree(b->d_model_of); cudaFree(b->d_order);
+  cudaSetDevice(prev);
+  delete b;
+  return 0;
+}
+
+namespace {
+struct DevGuard {
+  int prev = 0;
+  explicit DevGuard(int dev) { cudaGetDevice(&prev); cudaSetDevice(dev); }
+  ~DevGuard() { cudaSetDevice(prev); }
+};
+__global__ void fill_rows_kernel(double* dst, int B, int stride, const DevModel* models, const int* model_of, int what) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * stride) return;
+  const int inst = i / stride, k = i % stride;
+  const DevModel& M = models[model_of ? model_of[inst] : 0];
+  if (what == 0) dst[i] = k < M.nq ? M.qpos0[k] : 0.0;
+  else dst[i] = k < M.n_scaled ? M.scale[k] : 0.0;
+}
+}  // namespace
+
+extern "C" int gmr_batch_reset(gmr_batch* b, const double* q0_dev) {
+  if (!b) return fail(-1, "null batch");
+  DevGuard g(b->device);
+  const int n = b->B * b->nq_max;
+  if (q0_dev) CU(cudaMemcpyAsync(b->d_q, q0_dev, sizeof(double) * n, cudaMemcpyDeviceToDevice, b->stream));
+  else fill_rows_kernel<<<(n + 255) / 256, 256, 0, b->stream>>>(b->d_q, b->B, b->nq_max, b->d_models, b->d_model_of, 0);
+  CU(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int gmr_batch_set_scale(gmr_batch* b, const double* scale_dev) {
+  if (!b) return fail(-1, "null batch");
+  DevGuard g(b->device);
+  const int n = b->B * b->s_max;
+  if (scale_dev) CU(cudaMemcpyAsync(b->d_scale, scale_dev, sizeof(double) * n, cudaMemcpyDeviceToDevice, b->stream));
+  else fill_rows_kernel<<<(n + 255) / 256, 256, 0, b->stream>>>(b->d_scale, b->B, b->s_max, b->d_models, b->d_model_of, 1);
+  CU(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int gmr_batch_set_order(gmr_batch* b, const int32_t* order_dev) {
+  if (!b) return fail(-1, "null batch");
+  DevGuard g(b->device);
+  if (!order_dev) { if (b->d_order) { cudaFree(b->d_order); b->d_order = nullptr; } return 0; }
+  if (!b->d_order) CU(cudaMalloc(&b->d_order, sizeof(int) * (size_t)b->B));
+  CU(cudaMemcpyAsync(b->d_order, order_dev, sizeof(int) * (size_t)b->B, cudaMemcpyDeviceToDevice, b->stream));
+  return 0;
+}
+
+extern "C" int gmr_batch_get_state(gmr_batch* b, double* q_dev) {
+  if (!b || !q_dev) return fail(-1, "null argument");
+  DevGuard g(b->device);
+  CU(cudaMemcpyAsync(q_dev, b->d_q, sizeof(double) * (size_t)b->B * b->nq_max, cudaMemcpyDeviceToDevice, b->stream));
+  return 0;
+}
+
+extern "C" int gmr_batch_dims(const gmr_batch* b, int32_t* B, int32_t* nq_max, int32_t* s_max, int32_t* h_max, int32_t* nbody_max) {
+  if (!b) return fail(-1, "null batch");
+  if (B) *B = b->B;
+  if (nq_max) *nq_max = b->nq_max;
+  if (s_max) *s_max = b->s_max;
+  if (h_max) *h_max = b->h_max;
+  if (nbody_max) *nbody_max = b->nbody_max;
+  return 0;
+}
+
+extern "C" int gmr_batch_launch_info(const gmr_batch* b, int32_t* grid, int32_t* warps_per_cta, int32_t* smem_bytes, int32_t* smem_per_instance) {
+  if (!b) return fail(-1, "null batch");
+  if (grid) *grid = b->grid;
+  if (warps_per_cta) *warps_per_cta = b->warps_per_cta;
+  if (smem_bytes) *smem_bytes = (int)b->smem_bytes;
+  if (smem_per_instance) *smem_per_instance = (int)(sizeof(double) * b->lay.total);
+  return 0;
+}
+
+static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const int32_t* T_of_dev, int T_max, int to_ground,
+                        double* qpos_out, double* scaled_out, const gmr_diag* diag) {
+  if (!b || !human_dev) return fail(-1, "null argument");
+  if (dtype != GMR_F32 && dtype != GMR_F64) return fail(-1, "human_dtype must be GMR_F32 or GMR_F64");
+  if (T_max < 1) return fail(-1, "T_max must be >= 1");
+  DevGuard g(b->device);
+  RunArgs a{};
+  a.models = b->d_models; a.model_of = b->d_model_of;
+  a.human = human_dev; a.human_frame_stride = (long long)b->h_max * 7; a.human_inst_stride = a.human_frame_stride * T_max;
+  a.T_of = T_of_dev; a.T_max = T_max; a.to_ground = to_ground;
+  a.scale = b->d_scale; a.s_max = b->s_max; a.q_state = b->d_q; a.nq_max = b->nq_max;
+  a.qpos_out = qpos_out; a.scaled_out = scaled_out;
+  a.err_out = diag ? diag->err_dev : nullptr; a.iters_out = diag ? diag->iters_dev : nullptr; a.nfact_out = diag ? diag->nfact_dev : nullptr;
+  a.counter = b->d_counter; a.order = b->d_order; a.B = b->B; a.lay = b->lay;
+  CU(cudaMemsetAsync(b->d_counter, 0, sizeof(int), b->stream));
+  if (dtype == GMR_F32) clip_kernel<float><<<b->grid, 32 * b->warps_per_cta, b->smem_bytes, b->stream>>>(a);
+  else clip_kernel<double><<<b->grid, 32 * b->warps_per_cta, b->smem_bytes, b->stream>>>(a);
+  CU(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int gmr_batch_step(gmr_batch* b, const void* human_dev, int human_dtype, int offset_to_ground,
+                              double* qpos_out_dev, double* scaled_out_dev, const gmr_diag* diag) {
+  return launch_clips(b, human_dev, human_dtype, nullptr, 1, offset_to_ground, qpos_out_dev, scaled_out_dev, diag);
+}
+
+extern "C" int gmr_batch_run(gmr_batch* b, const void* human_dev, int human_dtype, const int32_t* T_of_instance_dev,
+                             int T_max, int offset_to_ground, double* qpos_out_dev, const gmr_diag* diag) {
+  return launch_clips(b, human_dev, human_dtype, T_of_instance_dev, T_max, offset_to_ground, qpos_out_dev, nullptr, diag);
+}
+
+// ---------------------------------------------------------------- stage entry points
+static StageArgs stage_args(gmr_batch* b) {
+  StageArgs a{};
+  a.models = b->d_models; a.model_of = b->d_model_of; a.B = b->B; a.lay = b->lay;
+  a.nq_max = b->nq_max; a.s_max = b->s_max; a.nbody_max = b->nbody_max; a.nv_max = b->nv_max; a.m_max = std::max(b->m_max, 1);
+  a.scale = b->d_scale; a.q = b->d_q;
+  return a;
+}
+#define STAGE_LAUNCH(kernel, b, a) do { \
+    const int w_ = b->warps_per_cta; \
+    CU(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes)); \
+    kernel<<<(b->B + w_ - 1) / w_, 32 * w_, b->smem_bytes, b->stream>>>(a); \
+    CU(cudaGetLastError()); } while (0)
+
+extern "C" int gmr_target_prep(gmr_batch* b, const void* human_dev, int human_dtype, int offset_to_ground, double* scaled_out_dev) {
+  if (!b || !human_dev || !scaled_out_dev) return fail(-1, "null argument");
+  DevGuard g(b->device);
+  StageArgs a = stage_args(b);
+  a.human = human_dev; a.human_inst_stride = (long long)b->h_max * 7; a.to_ground = offset_to_ground; a.scaled_out = scaled_out_dev;
+  if (human_dtype == GMR_F32) STAGE_LAUNCH(prep_kernel<float>, b, a);
+  else if (human_dtype == GMR_F64) STAGE_LAUNCH(prep_kernel<double>, b, a);
+  else return fail(-1, "bad human_dtype");
+  return 0;
+}
+
+extern "C" int gmr_fk(gmr_batch* b, const double* q_dev, double* xpos_out_dev, double* xquat_out_dev) {
+  if (!b || !xpos_out_dev || !xquat_out_dev) return fail(-1, "null argument");
+  DevGuard g(b->device);
+  StageArgs a = stage_args(b);
+  if (q_dev) a.q = q_dev;
+  a.xpos_out = xpos_out_dev; a.xquat_out = xquat_out_dev;
+  STAGE_LAUNCH(fk_kernel, b, a);
+  return 0;
+}
+
+extern "C" int gmr_build_qp(gmr_batch* b, int stage, const double* scaled_dev, double* e_out_dev, double* H_out_dev,
+                            double* c_out_dev, double* lo_out_dev, double* hi_out_dev) {
+  if (!b || !scaled_dev || !H_out_dev || !c_out_dev || !lo_out_dev || !hi_out_dev) return fail(-1, "null argument");
+  if (stage < 0 || stage > 1) return fail(-1, "stage must be 0 or 1");
+  DevGuard g(b->device);
+  StageArgs a = stage_args(b);
+  a.stage = stage; a.scaled = scaled_dev; a.e_out = e_out_dev; a.H_out = H_out_dev; a.c_out = c_out_dev;
+  a.lo_out = lo_out_dev; a.hi_out = hi_out_dev;
+  STAGE_LAUNCH(build_qp_kernel, b, a);
+  return 0;
+}
+
+extern "C" int gmr_qp_solve(int device, void* stream, int n_qp, int n, const double* H_dev, const double* c_dev,
+                            const double* lo_dev, const double* hi_dev, double* x_out_dev, int32_t* nfact_out_dev) {
+  if (n_qp < 1 || n < 1 || n > GMR_MAX_NV) return fail(-1, "bad QP size (n <= 64)");
+  if (!H_dev || !c_dev || !lo_dev || !hi_dev || !x_out_dev) return fail(-1, "null argument");
+  DevGuard g(device);
+  const int w = 4;
+  const size_t smem = sizeof(double) * (size_t)w * (n * (n + 1) + 5 * n);
+  CU(cudaFuncSetAttribute(qp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  qp_kernel<<<(n_qp + w - 1) / w, 32 * w, smem, (cudaStream_t)stream>>>(n_qp, n, H_dev, c_dev, lo_dev, hi_dev, x_out_dev, nfact_out_dev);
+  CU(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int gmr_fk_bodies_f32(gmr_model* m, void* stream, int N, const float* root_pos_dev, const float* root_rot_xyzw_dev,
+                                 const float* dof_pos_dev, float* body_pos_out_dev, float* body_rot_out_dev) {
+  if (!m || N < 1 || !root_pos_dev || !root_rot_xyzw_dev || !dof_pos_dev || !body_pos_out_dev) return fail(-1, "bad argument");
+  DevGuard g(m->device);
+  float* scratch = nullptr;
+  if (!body_rot_out_dev) CU(cudaMallocAsync(&scratch, sizeof(float) * (size_t)N * m->tail.nbody * 4, (cudaStream_t)stream));
+  fk_tail_kernel<<<(N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(m->tail, N, root_pos_dev, root_rot_xyzw_dev, dof_pos_dev,
+                                                                    body_pos_out_dev, body_rot_out_dev, scratch);
+  cudaError_t e = cudaGetLastError();
+  if (scratch) cudaFreeAsync(scratch, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(-100, cudaGetErrorString(e));
+  return 0;
+}

@@ -1,0 +1,268 @@
+// gmr_clip.cuh - the fused clip kernel (Kernels 1-4 of the north star in one launch) and the
+// per-stage kernels that expose the same device code for parity tests.
+//
+// Work decomposition: one warp = one IK instance (clip x robot) for the whole clip; frames are
+// strictly sequential inside a clip (warm start, motion_retarget.py:185), clips are independent.
+// Warps pull instances from a global atomic queue (optionally in a host-given order, longest
+// first), so ragged clip lengths balance across the 148 SMs without a tail.
+#pragma once
+#include "gmr_stages.cuh"
+
+namespace gmr {
+
+struct RunArgs {
+  const DevModel* models;        // [n_models]
+  const int* model_of;           // [B] or null (all 0)
+  const void* human;             // [B, T_max, h_max, 7]
+  long long human_inst_stride;   // elements between instances
+  long long human_frame_stride;  // elements between frames
+  const int* T_of;               // [B] or null
+  int T_max;
+  int to_ground;
+  const double* scale;           // [B, s_max]
+  int s_max;
+  double* q_state;               // [B, nq_max] in/out
+  int nq_max;
+  double* qpos_out;              // [B, T_max, nq_max] or null
+  double* scaled_out;            // [B, T_max, s_max, 7] or null
+  double* err_out;               // [B, T_max, 2] or null
+  int* iters_out;                // [B, T_max, 2] or null
+  int* nfact_out;                // [B, T_max] or null
+  int* counter;                  // work queue head
+  const int* order;              // [B] or null
+  int B;
+  Lay lay;
+};
+
+// One solve_ik + integrate_inplace (+ the error evaluation that follows it in the reference loop).
+__device__ __forceinline__ double ik_iteration(const DevModel& M, const Lay& lay, double* sm, int stage, int lane, int& nfact) {
+  const double mu = stage_stiffness(M, lay, sm, stage, lane);
+  stage_assemble(M, lay, sm, stage, mu, lane);
+  const int nf = qp_solve(M.nv, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.rhs, sm + lay.x, lane);
+  nfact = (nf < 0 || nfact < 0) ? -abs(nfact) - abs(nf) : nfact + nf;
+  stage_integrate(M, lay, sm, lane);
+  stage_fk(M, lay, sm, lane);
+  return stage_errors(M, lay, sm, stage, lane);
+}
+
+template <typename TIn>
+__global__ void __launch_bounds__(128) clip_kernel(const RunArgs a) {
+  extern __shared__ double smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const Lay lay = a.lay;
+  double* sm = smem + (size_t)warp * lay.total;
+  for (;;) {
+    int slot = 0;
+    if (lane == 0) slot = atomicAdd(a.counter, 1);
+    slot = __shfl_sync(GMR_FULL, slot, 0);
+    if (slot >= a.B) break;
+    const int inst = a.order ? a.order[slot] : slot;
+    const DevModel& M = a.models[a.model_of ? a.model_of[inst] : 0];
+    const int T = a.T_of ? min(a.T_of[inst], a.T_max) : a.T_max;
+    double* qs = a.q_state + (size_t)inst * a.nq_max;
+    for (int i = lane; i < M.nq; i += 32) sm[lay.q + i] = qs[i];
+    __syncwarp();
+    stage_fk(M, lay, sm, lane);
+    const double* scale = a.scale + (size_t)inst * a.s_max;
+    const TIn* human = (const TIn*)a.human + (size_t)inst * a.human_inst_stride;
+    for (int t = 0; t < T; t++) {
+      stage_prep<TIn>(M, lay, sm, human + (size_t)t * a.human_frame_stride, scale, a.to_ground != 0, lane);
+      const size_t o = (size_t)inst * a.T_max + t;
+      if (a.scaled_out) {
+        double* so = a.scaled_out + o * a.s_max * 7;
+        for (int i = lane; i < M.n_scaled * 7; i += 32) so[i] = sm[lay.scaled + i];
+      }
+      int nfact = 0;
+#pragma unroll 1
+      for (int stage = 0; stage < 2; stage++) {
+        double err = 0;
+        int solves = 0;
+        if (M.use[stage]) {
+          // motion_retarget.py:143-161 / :163-182
+          double curr = stage_errors(M, lay, sm, stage, lane);
+          double next = ik_iteration(M, lay, sm, stage, lane, nfact);
+          int it = 0;
+          while (curr - next > M.converge_eps && it < M.max_iter) {
+            curr = next;
+            next = ik_iteration(M, lay, sm, stage, lane, nfact);
+            it++;
+          }
+          err = next;
+          solves = it + 1;
+        }
+        if (lane == 0) {
+          if (a.err_out) a.err_out[2 * o + stage] = err;
+          if (a.iters_out) a.iters_out[2 * o + stage] = solves;
+        }
+      }
+      if (lane == 0 && a.nfact_out) a.nfact_out[o] = nfact;
+      if (a.qpos_out) {
+        double* qo = a.qpos_out + o * a.nq_max;
+        for (int i = lane; i < M.nq; i += 32) qo[i] = sm[lay.q + i];
+      }
+    }
+    for (int i = lane; i < M.nq; i += 32) qs[i] = sm[lay.q + i];
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------- per-stage kernels (parity tests)
+struct StageArgs {
+  const DevModel* models;
+  const int* model_of;
+  int B;
+  Lay lay;
+  int nq_max, s_max, nbody_max, nv_max, m_max;
+  int stage, to_ground;
+  const void* human;      // [B,h,7]
+  long long human_inst_stride;
+  const double* scale;    // [B,s_max]
+  const double* q;        // [B,nq_max]
+  const double* scaled;   // [B,s_max,7]
+  double *scaled_out, *xpos_out, *xquat_out, *e_out, *H_out, *c_out, *lo_out, *hi_out;
+};
+
+template <typename TIn>
+__global__ void prep_kernel(const StageArgs a) {
+  extern __shared__ double smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (inst >= a.B) return;
+  double* sm = smem + (size_t)warp * a.lay.total;
+  const DevModel& M = a.models[a.model_of ? a.model_of[inst] : 0];
+  stage_prep<TIn>(M, a.lay, sm, (const TIn*)a.human + (size_t)inst * a.human_inst_stride,
+                  a.scale + (size_t)inst * a.s_max, a.to_ground != 0, lane);
+  double* so = a.scaled_out + (size_t)inst * a.s_max * 7;
+  for (int i = lane; i < M.n_scaled * 7; i += 32) so[i] = sm[a.lay.scaled + i];
+}
+
+__global__ void fk_kernel(const StageArgs a) {
+  extern __shared__ double smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (inst >= a.B) return;
+  double* sm = smem + (size_t)warp * a.lay.total;
+  const DevModel& M = a.models[a.model_of ? a.model_of[inst] : 0];
+  for (int i = lane; i < M.nq; i += 32) sm[a.lay.q + i] = a.q[(size_t)inst * a.nq_max + i];
+  __syncwarp();
+  stage_fk(M, a.lay, sm, lane);
+  for (int i = lane; i < M.nbody * 3; i += 32) a.xpos_out[(size_t)inst * a.nbody_max * 3 + i] = sm[a.lay.xpos + i];
+  for (int i = lane; i < M.nbody * 4; i += 32) a.xquat_out[(size_t)inst * a.nbody_max * 4 + i] = sm[a.lay.xquat + i];
+}
+
+__global__ void build_qp_kernel(const StageArgs a) {
+  extern __shared__ double smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (inst >= a.B) return;
+  const Lay& lay = a.lay;
+  double* sm = smem + (size_t)warp * lay.total;
+  const DevModel& M = a.models[a.model_of ? a.model_of[inst] : 0];
+  for (int i = lane; i < M.nq; i += 32) sm[lay.q + i] = a.q[(size_t)inst * a.nq_max + i];
+  for (int i = lane; i < M.n_scaled * 7; i += 32) sm[lay.scaled + i] = a.scaled[(size_t)inst * a.s_max * 7 + i];
+  __syncwarp();
+  stage_fk(M, lay, sm, lane);
+  stage_errors(M, lay, sm, a.stage, lane);
+  const double mu = stage_stiffness(M, lay, sm, a.stage, lane);
+  stage_assemble(M, lay, sm, a.stage, mu, lane);
+  const int n = M.nv, m = M.n_task[a.stage];
+  if (a.e_out) for (int i = lane; i < 6 * m; i += 32) a.e_out[(size_t)inst * a.m_max * 6 + i] = sm[lay.e + i];
+  double* Ho = a.H_out + (size_t)inst * a.nv_max * a.nv_max;
+  for (int idx = lane; idx < n * n; idx += 32) {
+    const int i = idx / n, j = idx % n;
+    Ho[i * a.nv_max + j] = sm[lay.H + (i >= j ? tri(i) + j : tri(j) + i)];
+  }
+  for (int i = lane; i < n; i += 32) {
+    a.c_out[(size_t)inst * a.nv_max + i] = sm[lay.c + i];
+    a.lo_out[(size_t)inst * a.nv_max + i] = sm[lay.lo + i];
+    a.hi_out[(size_t)inst * a.nv_max + i] = sm[lay.hi + i];
+  }
+}
+
+// generic box QP: H [n_qp, n, n] full symmetric
+__global__ void qp_kernel(int n_qp, int n, const double* H, const double* c, const double* lo, const double* hi,
+                          double* x_out, int* nfact_out) {
+  extern __shared__ double smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (inst >= n_qp) return;
+  const int nH = n * (n + 1) / 2;
+  double* sm = smem + (size_t)warp * (2 * nH + 5 * n);
+  double *sH = sm, *sL = sm + nH, *sc = sL + nH, *slo = sc + n, *shi = slo + n, *srhs = shi + n, *sx = srhs + n;
+  const double* Hi = H + (size_t)inst * n * n;
+  for (int idx = lane; idx < n * n; idx += 32) {
+    const int i = idx / n, j = idx % n;
+    if (j <= i) sH[tri(i) + j] = Hi[idx];
+  }
+  for (int i = lane; i < n; i += 32) { sc[i] = c[(size_t)inst * n + i]; slo[i] = lo[(size_t)inst * n + i]; shi[i] = hi[(size_t)inst * n + i]; }
+  __syncwarp();
+  const int nf = qp_solve(n, sH, sc, slo, shi, sL, srhs, sx, lane);
+  for (int i = lane; i < n; i += 32) x_out[(size_t)inst * n + i] = sx[i];
+  if (lane == 0 && nfact_out) nfact_out[inst] = nf;
+}
+
+// ---------------------------------------------------------------- FK tail, float32 (drivers' local_body_pos)
+// KinematicsModel.forward_kinematics (kinematics_model.py:213-246): xyzw quaternions, float32,
+// body 0 = the root body (given pose), one thread per sample walking the bodies in order.
+struct FkTailModel {
+  int nbody;                 // bodies excluding world
+  const int* parent;         // [nbody] index among these bodies, -1 for the root
+  const float* trans;        // [nbody*3]
+  const float* rot_xyzw;     // [nbody*4]
+  const float* axis;         // [nbody*3] normalised joint axis (0 if none)
+  const int* dof;            // [nbody] index into dof_pos or -1
+  int ndof;
+};
+
+__device__ __forceinline__ void quat_mul_xyzw(const float* a, const float* b, float* o) {
+  // same factorisation as torch_utils.quat_mul (torch_utils.py:118-138)
+  const float x1 = a[0], y1 = a[1], z1 = a[2], w1 = a[3], x2 = b[0], y2 = b[1], z2 = b[2], w2 = b[3];
+  const float ww = (z1 + x1) * (x2 + y2), yy = (w1 - y1) * (w2 + z2), zz = (w1 + y1) * (w2 - z2);
+  const float xx = ww + yy + zz;
+  const float qq = 0.5f * (xx + (z1 - x1) * (x2 - y2));
+  o[3] = qq - ww + (z1 - y1) * (y2 - z2);
+  o[0] = qq - xx + (x1 + w1) * (x2 + w2);
+  o[1] = qq - yy + (w1 - x1) * (y2 + z2);
+  o[2] = qq - zz + (z1 + y1) * (w2 - x2);
+}
+__device__ __forceinline__ void quat_rotate_xyzw(const float* q, const float* v, float* o) {
+  // torch_utils.quat_rotate (torch_utils.py:66-75): a + b + c
+  const float w = q[3];
+  const float s = 2.0f * w * w - 1.0f;
+  const float cx = q[1] * v[2] - q[2] * v[1], cy = q[2] * v[0] - q[0] * v[2], cz = q[0] * v[1] - q[1] * v[0];
+  const float d = 2.0f * (q[0] * v[0] + q[1] * v[1] + q[2] * v[2]);
+  o[0] = v[0] * s + cx * w * 2.0f + q[0] * d;
+  o[1] = v[1] * s + cy * w * 2.0f + q[1] * d;
+  o[2] = v[2] * s + cz * w * 2.0f + q[2] * d;
+}
+
+__global__ void fk_tail_kernel(FkTailModel m, int N, const float* root_pos, const float* root_rot, const float* dof_pos,
+                               float* body_pos, float* body_rot_or_null, float* rot_scratch) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float* bp = body_pos + (size_t)n * m.nbody * 3;
+  float* br = (body_rot_or_null ? body_rot_or_null : rot_scratch) + (size_t)n * m.nbody * 4;
+  for (int k = 0; k < 3; k++) bp[k] = root_pos[3 * n + k];
+  for (int k = 0; k < 4; k++) br[k] = root_rot[4 * n + k];
+  for (int j = 1; j < m.nbody; j++) {
+    const int p = m.parent[j];
+    float jr[4] = {0.f, 0.f, 0.f, 1.f};
+    const int d = m.dof[j];
+    if (d >= 0) {
+      // axis_angle_to_quat (torch_utils.py:354-359): normalize(axis) * sin(theta/2), cos(theta/2), then quat_unit
+      const float th = dof_pos[(size_t)n * m.ndof + d] / 2.0f;
+      const float s = sinf(th), c = cosf(th);
+      jr[0] = m.axis[3 * j] * s; jr[1] = m.axis[3 * j + 1] * s; jr[2] = m.axis[3 * j + 2] * s; jr[3] = c;
+      const float nn = fmaxf(sqrtf(jr[0] * jr[0] + jr[1] * jr[1] + jr[2] * jr[2] + jr[3] * jr[3]), 1e-9f);
+      jr[0] /= nn; jr[1] /= nn; jr[2] /= nn; jr[3] /= nn;
+    }
+    float pr[4] = {br[4 * p], br[4 * p + 1], br[4 * p + 2], br[4 * p + 3]}, wt[3], lr[4], cr[4];
+    quat_rotate_xyzw(pr, m.trans + 3 * j, wt);
+    for (int k = 0; k < 3; k++) bp[3 * j + k] = bp[3 * p + k] + wt[k];
+    quat_mul_xyzw(m.rot_xyzw + 4 * j, jr, lr);
+    quat_mul_xyzw(pr, lr, cr);
+    for (int k = 0; k < 4; k++) br[4 * j + k] = cr[k];
+  }
+}
+
+}  // namespace gmr

@@ -1,0 +1,139 @@
+// gmr_device.cuh - device-side data structures and small math helpers (sm_100a).
+//
+// One warp owns one IK instance (clip x robot).  All arithmetic is float64: the reference
+// path is float64 end to end (numpy / mjtNum) and its convergence rule
+// `curr - next > 0.001` (motion_retarget.py:153,172) is a discontinuous decision on an
+// error norm, so reduced precision would flip iterations; B200 issues FP64 FMAs at half
+// the FP32 rate, which is plenty for a latency/issue-bound kernel.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#define GMR_FULL 0xffffffffu
+
+namespace gmr {
+
+// dof kinds (derived from the joint type at flatten time)
+enum : int { DOF_FREE_T = 0, DOF_FREE_R = 1, DOF_SLIDE = 2, DOF_HINGE = 3 };
+
+// Flattened (source, robot) constants, immutable, in global memory (read through L1).
+// Kinematic tree replaces mj.MjModel (motion_retarget.py:27); task tables replace the
+// FrameTask lists (:78-114); prep tables replace pos/rot_offsets1 + human_scale_table.
+struct DevModel {
+  int nbody, njnt, nq, nv, n_human, n_scaled, nlevel, ref_body;
+  int use[2], n_task[2];
+  int max_iter;
+  double damping, converge_eps, limit_gain, lm_damping, timestep;
+  // bodies
+  const int* body_parent;    // [nbody]
+  const double* body_pos;    // [nbody*3]
+  const double* body_quat;   // [nbody*4]
+  const int* body_jntadr;    // [nbody]
+  const int* body_jntnum;    // [nbody]
+  const int* level_start;    // [nlevel+1] into level_body (level 1 = children of world)
+  const int* level_body;     // [nbody-1] body ids sorted by depth
+  // joints
+  const int* jnt_type;       // [njnt]
+  const int* jnt_qposadr;    // [njnt]
+  const int* jnt_dofadr;     // [njnt]
+  const double* jnt_axis;    // [njnt*3]
+  const double* qpos0;       // [nq]
+  // dofs
+  const int* dof_kind;       // [nv]
+  const int* dof_qadr;       // [nv] qpos index (free rot dofs: index of the quaternion w)
+  const int* dof_parent;     // [nv] parent dof in the kinematic tree, -1 at the top
+  const int* dof_limited;    // [nv]
+  const double* dof_lo;      // [nv] joint range lower
+  const double* dof_hi;      // [nv]
+  const unsigned* dof_taskmask;  // [2*nv] bit t set: task t of the stage is in the dof's subtree
+  // target preparation
+  const int* scaled_index;   // [s] body index inside a human frame
+  const double* scale;       // [s]
+  const double* pos_off;     // [s*3]
+  const double* rot_off;     // [s*4]
+  const int* is_foot;        // [s]
+  // tasks, stage-major: [2*MAXT]
+  const int* task_body;
+  const int* task_src;
+  const double* task_wpos;
+  const double* task_wrot;
+};
+
+// Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
+struct Lay {
+  int q, scaled, c, x, lo, hi, rhs, H;    // persistent across the QP solve
+  int xpos, xquat, S, e, K, g;            // kinematics / assembly scratch ...
+  int L;                                  // ... overlaid by the Cholesky factor during the solve
+  int total;                              // doubles per warp
+  int maxt;                               // stride of the stage-major task tables
+};
+
+// ---------------------------------------------------------------- quaternion / vector helpers (wxyz)
+__device__ __forceinline__ void qmul(const double* a, const double* b, double* o) {
+  double w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+  double x = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  double y = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
+  double z = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+  o[0] = w; o[1] = x; o[2] = y; o[3] = z;
+}
+// v' = R(q) v
+__device__ __forceinline__ void qrot(const double* q, const double* v, double* o) {
+  double tx = 2.0 * (q[2] * v[2] - q[3] * v[1]);
+  double ty = 2.0 * (q[3] * v[0] - q[1] * v[2]);
+  double tz = 2.0 * (q[1] * v[1] - q[2] * v[0]);
+  double ox = v[0] + q[0] * tx + (q[2] * tz - q[3] * ty);
+  double oy = v[1] + q[0] * ty + (q[3] * tx - q[1] * tz);
+  double oz = v[2] + q[0] * tz + (q[1] * ty - q[2] * tx);
+  o[0] = ox; o[1] = oy; o[2] = oz;
+}
+// v' = R(q)^T v
+__device__ __forceinline__ void qrot_inv(const double* q, const double* v, double* o) {
+  double c[4] = {q[0], -q[1], -q[2], -q[3]};
+  qrot(c, v, o);
+}
+__device__ __forceinline__ void q2mat(const double* q, double* m) {
+  double w = q[0], x = q[1], y = q[2], z = q[3];
+  m[0] = 1 - 2 * (y * y + z * z); m[1] = 2 * (x * y - w * z); m[2] = 2 * (x * z + w * y);
+  m[3] = 2 * (x * y + w * z); m[4] = 1 - 2 * (x * x + z * z); m[5] = 2 * (y * z - w * x);
+  m[6] = 2 * (x * z - w * y); m[7] = 2 * (y * z + w * x); m[8] = 1 - 2 * (x * x + y * y);
+}
+__device__ __forceinline__ void normalize4(double* q) {   // mju_normalize4
+  double n2 = q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+  if (n2 < 1e-30) { q[0] = 1; q[1] = q[2] = q[3] = 0; return; }
+  double inv = 1.0 / sqrt(n2);
+  q[0] *= inv; q[1] *= inv; q[2] *= inv; q[3] *= inv;
+}
+__device__ __forceinline__ void cross3(const double* a, const double* b, double* o) {
+  double x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2], z = a[0] * b[1] - a[1] * b[0];
+  o[0] = x; o[1] = y; o[2] = z;
+}
+// C = A B (3x3 row-major); C may alias neither input
+__device__ __forceinline__ void mm3(const double* A, const double* B, double* C) {
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) C[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+}
+// C = A^T B
+__device__ __forceinline__ void mtm3(const double* A, const double* B, double* C) {
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) C[3 * i + j] = A[i] * B[j] + A[3 + i] * B[3 + j] + A[6 + i] * B[6 + j];
+}
+__device__ __forceinline__ void skew3(const double* w, double* S) {
+  S[0] = 0; S[1] = -w[2]; S[2] = w[1]; S[3] = w[2]; S[4] = 0; S[5] = -w[0]; S[6] = -w[1]; S[7] = w[0]; S[8] = 0;
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(GMR_FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(GMR_FULL, v, o));
+  return v;
+}
+
+}  // namespace gmr

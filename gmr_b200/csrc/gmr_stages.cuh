@@ -1,0 +1,519 @@
+// gmr_stages.cuh - the warp-level stages of one retarget() call.
+//
+//   stage_prep      Kernel 1  scale + offset (+ground)        motion_retarget.py:209-270
+//   stage_fk        Kernel 2  mj_kinematics + spatial axes    (mink Configuration.update)
+//   stage_errors    Kernel 2  FrameTask.compute_error         motion_retarget.py:188-200
+//   stage_stiffness Kernel 2  FrameTask.compute_jacobian, folded into a 6x6 stiffness
+//   stage_assemble  Kernel 3  mink build_ik: H, c, box
+//   qp_solve        Kernel 3  exact box QP (stands in for daqp)
+//   stage_integrate Kernel 4  mj_integratePos
+// Kernel 4's convergence control lives in gmr_clip.cuh.
+//
+// Every function is called by all 32 lanes of the owning warp with warp-uniform
+// arguments; `sm` is the warp's private shared-memory block laid out by `Lay`.
+#pragma once
+#include "gmr_device.cuh"
+
+namespace gmr {
+
+#define LIE_EPS 1e-10   // mink get_epsilon(float64)
+
+// ------------------------------------------------------------------ Kernel 1: target preparation
+// lane i < s handles scaled body i (entry 0 = human root).  Reads one frame of the human
+// stream (7 numbers per body, float or double), writes sm[scaled + 7*i .. +7] = pos, quat wxyz.
+template <typename TIn>
+__device__ __forceinline__ void stage_prep(const DevModel& M, const Lay& lay, double* sm, const TIn* frame,
+                                           const double* scale, bool to_ground, int lane) {
+  const int s = M.n_scaled;
+  double p[3] = {0, 0, 0}, q[4] = {1, 0, 0, 0};
+  if (lane < s) {
+    const TIn* b = frame + 7 * __ldg(M.scaled_index + lane);
+    p[0] = (double)b[0]; p[1] = (double)b[1]; p[2] = (double)b[2];
+    q[0] = (double)b[3]; q[1] = (double)b[4]; q[2] = (double)b[5]; q[3] = (double)b[6];
+  }
+  // root position to every lane
+  double r0 = __shfl_sync(GMR_FULL, p[0], 0), r1 = __shfl_sync(GMR_FULL, p[1], 0), r2 = __shfl_sync(GMR_FULL, p[2], 0);
+  double out[7] = {0, 0, 0, 1, 0, 0, 0};
+  if (lane < s) {
+    double sc = scale[lane], s0 = scale[0];
+    double pos[3];
+    if (lane == 0) { pos[0] = s0 * r0; pos[1] = s0 * r1; pos[2] = s0 * r2; }
+    else { pos[0] = (p[0] - r0) * sc + s0 * r0; pos[1] = (p[1] - r1) * sc + s0 * r1; pos[2] = (p[2] - r2) * sc + s0 * r2; }
+    // scipy Rotation normalises on from_quat and the product is unit again
+    double n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    q[0] /= n; q[1] /= n; q[2] /= n; q[3] /= n;
+    double ro[4] = {__ldg(M.rot_off + 4 * lane), __ldg(M.rot_off + 4 * lane + 1), __ldg(M.rot_off + 4 * lane + 2), __ldg(M.rot_off + 4 * lane + 3)};
+    double uq[4];
+    qmul(q, ro, uq);
+    n = sqrt(uq[0] * uq[0] + uq[1] * uq[1] + uq[2] * uq[2] + uq[3] * uq[3]);
+    uq[0] /= n; uq[1] /= n; uq[2] /= n; uq[3] /= n;
+    double po[3] = {__ldg(M.pos_off + 3 * lane), __ldg(M.pos_off + 3 * lane + 1), __ldg(M.pos_off + 3 * lane + 2)}, off[3];
+    qrot(uq, po, off);
+    out[0] = pos[0] + off[0]; out[1] = pos[1] + off[1]; out[2] = pos[2] + off[2];
+    out[3] = uq[0]; out[4] = uq[1]; out[5] = uq[2]; out[6] = uq[3];
+  }
+  if (to_ground) {   // motion_retarget.py:252-270
+    double z = (lane < s && __ldg(M.is_foot + lane)) ? out[2] : INFINITY;
+    double lowest = warp_min(z);
+    out[2] = out[2] - lowest + 0.1;
+  }
+  if (lane < s) {
+    double* d = sm + lay.scaled + 7 * lane;
+#pragma unroll
+    for (int k = 0; k < 7; k++) d[k] = out[k];
+  }
+  __syncwarp();
+}
+
+// ------------------------------------------------------------------ Kernel 2: forward kinematics
+// Level-synchronous mj_kinematics: bodies of one depth in parallel (one lane each), levels in
+// sequence.  Also writes the spatial axis S[dof] = (v_O, w): twist of the dof expressed at the
+// reference point O = origin of the floating base (world origin if there is none), so that the
+// geometric Jacobian column of ANY descendant frame at x is [v_O + w x (x - O); w].
+__device__ __forceinline__ void stage_fk(const DevModel& M, const Lay& lay, double* sm, int lane) {
+  const double* q = sm + lay.q;
+  double* xpos = sm + lay.xpos;
+  double* xquat = sm + lay.xquat;
+  double* S = sm + lay.S;
+  if (lane == 0) { xpos[0] = xpos[1] = xpos[2] = 0; xquat[0] = 1; xquat[1] = xquat[2] = xquat[3] = 0; }
+  __syncwarp();
+  const int ref = M.ref_body;
+  for (int lv = 0; lv < M.nlevel; lv++) {
+    const int beg = __ldg(M.level_start + lv), end = __ldg(M.level_start + lv + 1);
+    for (int idx = beg + lane; idx < end; idx += 32) {
+      const int b = __ldg(M.level_body + idx);
+      const int jadr = __ldg(M.body_jntadr + b), jnum = __ldg(M.body_jntnum + b);
+      double pos[3], quat[4];
+      if (jnum == 1 && __ldg(M.jnt_type + jadr) == 0) {   // free joint
+        const int qa = __ldg(M.jnt_qposadr + jadr), da = __ldg(M.jnt_dofadr + jadr);
+        pos[0] = q[qa]; pos[1] = q[qa + 1]; pos[2] = q[qa + 2];
+        quat[0] = q[qa + 3]; quat[1] = q[qa + 4]; quat[2] = q[qa + 5]; quat[3] = q[qa + 6];
+        normalize4(quat);
+        double R[9];
+        q2mat(quat, R);
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+          double* st = S + 6 * (da + i);
+          st[0] = (i == 0); st[1] = (i == 1); st[2] = (i == 2); st[3] = st[4] = st[5] = 0;
+          double* sr = S + 6 * (da + 3 + i);
+          // O = this body's origin -> v_O = 0
+          sr[0] = sr[1] = sr[2] = 0; sr[3] = R[i]; sr[4] = R[3 + i]; sr[5] = R[6 + i];
+        }
+      } else {
+        const int p = __ldg(M.body_parent + b);
+        double pq[4] = {xquat[4 * p], xquat[4 * p + 1], xquat[4 * p + 2], xquat[4 * p + 3]};
+        double bp[3] = {__ldg(M.body_pos + 3 * b), __ldg(M.body_pos + 3 * b + 1), __ldg(M.body_pos + 3 * b + 2)};
+        double bq[4] = {__ldg(M.body_quat + 4 * b), __ldg(M.body_quat + 4 * b + 1), __ldg(M.body_quat + 4 * b + 2), __ldg(M.body_quat + 4 * b + 3)};
+        double t[3];
+        qrot(pq, bp, t);
+        pos[0] = xpos[3 * p] + t[0]; pos[1] = xpos[3 * p + 1] + t[1]; pos[2] = xpos[3 * p + 2] + t[2];
+        qmul(pq, bq, quat);
+        double O[3] = {0, 0, 0};
+        if (jnum > 0 && ref > 0) { O[0] = xpos[3 * ref]; O[1] = xpos[3 * ref + 1]; O[2] = xpos[3 * ref + 2]; }
+        for (int j = jadr; j < jadr + jnum; j++) {
+          const int qa = __ldg(M.jnt_qposadr + j), da = __ldg(M.jnt_dofadr + j);
+          double ax[3] = {__ldg(M.jnt_axis + 3 * j), __ldg(M.jnt_axis + 3 * j + 1), __ldg(M.jnt_axis + 3 * j + 2)}, aw[3];
+          qrot(quat, ax, aw);
+          const double val = q[qa] - __ldg(M.qpos0 + qa);
+          double* sd = S + 6 * da;
+          if (__ldg(M.jnt_type + j) == 2) {   // slide
+            sd[0] = aw[0]; sd[1] = aw[1]; sd[2] = aw[2]; sd[3] = sd[4] = sd[5] = 0;
+            pos[0] += aw[0] * val; pos[1] += aw[1] * val; pos[2] += aw[2] * val;
+          } else {                            // hinge, anchor = body origin (jnt_pos = 0)
+            double r[3] = {O[0] - pos[0], O[1] - pos[1], O[2] - pos[2]}, v[3];
+            cross3(aw, r, v);
+            sd[0] = v[0]; sd[1] = v[1]; sd[2] = v[2]; sd[3] = aw[0]; sd[4] = aw[1]; sd[5] = aw[2];
+            double sh, ch;
+            sincos(0.5 * val, &sh, &ch);
+            double ql[4] = {ch, sh * ax[0], sh * ax[1], sh * ax[2]}, nq[4];
+            qmul(quat, ql, nq);
+            quat[0] = nq[0]; quat[1] = nq[1]; quat[2] = nq[2]; quat[3] = nq[3];
+          }
+        }
+        normalize4(quat);
+      }
+      xpos[3 * b] = pos[0]; xpos[3 * b + 1] = pos[1]; xpos[3 * b + 2] = pos[2];
+      xquat[4 * b] = quat[0]; xquat[4 * b + 1] = quat[1]; xquat[4 * b + 2] = quat[2]; xquat[4 * b + 3] = quat[3];
+    }
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------ mink SO3/SE3 log
+__device__ __forceinline__ void se3_log_dev(const double* q, const double* p, double* out) {
+  const double qw = q[0], n2 = q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+  double f;
+  if (n2 < LIE_EPS) {
+    f = 2.0 / qw - 2.0 / 3.0 * n2 / (qw * qw * qw);
+  } else {
+    const double n = sqrt(n2);
+    if (fabs(qw) < LIE_EPS) f = (qw > 0 ? 1.0 : -1.0) * 3.14159265358979323846 / n;
+    else f = 2.0 * atan2(qw < 0 ? -n : n, fabs(qw)) / n;
+  }
+  const double w0 = f * q[1], w1 = f * q[2], w2 = f * q[3];
+  const double th2 = w0 * w0 + w1 * w1 + w2 * w2;
+  double k;
+  if (th2 < LIE_EPS) k = 1.0 / 12.0;
+  else { const double th = sqrt(th2); double sh, ch; sincos(0.5 * th, &sh, &ch); k = (1.0 - 0.5 * th * ch / sh) / th2; }
+  // V^-1 p = p - 1/2 w x p + k w x (w x p)
+  double w[3] = {w0, w1, w2}, c1[3], c2[3];
+  cross3(w, p, c1);
+  cross3(w, c1, c2);
+  out[0] = p[0] - 0.5 * c1[0] + k * c2[0];
+  out[1] = p[1] - 0.5 * c1[1] + k * c2[1];
+  out[2] = p[2] - 0.5 * c1[2] + k * c2[2];
+  out[3] = w0; out[4] = w1; out[5] = w2;
+}
+
+// ------------------------------------------------------------------ Kernel 2: task errors
+// lane t < m: e_t = log(T_b^-1 T_t) -> sm[e + 6t]; returns ||concat e|| (unweighted, :188-200),
+// bitwise identical on all lanes.
+__device__ __forceinline__ double stage_errors(const DevModel& M, const Lay& lay, double* sm, int stage, int lane) {
+  const int m = M.n_task[stage];
+  double ss = 0;
+  if (lane < m) {
+    const int body = __ldg(M.task_body + stage * lay.maxt + lane);
+    const double* tgt = sm + lay.scaled + 7 * __ldg(M.task_src + stage * lay.maxt + lane);
+    const double* xp = sm + lay.xpos + 3 * body;
+    const double* xq = sm + lay.xquat + 4 * body;
+    double qi[4] = {xq[0], -xq[1], -xq[2], -xq[3]}, qbt[4], d[3] = {tgt[0] - xp[0], tgt[1] - xp[1], tgt[2] - xp[2]}, pbt[3], e[6];
+    qmul(qi, tgt + 3, qbt);
+    qrot(qi, d, pbt);
+    se3_log_dev(qbt, pbt, e);
+    double* eo = sm + lay.e + 6 * lane;
+#pragma unroll
+    for (int k = 0; k < 6; k++) { eo[k] = e[k]; ss += e[k] * e[k]; }
+  }
+  ss = warp_sum(ss);
+  __syncwarp();
+  return sqrt(ss);
+}
+
+// ------------------------------------------------------------------ Kernel 2: task Jacobians as stiffness
+// mink: J_t = -Jl^-1(e_t) [R^T Jp; R^T Jr]  (FrameTask.compute_jacobian) and
+//       H += (W J_t)^T (W J_t), c += (W e_t)^T (W J_t)   (Task.compute_qp_objective).
+// The geometric Jacobian column of dof k at frame t is T(r_t) S_k with r_t = x_t - O and
+// T(r) = [[I, -[r]x],[0, I]], so W J_t[:,k] = N_t S_k with the 6x6
+//       N_t = -[[wp P, wp Pr],[0, wr P]],  P = Ji R^T,  Pr = -P [r]x + B R^T,
+// where Jl^-1(e) = [[Ji, B],[0, Ji]].  Lane t stores K_t = N_t^T N_t (21 packed) and
+// g_t = N_t^T W e_t (6); the assembly then needs only S_k^T (sum K_t) S_l - no 6 x nv Jacobian.
+// Returns sum_t mu_t = sum_t ||W e_t||^2 (all lanes).
+__device__ __forceinline__ double stage_stiffness(const DevModel& M, const Lay& lay, double* sm, int stage, int lane) {
+  const int m = M.n_task[stage];
+  double mu = 0;
+  if (lane < m) {
+    const int body = __ldg(M.task_body + stage * lay.maxt + lane);
+    const double wp = __ldg(M.task_wpos + stage * lay.maxt + lane), wr = __ldg(M.task_wrot + stage * lay.maxt + lane);
+    const double a = wp * wp, b = wr * wr;
+    const double* e = sm + lay.e + 6 * lane;
+    const double ev[3] = {e[0], e[1], e[2]}, w[3] = {e[3], e[4], e[5]};
+    mu = a * (ev[0] * ev[0] + ev[1] * ev[1] + ev[2] * ev[2]) + b * (w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+    const double th2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
+    double R[9], Rt[9];
+    q2mat(sm + lay.xquat + 4 * body, R);
+    Rt[0] = R[0]; Rt[1] = R[3]; Rt[2] = R[6]; Rt[3] = R[1]; Rt[4] = R[4]; Rt[5] = R[7]; Rt[6] = R[2]; Rt[7] = R[5]; Rt[8] = R[8];
+    double P[9], Pr[9];
+    if (th2 < LIE_EPS) {            // mink SE3.ljacinv returns the identity here
+#pragma unroll
+      for (int i = 0; i < 9; i++) { P[i] = Rt[i]; Pr[i] = 0; }
+    } else {
+      const double th = sqrt(th2);
+      double s, c;
+      sincos(th, &s, &c);
+      double W[9], W2[9], Ji[9];
+      skew3(w, W);
+      mm3(W, W, W2);
+      const double A = (1.0 / th2) * (1.0 - (th * s / (2.0 * (1.0 - c))));
+#pragma unroll
+      for (int i = 0; i < 9; i++) Ji[i] = ((i % 4 == 0) ? 1.0 : 0.0) - 0.5 * W[i] + A * W2[i];
+      // Barfoot Q(v, w)
+      const double Bc = (th - s) / (th2 * th), Cc = (1.0 - 0.5 * th2 - c) / (th2 * th2),
+                   Dc = (2.0 * th - 3.0 * s + th * c) / (2.0 * th2 * th2 * th);
+      double V[9], VW[9], WV[9], WVW[9], VWW[9], t1[9], t2[9], Q[9];
+      skew3(ev, V);
+      mm3(V, W, VW);
+      mm3(W, V, WV);
+      mm3(WV, W, WVW);
+      mm3(VW, W, VWW);
+      mm3(WVW, W, t1);
+      mm3(W, WVW, t2);
+#pragma unroll
+      for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+          const int ij = 3 * i + j, ji = 3 * j + i;
+          // WWV = -(VWW)^T  ->  VWW + WWV = VWW - VWW^T
+          Q[ij] = 0.5 * V[ij] + Bc * (WV[ij] + VW[ij] + WVW[ij]) - Cc * (VWW[ij] - VWW[ji] - 3.0 * WVW[ij]) + Dc * (t1[ij] + t2[ij]);
+        }
+      double T[9], Bm[9];
+      mm3(Ji, Q, T);
+      mm3(T, Ji, Bm);               // B = -Bm
+      mm3(Ji, Rt, P);
+      mm3(Bm, Rt, Pr);
+#pragma unroll
+      for (int i = 0; i < 9; i++) Pr[i] = -Pr[i];
+    }
+    // Pr += -P [r]x
+    const int ref = M.ref_body;
+    const double* xp = sm + lay.xpos + 3 * body;
+    const double* xo = sm + lay.xpos + 3 * ref;     // world (body 0) has xpos = 0
+    const double r[3] = {xp[0] - xo[0], xp[1] - xo[1], xp[2] - xo[2]};
+    double Sr[9], PS[9];
+    skew3(r, Sr);
+    mm3(P, Sr, PS);
+#pragma unroll
+    for (int i = 0; i < 9; i++) Pr[i] -= PS[i];
+    // K = [[a P'P, a P'Pr],[., a Pr'Pr + b P'P]]
+    double PtP[9], PtPr[9], PrtPr[9];
+    mtm3(P, P, PtP);
+    mtm3(P, Pr, PtPr);
+    mtm3(Pr, Pr, PrtPr);
+    double* K = sm + lay.K + 21 * lane;
+    // packed lower 6x6: (i,j) -> i(i+1)/2 + j
+    K[0] = a * PtP[0];
+    K[1] = a * PtP[3]; K[2] = a * PtP[4];
+    K[3] = a * PtP[6]; K[4] = a * PtP[7]; K[5] = a * PtP[8];
+#pragma unroll
+    for (int i = 0; i < 3; i++) {       // rows 3..5: [ (a P'Pr)^T | a Pr'Pr + b P'P ]
+      const int base = (3 + i) * (4 + i) / 2;
+#pragma unroll
+      for (int j = 0; j < 3; j++) K[base + j] = a * PtPr[3 * j + i];
+#pragma unroll
+      for (int j = 0; j <= i; j++) K[base + 3 + j] = a * PrtPr[3 * i + j] + b * PtP[3 * i + j];
+    }
+    // g = -[a P' ev ; a Pr' ev + b P' w]
+    double* g = sm + lay.g + 6 * lane;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      g[i] = -a * (P[i] * ev[0] + P[3 + i] * ev[1] + P[6 + i] * ev[2]);
+      g[3 + i] = -(a * (Pr[i] * ev[0] + Pr[3 + i] * ev[1] + Pr[6 + i] * ev[2]) + b * (P[i] * w[0] + P[3 + i] * w[1] + P[6 + i] * w[2]));
+    }
+  }
+  mu = warp_sum(mu);
+  __syncwarp();
+  return mu;
+}
+
+// ------------------------------------------------------------------ Kernel 3: assembly (mink build_ik)
+// lane l = dof l:  Kc = sum of K_t over tasks in the subtree of dof l,  F = Kc S_l,
+// H[l][k] = S_k . F for every ancestor-or-self k of l (all other entries are structurally 0),
+// c[l] = S_l . sum g_t.  diag += damping + lm_damping * sum mu.  Also the ConfigurationLimit box.
+__device__ __forceinline__ void stage_assemble(const DevModel& M, const Lay& lay, double* sm, int stage, double mu_sum, int lane) {
+  const int n = M.nv;
+  double* H = sm + lay.H;
+  const int nH = n * (n + 1) / 2;
+  for (int i = lane; i < nH; i += 32) H[i] = 0.0;
+  __syncwarp();
+  const double diag = M.damping + M.lm_damping * mu_sum;
+  const double* q = sm + lay.q;
+  for (int l = lane; l < n; l += 32) {
+    unsigned mask = __ldg(M.dof_taskmask + stage * n + l);
+    double Kc[21], gc[6];
+#pragma unroll
+    for (int i = 0; i < 21; i++) Kc[i] = 0;
+#pragma unroll
+    for (int i = 0; i < 6; i++) gc[i] = 0;
+    while (mask) {
+      const int t = __ffs(mask) - 1;
+      mask &= mask - 1;
+      const double* K = sm + lay.K + 21 * t;
+      const double* g = sm + lay.g + 6 * t;
+#pragma unroll
+      for (int i = 0; i < 21; i++) Kc[i] += K[i];
+#pragma unroll
+      for (int i = 0; i < 6; i++) gc[i] += g[i];
+    }
+    const double* Sl = sm + lay.S + 6 * l;
+    double s[6], F[6];
+#pragma unroll
+    for (int i = 0; i < 6; i++) s[i] = Sl[i];
+#pragma unroll
+    for (int i = 0; i < 6; i++) {
+      double acc = 0;
+#pragma unroll
+      for (int j = 0; j < 6; j++) acc += Kc[i >= j ? i * (i + 1) / 2 + j : j * (j + 1) / 2 + i] * s[j];
+      F[i] = acc;
+    }
+    double cl = 0;
+#pragma unroll
+    for (int i = 0; i < 6; i++) cl += s[i] * gc[i];
+    sm[lay.c + l] = cl;
+    double* Hrow = H + l * (l + 1) / 2;
+    for (int k = l; k >= 0; k = __ldg(M.dof_parent + k)) {
+      const double* Sk = sm + lay.S + 6 * k;
+      double h = 0;
+#pragma unroll
+      for (int i = 0; i < 6; i++) h += Sk[i] * F[i];
+      Hrow[k] = h + (k == l ? diag : 0.0);
+    }
+    // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs
+    double lo = -INFINITY, hi = INFINITY;
+    if (__ldg(M.dof_limited + l)) {
+      const double qv = q[__ldg(M.dof_qadr + l)];
+      hi = M.limit_gain * (__ldg(M.dof_hi + l) - qv);
+      lo = -M.limit_gain * (qv - __ldg(M.dof_lo + l));
+    }
+    sm[lay.lo + l] = lo;
+    sm[lay.hi + l] = hi;
+  }
+  __syncwarp();
+}
+
+// ------------------------------------------------------------------ Kernel 3: exact box QP
+//   min 1/2 x'Hx + c'x   s.t. lo <= x <= hi,   H SPD (>= damping I), packed lower in sm[H].
+// Block principal pivoting (Judice-Pires) with Murty's single-pivot fallback; each pass is one
+// left-looking Cholesky of H with the rows/columns of the active set replaced by identity
+// (lane i owns rows i and i+32), two triangular solves and a KKT check.  The minimiser is unique,
+// so any exact method (daqp in the reference) returns the same x up to rounding.
+// Uses sm[L] (factor; diagonal holds 1/L_kk), sm[rhs], writes sm[x].  Returns #factorisations
+// (negative if H was not positive definite).
+#define QP_PTOL 1e-10
+#define QP_DTOL 1e-9
+
+__device__ __forceinline__ int tri(int i) { return i * (i + 1) / 2; }
+
+__device__ __forceinline__ int qp_solve(int n, const double* __restrict__ H, const double* __restrict__ c,
+                                        const double* __restrict__ lo, const double* __restrict__ hi,
+                                        double* __restrict__ L, double* __restrict__ rhs, double* __restrict__ x, int lane) {
+  const int i0 = lane, i1 = lane + 32;
+  const bool has0 = i0 < n, has1 = i1 < n;
+  const double lo0 = has0 ? lo[i0] : 0, hi0 = has0 ? hi[i0] : 0, lo1 = has1 ? lo[i1] : 0, hi1 = has1 ? hi[i1] : 0;
+  const double c0 = has0 ? c[i0] : 0, c1 = has1 ? c[i1] : 0;
+  int st0 = 0, st1 = 0;                 // 0 free, -1 at lower, +1 at upper
+  unsigned long long act = 0;           // warp-uniform active mask
+  int best = n + 1, p = 3, nfact = 0;
+  bool spd = true;
+  for (int it = 0; it < 400; it++) {
+    // ---- right-hand side: active rows carry their bound, free rows -c_F - H_FA x_A
+    double xa0 = st0 < 0 ? lo0 : (st0 > 0 ? hi0 : 0.0), xa1 = st1 < 0 ? lo1 : (st1 > 0 ? hi1 : 0.0);
+    if (act) {
+      if (has0) x[i0] = xa0;
+      if (has1) x[i1] = xa1;
+      __syncwarp();
+    }
+    double r0 = st0 ? xa0 : -c0, r1 = st1 ? xa1 : -c1;
+    for (unsigned long long mk = act; mk; mk &= mk - 1) {
+      const int j = __ffsll((long long)mk) - 1;
+      const double xj = x[j];
+      if (has0 && !st0) r0 -= H[i0 >= j ? tri(i0) + j : tri(j) + i0] * xj;
+      if (has1 && !st1) r1 -= H[i1 >= j ? tri(i1) + j : tri(j) + i1] * xj;
+    }
+    __syncwarp();
+    // ---- Cholesky, left-looking, identity on the active set
+    const double* Hr0 = H + tri(i0);
+    const double* Hr1 = H + tri(i1);
+    double* Lr0 = L + tri(i0);
+    double* Lr1 = L + tri(i1);
+    for (int k = 0; k < n; k++) {
+      const bool ak = (act >> k) & 1ull;
+      const double* Lk = L + tri(k);
+      double s0 = 0, s1 = 0;
+      if (!ak) {
+        if (has0 && i0 >= k && !st0) {
+          double a = Hr0[k], b = 0;
+          int j = 0;
+          for (; j + 1 < k; j += 2) { a -= Lr0[j] * Lk[j]; b -= Lr0[j + 1] * Lk[j + 1]; }
+          if (j < k) a -= Lr0[j] * Lk[j];
+          s0 = a + b;
+        }
+        if (has1 && i1 >= k && !st1) {
+          double a = Hr1[k], b = 0;
+          int j = 0;
+          for (; j + 1 < k; j += 2) { a -= Lr1[j] * Lk[j]; b -= Lr1[j + 1] * Lk[j + 1]; }
+          if (j < k) a -= Lr1[j] * Lk[j];
+          s1 = a + b;
+        }
+      }
+      double piv = __shfl_sync(GMR_FULL, (k < 32) ? s0 : s1, k & 31);
+      if (ak) piv = 1.0;
+      if (!(piv > 0.0)) { spd = false; piv = 1.0; }
+      const double inv = rsqrt(piv);
+      if (has0 && i0 >= k) Lr0[k] = (i0 == k) ? inv : s0 * inv;     // diagonal stores 1/L_kk
+      if (has1 && i1 >= k) Lr1[k] = (i1 == k) ? inv : s1 * inv;
+      __syncwarp();
+    }
+    nfact++;
+    // ---- forward solve L y = r (column oriented), then L' x = y (row oriented)
+    for (int k = 0; k < n; k++) {
+      const double yk = __shfl_sync(GMR_FULL, (k < 32) ? r0 : r1, k & 31) * L[tri(k) + k];
+      if (i0 == k) r0 = yk; else if (has0 && i0 > k) r0 -= Lr0[k] * yk;
+      if (i1 == k) r1 = yk; else if (has1 && i1 > k) r1 -= Lr1[k] * yk;
+    }
+    for (int k = n - 1; k >= 0; k--) {
+      const double* Lk = L + tri(k);
+      const double xk = __shfl_sync(GMR_FULL, (k < 32) ? r0 : r1, k & 31) * Lk[k];
+      if (i0 == k) r0 = xk; else if (i0 < k) r0 -= Lk[i0] * xk;
+      if (i1 == k) r1 = xk; else if (i1 < k) r1 -= Lk[i1] * xk;
+    }
+    // exact bounds on the active set (the solve reproduces them up to rounding)
+    if (st0) r0 = xa0;
+    if (st1) r1 = xa1;
+    if (has0) x[i0] = r0;
+    if (has1) x[i1] = r1;
+    __syncwarp();
+    // ---- KKT check
+    bool bad0 = false, bad1 = false;
+    if (has0 && !st0) bad0 = (r0 < lo0 - QP_PTOL) || (r0 > hi0 + QP_PTOL);
+    if (has1 && !st1) bad1 = (r1 < lo1 - QP_PTOL) || (r1 > hi1 + QP_PTOL);
+    if (act) {
+      if (has0 && st0) {
+        double g = c0;
+        for (int j = 0; j < n; j++) g += H[i0 >= j ? tri(i0) + j : tri(j) + i0] * x[j];
+        bad0 = st0 < 0 ? (g < -QP_DTOL) : (g > QP_DTOL);
+      }
+      if (has1 && st1) {
+        double g = c1;
+        for (int j = 0; j < n; j++) g += H[i1 >= j ? tri(i1) + j : tri(j) + i1] * x[j];
+        bad1 = st1 < 0 ? (g < -QP_DTOL) : (g > QP_DTOL);
+      }
+    }
+    const unsigned b0 = __ballot_sync(GMR_FULL, bad0), b1 = __ballot_sync(GMR_FULL, bad1);
+    const int nbad = __popc(b0) + __popc(b1);
+    if (nbad == 0) break;
+    bool all;
+    if (nbad < best) { best = nbad; p = 3; all = true; }
+    else if (p > 0) { p--; all = true; }
+    else all = false;
+    const int last = b1 ? 63 - __clz(b1) : 31 - __clz(b0);
+    if (bad0 && (all || i0 == last)) st0 = st0 ? 0 : (r0 < lo0 ? -1 : 1);
+    if (bad1 && (all || i1 == last)) st1 = st1 ? 0 : (r1 < lo1 ? -1 : 1);
+    act = (unsigned long long)__ballot_sync(GMR_FULL, st0 != 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 != 0) << 32);
+  }
+  __syncwarp();
+  return spd ? nfact : -nfact;
+}
+
+// ------------------------------------------------------------------ Kernel 4: integrate
+// solve_ik returns v = dq/dt and integrate_inplace applies q <- q (+) v dt (mj_integratePos);
+// the divide/multiply is kept so rounding follows the reference.
+__device__ __forceinline__ void stage_integrate(const DevModel& M, const Lay& lay, double* sm, int lane) {
+  double* q = sm + lay.q;
+  const double* x = sm + lay.x;
+  const double dt = M.timestep;
+  for (int i = lane; i < M.nv; i += 32) {
+    const int kind = __ldg(M.dof_kind + i), qa = __ldg(M.dof_qadr + i);
+    if (kind == DOF_FREE_R) {
+      if (qa >= 0) {     // first rotational dof of the free joint updates the quaternion
+        double w[3] = {x[i] / dt, x[i + 1] / dt, x[i + 2] / dt};
+        double n = sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+        double quat[4] = {q[qa], q[qa + 1], q[qa + 2], q[qa + 3]};
+        normalize4(quat);
+        if (n < 1e-15) { w[0] = 1; w[1] = w[2] = 0; n = 0; } else { w[0] /= n; w[1] /= n; w[2] /= n; }
+        const double ang = dt * n;
+        if (ang != 0.0) {
+          double sh, ch;
+          sincos(0.5 * ang, &sh, &ch);
+          double qr[4] = {ch, sh * w[0], sh * w[1], sh * w[2]}, nq[4];
+          qmul(quat, qr, nq);
+          quat[0] = nq[0]; quat[1] = nq[1]; quat[2] = nq[2]; quat[3] = nq[3];
+        }
+        q[qa] = quat[0]; q[qa + 1] = quat[1]; q[qa + 2] = quat[2]; q[qa + 3] = quat[3];
+      }
+    } else {
+      q[qa] += dt * (x[i] / dt);
+    }
+  }
+  __syncwarp();
+}
+
+}  // namespace gmr

@@ -119,6 +119,12 @@ int gmr_batch_reset(gmr_batch* b, const double* q0_dev);
  * NULL restores the model's table. */
 int gmr_batch_set_scale(gmr_batch* b, const double* scale_dev);
 int gmr_batch_get_state(gmr_batch* b, double* q_dev /* [B,nq_max] */);
+/* processing order of the work queue (device, [B], a permutation; longest clips first balances
+ * ragged batches); NULL = instance order. */
+int gmr_batch_set_order(gmr_batch* b, const int32_t* order_dev);
+/* launch geometry chosen at create time (for reporting) */
+int gmr_batch_launch_info(const gmr_batch* b, int32_t* grid, int32_t* warps_per_cta,
+                          int32_t* smem_bytes_per_cta, int32_t* smem_bytes_per_instance);
 int gmr_batch_dims(const gmr_batch* b, int32_t* B, int32_t* nq_max, int32_t* s_max,
                    int32_t* h_max, int32_t* nbody_max);
 

@@ -1,0 +1,259 @@
+"""GPU parity: every stage and the fused clip kernel, through the C ABI, against the oracle."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+PAIRS = [("bvh", "unitree_g1"), ("smplx", "unitree_g1_with_hands"), ("smplx", "galaxea_r1pro"),
+         ("bvh", "engineai_pm01"), ("smplx", "hightorque_hi"), ("smplx", "kuavo_s45"), ("smplx", "booster_k1"),
+         ("bvh", "booster_t1"), ("smplx", "stanford_toddy"), ("bvh", "fourier_n1")]
+
+QPOS_TOL = 1e-3      # rad, north_star
+ROOT_TOL = 1e-4      # m, north_star
+
+
+def _setup(src, robot, B, T, seed=3):
+    import torch  # noqa: F401
+    from gmr_b200 import model_pack, synth
+    from gmr_b200.engine import BatchedRetargeter, DeviceModel
+    m, t = model_pack.build_tables(src, robot)
+    human, heights, names = synth.synth_human_clips(m, t, src, B=B, T=T, seed=seed)
+    dm = DeviceModel.load(src, robot, names)
+    br = BatchedRetargeter(dm, B)
+    br.set_heights(heights)
+    return m, t, dm, br, human, heights
+
+
+def _random_q(m, rng, B):
+    q = np.tile(m.qpos0, (B, 1))
+    for j in range(m.njnt):
+        qa = m.jnt_qposadr[j]
+        if m.jnt_type[j] == 0:
+            q[:, qa:qa + 3] += rng.normal(size=(B, 3)) * 0.3
+            w = rng.normal(size=(B, 4))
+            q[:, qa + 3:qa + 7] = w / np.linalg.norm(w, axis=-1, keepdims=True)
+        elif m.jnt_limited[j]:
+            q[:, qa] = rng.uniform(m.jnt_range[j, 0], m.jnt_range[j, 1], size=B)
+        else:
+            q[:, qa] = rng.uniform(-1, 1, size=B)
+    return q
+
+
+@pytest.mark.parametrize("src,robot", PAIRS)
+def test_kernel1_target_prep(src, robot):
+    from gmr_b200 import synth
+    from oracle import oracle as oc
+    m, t, dm, br, human, heights = _setup(src, robot, 8, 3)
+    sc = synth.clip_scales(t, heights)
+    for ground in (False, True):
+        out = br.target_prep(human[:, 1], ground).cpu().numpy()
+        for b in range(8):
+            ref = oc.prepare(dm.desc, human[b, 1].astype(np.float64), sc[b], ground)
+            np.testing.assert_allclose(out[b, :t.n_scaled], ref, atol=1e-13)
+
+
+def test_kernel1_matches_reference_golden(golden_dir):
+    """Against vectors produced by the reference's own update_targets (tools/make_golden.py)."""
+    from gmr_b200 import model_pack, synth
+    from gmr_b200.engine import BatchedRetargeter, DeviceModel
+    for f in sorted(glob.glob(os.path.join(golden_dir, "target_prep_*.npz"))):
+        src, robot = os.path.basename(f)[len("target_prep_"):-4].split("_", 1)
+        g = np.load(f)
+        names = [str(n) for n in g["names"]]
+        dm = DeviceModel.load(src, robot, names)
+        t = dm.desc.tables
+        human = g["human"]                      # [2, T, h, 7] float64
+        B, T = human.shape[:2]
+        br = BatchedRetargeter(dm, B)
+        br.set_heights(g["heights"])
+        for ground in (0, 1):
+            for ti in range(T):
+                out = br.target_prep(human[:, ti], bool(ground)).cpu().numpy()
+                for b in range(B):
+                    np.testing.assert_allclose(out[b, :t.n_scaled], g[f"scaled_b{b}_g{ground}"][ti], atol=1e-13)
+
+
+@pytest.mark.parametrize("src,robot", PAIRS)
+def test_kernel2_fk(src, robot):
+    from oracle import oracle as oc
+    m, t, dm, br, human, heights = _setup(src, robot, 16, 1)
+    q = _random_q(m, np.random.default_rng(1), 16)
+    xpos, xquat = br.fk(q)
+    xpos, xquat = xpos.cpu().numpy(), xquat.cpu().numpy()
+    for b in range(16):
+        rp, rq = oc.fk(dm.desc, q[b])
+        np.testing.assert_allclose(xpos[b, :m.nbody], rp, atol=1e-13)
+        np.testing.assert_allclose(xquat[b, :m.nbody], rq, atol=1e-13)
+
+
+@pytest.mark.parametrize("src,robot", PAIRS)
+def test_kernel23_build_qp(src, robot):
+    from gmr_b200 import synth
+    from oracle import oracle as oc
+    B = 16
+    m, t, dm, br, human, heights = _setup(src, robot, B, 2)
+    q = _random_q(m, np.random.default_rng(2), B)
+    # moderate errors: start from qpos0-ish joint values too
+    q[B // 2:, 7 if m.jnt_type[0] == 0 else 0:] *= 0.3
+    br.reset(q)
+    scaled = br.target_prep(human[:, 0]).cpu().numpy()
+    for stage in range(2):
+        if not t.use_table[stage]:
+            continue
+        H, c, lo, hi, e = [x.cpu().numpy() for x in br.build_qp(stage, scaled)]
+        for b in range(B):
+            Hr, cr, lor, hir, er = oc.build_qp(dm.desc, q[b], stage, scaled[b, :t.n_scaled])
+            scale = np.abs(Hr).max()
+            np.testing.assert_allclose(H[b, :m.nv, :m.nv], Hr, atol=1e-11 * scale)
+            np.testing.assert_allclose(c[b, :m.nv], cr, atol=1e-11 * max(1.0, np.abs(cr).max()))
+            np.testing.assert_allclose(e[b, :len(er)], er, atol=1e-12)
+            np.testing.assert_array_equal(np.isinf(lo[b, :m.nv]), np.isinf(lor))
+            fin = np.isfinite(lor)
+            np.testing.assert_allclose(lo[b, :m.nv][fin], lor[fin], atol=1e-14)
+            np.testing.assert_allclose(hi[b, :m.nv][fin], hir[fin], atol=1e-14)
+
+
+@pytest.mark.parametrize("n", [5, 27, 35, 49, 64])
+def test_kernel3_qp_solve(n):
+    from gmr_b200.engine import qp_solve
+    from oracle import oracle as oc
+    rng = np.random.default_rng(n)
+    N = 64
+    Hs, cs, los, his = [], [], [], []
+    for i in range(N):
+        A = rng.normal(size=(n + 10, n))
+        Hs.append(A.T @ A + 0.5 * np.eye(n))
+        cs.append(rng.normal(size=n) * (5 if i % 2 else 0.5))
+        lo = -np.abs(rng.normal(size=n)) * 0.3
+        hi = np.abs(rng.normal(size=n)) * 0.3
+        free = rng.random(n) < 0.2
+        lo[free], hi[free] = -np.inf, np.inf
+        los.append(lo)
+        his.append(hi)
+    x, nf = qp_solve(np.array(Hs), np.array(cs), np.array(los), np.array(his))
+    x, nf = x.cpu().numpy(), nf.cpu().numpy()
+    assert (nf > 0).all()
+    for i in range(N):
+        xr, nfr = oc.box_qp(Hs[i], cs[i], los[i], his[i])
+        np.testing.assert_allclose(x[i], xr, atol=1e-10)
+        assert nf[i] == nfr
+
+
+def _check_clip(qpos, ref, m, tag=""):
+    d = np.abs(qpos - ref)
+    free = m.jnt_type[0] == 0
+    if free:
+        assert d[..., :3].max() < ROOT_TOL, f"{tag} root pos err {d[..., :3].max()}"
+        # quaternion sign-insensitive
+        qa, qb = qpos[..., 3:7], ref[..., 3:7]
+        dq = np.minimum(np.abs(qa - qb).max(-1), np.abs(qa + qb).max(-1))
+        assert dq.max() < QPOS_TOL, f"{tag} root quat err {dq.max()}"
+        assert d[..., 7:].max() < QPOS_TOL, f"{tag} joint err {d[..., 7:].max()}"
+    else:
+        assert d.max() < QPOS_TOL, f"{tag} qpos err {d.max()}"
+    return d.max()
+
+
+@pytest.mark.parametrize("src,robot", PAIRS)
+def test_fused_clip_matches_oracle(src, robot):
+    from gmr_b200 import synth
+    from oracle import oracle as oc
+    B, T = 48, 40
+    m, t, dm, br, human, heights = _setup(src, robot, B, T)
+    qpos, diag = br.run(human, diag=True)
+    qpos = qpos.cpu().numpy()
+    ref = oc.run_clips(dm.desc, human, scale=synth.clip_scales(t, heights), nthreads=8)
+    worst = _check_clip(qpos[..., :m.nq], ref["qpos"], m, f"{src}->{robot}")
+    assert worst < 1e-7, f"float64 path should agree far below tolerance, got {worst}"
+    np.testing.assert_array_equal(diag["iters"].cpu().numpy(), ref["iters"])
+    np.testing.assert_allclose(diag["err"].cpu().numpy(), ref["err"], atol=1e-8)
+    assert (diag["nfact"].cpu().numpy() > 0).all()
+    # task-space residual no worse than the reference (north_star)
+    assert (diag["err"].cpu().numpy() <= ref["err"] + 1e-8).all()
+
+
+def test_step_equals_run_and_state_persists():
+    B, T = 16, 12
+    m, t, dm, br, human, heights = _setup("bvh", "unitree_g1", B, T)
+    full = br.run(human).cpu().numpy()
+    br.reset()
+    a = br.run(human[:, :5]).cpu().numpy()
+    b = br.run(human[:, 5:]).cpu().numpy()
+    np.testing.assert_array_equal(np.concatenate([a, b], 1), full)
+    br.reset()
+    steps = np.stack([br.step(human[:, i]).cpu().numpy() for i in range(T)], 1)
+    np.testing.assert_array_equal(steps, full)
+    np.testing.assert_array_equal(br.state().cpu().numpy(), full[:, -1])
+
+
+def test_ragged_lengths_and_order():
+    from gmr_b200 import synth
+    from oracle import oracle as oc
+    B, T = 24, 20
+    m, t, dm, br, human, heights = _setup("smplx", "unitree_g1", B, T)
+    T_of = np.random.default_rng(0).integers(1, T + 1, size=B).astype(np.int32)
+    br.set_order(np.argsort(-T_of).astype(np.int32))
+    qpos = br.run(human, T_of=T_of).cpu().numpy()
+    ref = oc.run_clips(dm.desc, human, T_of=T_of, scale=synth.clip_scales(t, heights), nthreads=8)
+    for b in range(B):
+        _check_clip(qpos[b, :T_of[b], :m.nq], ref["qpos"][b, :T_of[b]], m)
+        assert (qpos[b, T_of[b]:] == 0).all()
+
+
+def test_offset_to_ground_and_f64_stream():
+    from gmr_b200 import synth
+    from oracle import oracle as oc
+    B, T = 8, 10
+    m, t, dm, br, human, heights = _setup("smplx", "booster_t1", B, T)
+    h64 = human.astype(np.float64) + 1e-9
+    qpos = br.run(h64, offset_to_ground=True).cpu().numpy()
+    ref = oc.run_clips(dm.desc, h64, scale=synth.clip_scales(t, heights), offset_to_ground=True, nthreads=8)
+    assert _check_clip(qpos[..., :m.nq], ref["qpos"], m) < 1e-7
+
+
+def test_heterogeneous_launch():
+    """config 4: one launch, instance = (clip, robot)."""
+    from gmr_b200 import model_pack, synth
+    from gmr_b200.engine import BatchedRetargeter, DeviceModel
+    from oracle import oracle as oc
+    robots = ["unitree_g1", "unitree_g1_with_hands", "galaxea_r1pro", "kuavo_s45", "booster_k1"]
+    per, T = 6, 15
+    models, humans, refs, model_of, heights_all = [], [], [], [], []
+    for i, r in enumerate(robots):
+        m, t = model_pack.build_tables("smplx", r)
+        human, heights, names = synth.synth_human_clips(m, t, "smplx", B=per, T=T, seed=10 + i)
+        dm = DeviceModel.load("smplx", r, names)
+        models.append(dm)
+        humans.append(human)
+        heights_all += list(heights)
+        model_of += [i] * per
+        refs.append(oc.run_clips(dm.desc, human, scale=synth.clip_scales(t, heights), nthreads=8)["qpos"])
+    br = BatchedRetargeter(models, per * len(robots), model_of_instance=model_of)
+    br.set_heights(heights_all)
+    qpos = br.run(np.concatenate(humans, 0)).cpu().numpy()
+    for i, r in enumerate(robots):
+        m = models[i].desc.model
+        _check_clip(qpos[i * per:(i + 1) * per, :, :m.nq], refs[i], m, r)
+
+
+def test_fk_tail_matches_reference_golden(golden_dir):
+    import torch
+    from gmr_b200 import model_pack
+    from gmr_b200.engine import DeviceModel
+    for f in sorted(glob.glob(os.path.join(golden_dir, "fk_*.npz"))):
+        robot = os.path.basename(f)[3:-4]
+        g = np.load(f)
+        dm = DeviceModel.load("smplx", robot)
+        dev = torch.device("cuda", 0)
+        bp, br = dm.fk_bodies_f32(torch.from_numpy(g["root_pos"]).to(dev), torch.from_numpy(g["root_rot_xyzw"]).to(dev),
+                                  torch.from_numpy(g["dof_pos"]).to(dev))
+        np.testing.assert_allclose(bp.cpu().numpy(), g["body_pos"], atol=2e-6)
+        np.testing.assert_allclose(br.cpu().numpy(), g["body_rot_xyzw"], atol=2e-6)
+        n = g["dof_pos"].shape[0]
+        ident = torch.zeros((n, 4), device=dev)
+        ident[:, 3] = 1
+        lbp, _ = dm.fk_bodies_f32(torch.zeros((n, 3), device=dev), ident, torch.from_numpy(g["dof_pos"]).to(dev), want_rot=False)
+        np.testing.assert_allclose(lbp.cpu().numpy(), g["local_body_pos"], atol=2e-6)
