@@ -513,3 +513,50 @@ extern "C" int gmr_fk_bodies_f32(gmr_model* m, void* stream, int N, const float*
   if (e != cudaSuccess) return fail(-100, cudaGetErrorString(e));
   return 0;
 }
+
+// ---------------------------------------------------------------- roofline probe
+// Peak of the CUDA-core FMA pipe the kernels run on (MEASURED_PEAKS.json holds only HBM and the
+// bf16 tensor peak): 8 independent FMA chains per thread, every SM saturated.
+namespace {
+template <typename T>
+__global__ void fma_probe_kernel(T* sink, int iters, T a, T b) {
+  T x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  for (int i = 0; i < iters; i++) {
+    x0 = x0 * a + b; x1 = x1 * a + b; x2 = x2 * a + b; x3 = x3 * a + b;
+    x4 = x4 * a + b; x5 = x5 * a + b; x6 = x6 * a + b; x7 = x7 * a + b;
+  }
+  T r = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+  if (r == (T)123456789) sink[0] = r;     // never true; keeps the chains alive
+}
+template <typename T>
+int fma_probe(int device, double* tflops_out) {
+  DevGuard g(device);
+  int sms = 0;
+  CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+  T* sink = nullptr;
+  CU(cudaMalloc(&sink, sizeof(T)));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0));
+  CU(cudaEventCreate(&e1));
+  const int blocks = sms * 8, threads = 256, iters = 1 << 15;
+  double best = 0;
+  for (int rep = 0; rep < 4; rep++) {
+    CU(cudaEventRecord(e0, 0));
+    fma_probe_kernel<T><<<blocks, threads>>>(sink, iters, (T)0.999999, (T)1e-6);
+    CU(cudaEventRecord(e1, 0));
+    CU(cudaEventSynchronize(e1));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    const double flops = 2.0 * 8.0 * (double)iters * blocks * threads;
+    if (rep > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+  *tflops_out = best;
+  return 0;
+}
+}  // namespace
+
+extern "C" int gmr_probe_fma_peak(int device, int fp64, double* tflops_out) {
+  if (!tflops_out) return fail(-1, "null argument");
+  return fp64 ? fma_probe<double>(device, tflops_out) : fma_probe<float>(device, tflops_out);
+}

@@ -181,6 +181,30 @@ class BatchedRetargeter:
                                             C.byref(d) if d is not None else None), "gmr_batch_run")
         return (qpos, dout) if diag else qpos
 
+    def retarget_clips_host(self, human_host, qpos_host=None, T_of=None, offset_to_ground=False):
+        """Whole clips from HOST buffers to a HOST result: the call the dataset drivers make
+        (scripts/bvh_to_robot_dataset.py:84-113: new retargeter per clip -> per-frame retarget ->
+        stacked qpos).  human_host [B,T,h,7] float32/float64 torch CPU tensor (pinned for full copy
+        speed); returns qpos [B,T,nq_max] float64 on the host (pinned, reused between calls when
+        qpos_host is given).  Cold start per clip like the reference; asynchronous on the batch's
+        stream - synchronise the stream (or call .cpu-side sync) before reading the result."""
+        human_host = torch.as_tensor(human_host)
+        if human_host.is_cuda:
+            raise ValueError("retarget_clips_host takes host buffers; use run() for device tensors")
+        T = human_host.shape[1]
+        key = (tuple(human_host.shape), human_host.dtype)
+        if getattr(self, "_stage_key", None) != key:
+            self._stage_in = torch.empty(human_host.shape, dtype=human_host.dtype, device=self.tdev)
+            self._stage_out = torch.empty((self.B, T, self.nq_max), dtype=torch.float64, device=self.tdev)
+            self._stage_key = key
+        if qpos_host is None:
+            qpos_host = torch.empty((self.B, T, self.nq_max), dtype=torch.float64, pin_memory=True)
+        self._stage_in.copy_(human_host, non_blocking=True)
+        self.reset()
+        self.run(self._stage_in, T_of=T_of, offset_to_ground=offset_to_ground, out=self._stage_out)
+        qpos_host.copy_(self._stage_out, non_blocking=True)
+        return qpos_host
+
     def step(self, human, offset_to_ground=False, diag=False, want_scaled=False):
         """One retarget() call for every instance: human [B,h,7] -> qpos [B,nq_max]."""
         h, dt = self._human(human, 3)
@@ -235,3 +259,10 @@ def qp_solve(H, c, lo, hi, device: int = 0):
     _lib.check(_lib.lib().gmr_qp_solve(device, C.c_void_p(st), N, n, _ptr(H), _ptr(c), _ptr(lo), _ptr(hi), _ptr(x), _ptr(nf)),
                "gmr_qp_solve")
     return x, nf
+
+
+def probe_fma_peak(device: int = 0, fp64: bool = True) -> float:
+    """Measured CUDA-core FMA peak in TFLOP/s (compute roofline denominator)."""
+    out = C.c_double(0.0)
+    _lib.check(_lib.lib().gmr_probe_fma_peak(int(device), int(bool(fp64)), C.byref(out)), "gmr_probe_fma_peak")
+    return out.value

@@ -167,8 +167,12 @@ def synth_robot_motion(model: RobotModel, B: int, T: int, rng, fps: float = 30.0
 
 
 def synth_human_clips(model: RobotModel, tables: RetargetTables, src_human: str, B: int, T: int,
-                      seed: int = 0xB200, fps: float = 30.0, dtype=np.float32, chunk: int = 256):
-    """-> (human [B,T,h,7] dtype, heights [B] float64, human_names list)."""
+                      seed: int = 0xB200, fps: float = 30.0, dtype=np.float32, chunk: int = 256,
+                      workers: int = 1, out=None):
+    """-> (human [B,T,h,7] dtype, heights [B] float64, human_names list).
+    Chunks of `chunk` clips are seeded independently ([seed, first clip]), so the result does not
+    depend on `workers` (processes used to generate chunks in parallel).  `out` may be a
+    preallocated [B,T,h,7] array (e.g. the numpy view of a pinned torch tensor)."""
     names = human_body_names(src_human, tables)
     h = len(names)
     s = tables.n_scaled
@@ -185,10 +189,30 @@ def synth_human_clips(model: RobotModel, tables: RetargetTables, src_human: str,
                 break
         if not found:
             raise KeyError(tables.scaled_names[i])
-    out = np.zeros((B, T, h, 7), dtype)
+    if out is None:
+        out = np.zeros((B, T, h, 7), dtype)
+    assert out.shape == (B, T, h, 7)
     heights = np.zeros(B)
-    for c0 in range(0, B, chunk):
-        c1 = min(B, c0 + chunk)
+    jobs = [(model, tables, body_of, idx, h, seed, c0, min(B, c0 + chunk), T, fps, np.dtype(dtype)) for c0 in range(0, B, chunk)]
+    if workers > 1 and len(jobs) > 1:
+        import multiprocessing as mp
+        with mp.get_context("fork").Pool(min(workers, len(jobs))) as pool:
+            for c0, c1, arr, hts in pool.imap_unordered(_synth_chunk, jobs):
+                out[c0:c1] = arr
+                heights[c0:c1] = hts
+    else:
+        for job in jobs:
+            c0, c1, arr, hts = _synth_chunk(job)
+            out[c0:c1] = arr
+            heights[c0:c1] = hts
+    return out, heights, list(names)
+
+
+def _synth_chunk(job):
+    """One independently seeded chunk of clips -> (c0, c1, human [nb,T,h,7], heights [nb])."""
+    model, tables, body_of, idx, h, seed, c0, c1, T, fps, dtype = job
+    s = tables.n_scaled
+    if True:
         nb = c1 - c0
         rng = np.random.default_rng([seed, c0])
         q = synth_robot_motion(model, nb, T, rng, fps)
@@ -227,10 +251,10 @@ def synth_human_clips(model: RobotModel, tables: RetargetTables, src_human: str,
         dots = np.sum(full_q[:, 1:] * full_q[:, :-1], axis=-1)
         flip = np.cumprod(np.where(dots < 0, -1.0, 1.0), axis=1)
         full_q[:, 1:] *= flip[..., None]
-        out[c0:c1, :, :, :3] = full_p
-        out[c0:c1, :, :, 3:] = full_q
-        heights[c0:c1] = hts
-    return out, heights, list(names)
+        arr = np.empty((nb, T, h, 7), dtype)
+        arr[..., :3] = full_p
+        arr[..., 3:] = full_q
+    return c0, c1, arr, hts
 
 
 def clip_scales(tables: RetargetTables, heights: np.ndarray) -> np.ndarray:

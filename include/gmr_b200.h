@@ -165,6 +165,11 @@ int gmr_fk_bodies_f32(gmr_model* m, void* stream, int N, const float* root_pos_d
                       const float* root_rot_xyzw_dev, const float* dof_pos_dev,
                       float* body_pos_out_dev, float* body_rot_out_dev);
 
+/* Measurement helper (no reference counterpart): measured peak of the CUDA-core FMA pipe in
+ * TFLOP/s (fp64 != 0: DFMA, else FFMA) - the compute roofline denominator of bench.py.
+ * Synchronous, default stream. */
+int gmr_probe_fma_peak(int device, int fp64, double* tflops_out);
+
 #ifdef __cplusplus
 }
 #endif
