@@ -248,7 +248,7 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m) {
   int o = 0;
   auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };   // keep 16-byte alignment
   L.q = take(nq); L.scaled = take(7 * s); L.c = take(nv); L.x = take(nv); L.lo = take(nv); L.hi = take(nv);
-  L.rhs = take(nv); L.H = take(nv * (nv + 1) / 2);
+  L.H = take(nv * (nv + 1) / 2);
   const int region = o;
   L.xpos = take(3 * nbody); L.xquat = take(4 * nbody); L.S = take(6 * nv); L.e = take(6 * m);
   L.K = take(21 * m); L.g = take(6 * m);
@@ -293,14 +293,16 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   if (e == cudaSuccess) e = cudaMemcpy(b->d_models, hm.data(), sizeof(DevModel) * n_models, cudaMemcpyHostToDevice);
   if (e == cudaSuccess && model_of_instance)
     e = cudaMemcpy(b->d_model_of, model_of_instance, sizeof(int) * (size_t)B, cudaMemcpyHostToDevice);
-  // launch geometry: as many resident warps as shared memory allows, one instance per warp
+  // launch geometry: one instance per warp, as many warps per SM as shared memory and registers allow
   const size_t per_warp = sizeof(double) * (size_t)b->lay.total;
   int dev_smem = 0, sms = 0;
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, b->device);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device);
   if (e == cudaSuccess) {
-    b->warps_per_cta = 4;
-    while (b->warps_per_cta > 1 && per_warp * b->warps_per_cta > (size_t)dev_smem) b->warps_per_cta >>= 1;
+    // one CTA per SM, all its warps in lockstep through the tick loop (shared instruction stream);
+    // 12 warps = 384 threads keeps the 168-register kernel at one CTA of 64K registers
+    b->warps_per_cta = (int)std::min<size_t>({(size_t)12, (size_t)dev_smem / per_warp, (size_t)B});
+    if (b->warps_per_cta < 1) b->warps_per_cta = 1;
     b->smem_bytes = per_warp * b->warps_per_cta;
     if (b->smem_bytes > (size_t)dev_smem) e = cudaErrorInvalidConfiguration;
   }
@@ -493,7 +495,7 @@ extern "C" int gmr_qp_solve(int device, void* stream, int n_qp, int n, const dou
   if (!H_dev || !c_dev || !lo_dev || !hi_dev || !x_out_dev) return fail(-1, "null argument");
   DevGuard g(device);
   const int w = 4;
-  const size_t smem = sizeof(double) * (size_t)w * (n * (n + 1) + 5 * n);
+  const size_t smem = sizeof(double) * (size_t)w * (n * (n + 1) + 4 * n);
   CU(cudaFuncSetAttribute(qp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   qp_kernel<<<(n_qp + w - 1) / w, 32 * w, smem, (cudaStream_t)stream>>>(n_qp, n, H_dev, c_dev, lo_dev, hi_dev, x_out_dev, nfact_out_dev);
   CU(cudaGetLastError());

@@ -34,75 +34,143 @@ struct RunArgs {
   Lay lay;
 };
 
-// One solve_ik + integrate_inplace (+ the error evaluation that follows it in the reference loop).
-__device__ __forceinline__ double ik_iteration(const DevModel& M, const Lay& lay, double* sm, int stage, int lane, int& nfact) {
-  const double mu = stage_stiffness(M, lay, sm, stage, lane);
-  stage_assemble(M, lay, sm, stage, mu, lane);
-  const int nf = qp_solve(M.nv, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.rhs, sm + lay.x, lane);
-  nfact = (nf < 0 || nfact < 0) ? -abs(nfact) - abs(nf) : nfact + nf;
-  stage_integrate(M, lay, sm, lane);
-  stage_fk(M, lay, sm, lane);
-  return stage_errors(M, lay, sm, stage, lane);
+// Per-warp control state of the tick loop (all fields warp-uniform, kept in registers).
+struct Slot {
+  int inst;                      // instance being retargeted, -1 = none
+  int t, T;                      // current frame, clip length
+  int stage, it;                 // stage being solved, loop counter of motion_retarget.py:152/171
+  int nfact;                     // factorisations in this frame (negative once H was not SPD)
+  double curr;                   // curr_error of the reference loop
+  unsigned long long act_lo, act_hi;   // active set of the previous solve of this frame/stage
+};
+
+__device__ __forceinline__ int next_stage(const DevModel& M, int stage) {
+  stage++;
+  while (stage < 2 && !M.use[stage]) stage++;
+  return stage;
+}
+
+// Kernel 4 (control): what the reference does between two solve_ik calls, as a state machine.
+// Called once per tick by every warp that holds an instance, right after FK + error evaluation.
+// A "tick" is one solve_ik + integrate_inplace; the stage loop, the frame loop and the clip queue
+// advance here, so every warp of the CTA executes the same solver code in every tick whatever
+// frame, stage or iteration its own instance is in.
+template <typename TIn>
+__device__ __noinline__ void begin_frame(const RunArgs& a, const DevModel& M, const Lay& lay, double* sm, Slot& s, int lane) {
+  // frames without an enabled stage pass straight through (use_ik_match_table1/2 both false)
+  for (;;) {
+    const TIn* human = (const TIn*)a.human + (size_t)s.inst * a.human_inst_stride + (size_t)s.t * a.human_frame_stride;
+    stage_prep<TIn>(M, lay, sm, human, a.scale + (size_t)s.inst * a.s_max, a.to_ground != 0, lane);
+    const size_t o = (size_t)s.inst * a.T_max + s.t;
+    if (a.scaled_out) {
+      double* so = a.scaled_out + o * a.s_max * 7;
+      for (int i = lane; i < M.n_scaled * 7; i += 32) so[i] = sm[lay.scaled + i];
+    }
+    s.stage = next_stage(M, -1);
+    s.it = 0; s.nfact = 0; s.act_lo = s.act_hi = 0;
+    if (s.stage < 2) { s.curr = stage_errors(M, lay, sm, s.stage, lane); return; }
+    if (lane == 0) {
+      if (a.err_out) { a.err_out[2 * o] = 0; a.err_out[2 * o + 1] = 0; }
+      if (a.iters_out) { a.iters_out[2 * o] = 0; a.iters_out[2 * o + 1] = 0; }
+      if (a.nfact_out) a.nfact_out[o] = 0;
+    }
+    if (a.qpos_out) for (int i = lane; i < M.nq; i += 32) a.qpos_out[o * a.nq_max + i] = sm[lay.q + i];
+    if (++s.t >= s.T) { s.inst = -1; return; }
+  }
 }
 
 template <typename TIn>
-__global__ void __launch_bounds__(128) clip_kernel(const RunArgs a) {
+__global__ void __launch_bounds__(384, 1) clip_kernel(const RunArgs a) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const Lay lay = a.lay;
   double* sm = smem + (size_t)warp * lay.total;
+  Slot s;
+  s.inst = -1; s.t = s.T = 0; s.stage = 2; s.it = 0; s.nfact = 0; s.curr = 0; s.act_lo = s.act_hi = 0;
+  bool drained = false;
+  const DevModel* Mp = a.models;
   for (;;) {
-    int slot = 0;
-    if (lane == 0) slot = atomicAdd(a.counter, 1);
-    slot = __shfl_sync(GMR_FULL, slot, 0);
-    if (slot >= a.B) break;
-    const int inst = a.order ? a.order[slot] : slot;
-    const DevModel& M = a.models[a.model_of ? a.model_of[inst] : 0];
-    const int T = a.T_of ? min(a.T_of[inst], a.T_max) : a.T_max;
-    double* qs = a.q_state + (size_t)inst * a.nq_max;
-    for (int i = lane; i < M.nq; i += 32) sm[lay.q + i] = qs[i];
-    __syncwarp();
-    stage_fk(M, lay, sm, lane);
-    const double* scale = a.scale + (size_t)inst * a.s_max;
-    const TIn* human = (const TIn*)a.human + (size_t)inst * a.human_inst_stride;
-    for (int t = 0; t < T; t++) {
-      stage_prep<TIn>(M, lay, sm, human + (size_t)t * a.human_frame_stride, scale, a.to_ground != 0, lane);
-      const size_t o = (size_t)inst * a.T_max + t;
-      if (a.scaled_out) {
-        double* so = a.scaled_out + o * a.s_max * 7;
-        for (int i = lane; i < M.n_scaled * 7; i += 32) so[i] = sm[lay.scaled + i];
-      }
-      int nfact = 0;
-#pragma unroll 1
-      for (int stage = 0; stage < 2; stage++) {
-        double err = 0;
-        int solves = 0;
-        if (M.use[stage]) {
-          // motion_retarget.py:143-161 / :163-182
-          double curr = stage_errors(M, lay, sm, stage, lane);
-          double next = ik_iteration(M, lay, sm, stage, lane, nfact);
-          int it = 0;
-          while (curr - next > M.converge_eps && it < M.max_iter) {
-            curr = next;
-            next = ik_iteration(M, lay, sm, stage, lane, nfact);
-            it++;
-          }
-          err = next;
-          solves = it + 1;
-        }
-        if (lane == 0) {
-          if (a.err_out) a.err_out[2 * o + stage] = err;
-          if (a.iters_out) a.iters_out[2 * o + stage] = solves;
-        }
-      }
-      if (lane == 0 && a.nfact_out) a.nfact_out[o] = nfact;
-      if (a.qpos_out) {
-        double* qo = a.qpos_out + o * a.nq_max;
-        for (int i = lane; i < M.nq; i += 32) qo[i] = sm[lay.q + i];
+    // ---- phase 0: warps without an instance pull the next clip from the queue
+    while (s.inst < 0 && !drained) {
+      int slot = 0;
+      if (lane == 0) slot = atomicAdd(a.counter, 1);
+      slot = __shfl_sync(GMR_FULL, slot, 0);
+      if (slot >= a.B) { drained = true; break; }
+      s.inst = a.order ? a.order[slot] : slot;
+      Mp = a.models + (a.model_of ? a.model_of[s.inst] : 0);
+      s.T = a.T_of ? min(a.T_of[s.inst], a.T_max) : a.T_max;
+      s.t = 0;
+      if (s.T <= 0) { s.inst = -1; continue; }
+      const double* qs = a.q_state + (size_t)s.inst * a.nq_max;
+      for (int i = lane; i < Mp->nq; i += 32) sm[lay.q + i] = qs[i];
+      __syncwarp();
+      stage_fk(*Mp, lay, sm, lane);
+      const int inst = s.inst;
+      begin_frame<TIn>(a, *Mp, lay, sm, s, lane);
+      if (s.inst < 0) {            // clip had no enabled stage: state unchanged
+        (void)inst;
       }
     }
-    for (int i = lane; i < M.nq; i += 32) qs[i] = sm[lay.q + i];
-    __syncwarp();
+    if (!__syncthreads_or(s.inst >= 0)) break;
+    const DevModel& M = *Mp;
+    const bool on = s.inst >= 0;
+    // ---- phase 1: task stiffness + QP assembly (mink build_ik)
+    if (on) {
+      const double mu = stage_stiffness(M, lay, sm, s.stage, lane);
+      stage_assemble(M, lay, sm, s.stage, mu, lane);
+    }
+    __syncthreads();
+    // ---- phase 2: box QP
+    if (on) {
+      const int nf = qp_solve(M.nv, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.x, lane, s.act_lo, s.act_hi);
+      s.nfact = (nf < 0 || s.nfact < 0) ? -abs(s.nfact) - abs(nf) : s.nfact + nf;
+    }
+    __syncthreads();
+    // ---- phase 3: integrate, FK, error, and the control decisions of motion_retarget.py:143-185
+    if (on) {
+      stage_integrate(M, lay, sm, lane);
+      stage_fk(M, lay, sm, lane);
+      const double next = stage_errors(M, lay, sm, s.stage, lane);
+      if (s.curr - next > M.converge_eps && s.it < M.max_iter) {
+        s.curr = next;
+        s.it++;
+      } else {
+        const size_t o = (size_t)s.inst * a.T_max + s.t;
+        if (lane == 0) {
+          if (a.err_out) a.err_out[2 * o + s.stage] = next;
+          if (a.iters_out) a.iters_out[2 * o + s.stage] = s.it + 1;
+        }
+        const int prev = s.stage;
+        s.stage = next_stage(M, s.stage);
+        s.it = 0; s.act_lo = s.act_hi = 0;
+        if (s.stage < 2) {
+          s.curr = stage_errors(M, lay, sm, s.stage, lane);
+        } else {
+          if (lane == 0) {
+            for (int k = 0; k < 2; k++)
+              if (!M.use[k]) {
+                if (a.err_out) a.err_out[2 * o + k] = 0;
+                if (a.iters_out) a.iters_out[2 * o + k] = 0;
+              }
+            if (a.nfact_out) a.nfact_out[o] = s.nfact;
+          }
+          (void)prev;
+          if (a.qpos_out) {
+            double* qo = a.qpos_out + o * a.nq_max;
+            for (int i = lane; i < M.nq; i += 32) qo[i] = sm[lay.q + i];
+          }
+          if (++s.t < s.T) {
+            begin_frame<TIn>(a, M, lay, sm, s, lane);
+          } else {
+            double* qs = a.q_state + (size_t)s.inst * a.nq_max;
+            for (int i = lane; i < M.nq; i += 32) qs[i] = sm[lay.q + i];
+            __syncwarp();
+            s.inst = -1;
+          }
+        }
+      }
+    }
+    // (phase 0 of the next tick follows; its barrier closes this phase)
   }
 }
 
@@ -170,7 +238,7 @@ __global__ void build_qp_kernel(const StageArgs a) {
   double* Ho = a.H_out + (size_t)inst * a.nv_max * a.nv_max;
   for (int idx = lane; idx < n * n; idx += 32) {
     const int i = idx / n, j = idx % n;
-    Ho[i * a.nv_max + j] = sm[lay.H + (i >= j ? tri(i) + j : tri(j) + i)];
+    Ho[i * a.nv_max + j] = sym_at(sm + lay.H, n, i, j);
   }
   for (int i = lane; i < n; i += 32) {
     a.c_out[(size_t)inst * a.nv_max + i] = sm[lay.c + i];
@@ -187,16 +255,17 @@ __global__ void qp_kernel(int n_qp, int n, const double* H, const double* c, con
   const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
   if (inst >= n_qp) return;
   const int nH = n * (n + 1) / 2;
-  double* sm = smem + (size_t)warp * (2 * nH + 5 * n);
-  double *sH = sm, *sL = sm + nH, *sc = sL + nH, *slo = sc + n, *shi = slo + n, *srhs = shi + n, *sx = srhs + n;
+  double* sm = smem + (size_t)warp * (2 * nH + 4 * n);
+  double *sH = sm, *sL = sm + nH, *sc = sL + nH, *slo = sc + n, *shi = slo + n, *sx = shi + n;
   const double* Hi = H + (size_t)inst * n * n;
   for (int idx = lane; idx < n * n; idx += 32) {
     const int i = idx / n, j = idx % n;
-    if (j <= i) sH[tri(i) + j] = Hi[idx];
+    if (j <= i) sH[colbase(n, j) + i] = Hi[idx];
   }
   for (int i = lane; i < n; i += 32) { sc[i] = c[(size_t)inst * n + i]; slo[i] = lo[(size_t)inst * n + i]; shi[i] = hi[(size_t)inst * n + i]; }
   __syncwarp();
-  const int nf = qp_solve(n, sH, sc, slo, shi, sL, srhs, sx, lane);
+  unsigned long long act_lo = 0, act_hi = 0;      // cold start: the oracle's pivoting sequence
+  const int nf = qp_solve(n, sH, sc, slo, shi, sL, sx, lane, act_lo, act_hi);
   for (int i = lane; i < n; i += 32) x_out[(size_t)inst * n + i] = sx[i];
   if (lane == 0 && nfact_out) nfact_out[inst] = nf;
 }

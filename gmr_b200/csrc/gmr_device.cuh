@@ -61,12 +61,16 @@ struct DevModel {
 
 // Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
 struct Lay {
-  int q, scaled, c, x, lo, hi, rhs, H;    // persistent across the QP solve
+  int q, scaled, c, x, lo, hi, H;         // persistent across the QP solve
   int xpos, xquat, S, e, K, g;            // kinematics / assembly scratch ...
   int L;                                  // ... overlaid by the Cholesky factor during the solve
   int total;                              // doubles per warp
   int maxt;                               // stride of the stage-major task tables
 };
+
+// packed lower triangle, COLUMN-major: element (i,j), i >= j, lives at colbase(n,j) + i
+__device__ __forceinline__ int colbase(int n, int j) { return j * n - ((j * (j + 1)) >> 1); }
+__device__ __forceinline__ int tri(int i) { return i * (i + 1) / 2; }
 
 // ---------------------------------------------------------------- quaternion / vector helpers (wxyz)
 __device__ __forceinline__ void qmul(const double* a, const double* b, double* o) {

@@ -70,7 +70,7 @@ __device__ __forceinline__ void stage_prep(const DevModel& M, const Lay& lay, do
 // sequence.  Also writes the spatial axis S[dof] = (v_O, w): twist of the dof expressed at the
 // reference point O = origin of the floating base (world origin if there is none), so that the
 // geometric Jacobian column of ANY descendant frame at x is [v_O + w x (x - O); w].
-__device__ __forceinline__ void stage_fk(const DevModel& M, const Lay& lay, double* sm, int lane) {
+__device__ __noinline__ void stage_fk(const DevModel& M, const Lay& lay, double* sm, int lane) {
   const double* q = sm + lay.q;
   double* xpos = sm + lay.xpos;
   double* xquat = sm + lay.xquat;
@@ -168,7 +168,7 @@ __device__ __forceinline__ void se3_log_dev(const double* q, const double* p, do
 // ------------------------------------------------------------------ Kernel 2: task errors
 // lane t < m: e_t = log(T_b^-1 T_t) -> sm[e + 6t]; returns ||concat e|| (unweighted, :188-200),
 // bitwise identical on all lanes.
-__device__ __forceinline__ double stage_errors(const DevModel& M, const Lay& lay, double* sm, int stage, int lane) {
+__device__ __noinline__ double stage_errors(const DevModel& M, const Lay& lay, double* sm, int stage, int lane) {
   const int m = M.n_task[stage];
   double ss = 0;
   if (lane < m) {
@@ -198,7 +198,7 @@ __device__ __forceinline__ double stage_errors(const DevModel& M, const Lay& lay
 // where Jl^-1(e) = [[Ji, B],[0, Ji]].  Lane t stores K_t = N_t^T N_t (21 packed) and
 // g_t = N_t^T W e_t (6); the assembly then needs only S_k^T (sum K_t) S_l - no 6 x nv Jacobian.
 // Returns sum_t mu_t = sum_t ||W e_t||^2 (all lanes).
-__device__ __forceinline__ double stage_stiffness(const DevModel& M, const Lay& lay, double* sm, int stage, int lane) {
+__device__ __noinline__ double stage_stiffness(const DevModel& M, const Lay& lay, double* sm, int stage, int lane) {
   const int m = M.n_task[stage];
   double mu = 0;
   if (lane < m) {
@@ -298,7 +298,7 @@ __device__ __forceinline__ double stage_stiffness(const DevModel& M, const Lay& 
 // lane l = dof l:  Kc = sum of K_t over tasks in the subtree of dof l,  F = Kc S_l,
 // H[l][k] = S_k . F for every ancestor-or-self k of l (all other entries are structurally 0),
 // c[l] = S_l . sum g_t.  diag += damping + lm_damping * sum mu.  Also the ConfigurationLimit box.
-__device__ __forceinline__ void stage_assemble(const DevModel& M, const Lay& lay, double* sm, int stage, double mu_sum, int lane) {
+__device__ __noinline__ void stage_assemble(const DevModel& M, const Lay& lay, double* sm, int stage, double mu_sum, int lane) {
   const int n = M.nv;
   double* H = sm + lay.H;
   const int nH = n * (n + 1) / 2;
@@ -338,13 +338,12 @@ __device__ __forceinline__ void stage_assemble(const DevModel& M, const Lay& lay
 #pragma unroll
     for (int i = 0; i < 6; i++) cl += s[i] * gc[i];
     sm[lay.c + l] = cl;
-    double* Hrow = H + l * (l + 1) / 2;
     for (int k = l; k >= 0; k = __ldg(M.dof_parent + k)) {
       const double* Sk = sm + lay.S + 6 * k;
       double h = 0;
 #pragma unroll
       for (int i = 0; i < 6; i++) h += Sk[i] * F[i];
-      Hrow[k] = h + (k == l ? diag : 0.0);
+      H[colbase(n, k) + l] = h + (k == l ? diag : 0.0);     // element (l,k), k <= l (see qp_solve)
     }
     // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs
     double lo = -INFINITY, hi = INFINITY;
@@ -360,90 +359,121 @@ __device__ __forceinline__ void stage_assemble(const DevModel& M, const Lay& lay
 }
 
 // ------------------------------------------------------------------ Kernel 3: exact box QP
-//   min 1/2 x'Hx + c'x   s.t. lo <= x <= hi,   H SPD (>= damping I), packed lower in sm[H].
+//   min 1/2 x'Hx + c'x   s.t. lo <= x <= hi,   H SPD (>= damping I).
 // Block principal pivoting (Judice-Pires) with Murty's single-pivot fallback; each pass is one
-// left-looking Cholesky of H with the rows/columns of the active set replaced by identity
-// (lane i owns rows i and i+32), two triangular solves and a KKT check.  The minimiser is unique,
-// so any exact method (daqp in the reference) returns the same x up to rounding.
-// Uses sm[L] (factor; diagonal holds 1/L_kk), sm[rhs], writes sm[x].  Returns #factorisations
+// Cholesky of H with the rows/columns of the active set replaced by identity, two triangular
+// solves and a KKT check.  The minimiser is unique, so any exact method (daqp in the reference)
+// returns the same x up to rounding, whatever active set the search starts from.
+//
+// Storage: H and L are packed lower triangles in COLUMN-major order, element (i,j), i >= j, at
+// colbase(n,j) + i: the lanes of a warp walk down a column, so every shared-memory access of the
+// factorisation is either contiguous across lanes or a broadcast (no bank conflicts).  The
+// factorisation is left-looking by columns; at step k lane l owns row k + l, so all rows still
+// to be computed sit in the low lanes and a second pass is only needed while n - k > 32.
+// Uses sm[L] (diagonal holds 1/L_kk), writes sm[x].  `act_lo`/`act_hi` (warp-uniform bit masks of
+// the dofs held at their lower/upper bound) seed the search and return the final active set, so
+// consecutive solves of one frame start from the previous answer.  Returns #factorisations
 // (negative if H was not positive definite).
 #define QP_PTOL 1e-10
 #define QP_DTOL 1e-9
 
-__device__ __forceinline__ int tri(int i) { return i * (i + 1) / 2; }
+// symmetric read of a packed column-major lower triangle
+__device__ __forceinline__ double sym_at(const double* H, int n, int i, int j) {
+  return i >= j ? H[colbase(n, j) + i] : H[colbase(n, i) + j];
+}
 
-__device__ __forceinline__ int qp_solve(int n, const double* __restrict__ H, const double* __restrict__ c,
-                                        const double* __restrict__ lo, const double* __restrict__ hi,
-                                        double* __restrict__ L, double* __restrict__ rhs, double* __restrict__ x, int lane) {
+__device__ __noinline__ int qp_solve(int n, const double* __restrict__ H, const double* __restrict__ c,
+                                     const double* __restrict__ lo, const double* __restrict__ hi,
+                                     double* __restrict__ L, double* __restrict__ x, int lane,
+                                     unsigned long long& act_lo, unsigned long long& act_hi) {
   const int i0 = lane, i1 = lane + 32;
-  const bool has0 = i0 < n, has1 = i1 < n;
+  const bool has0 = i0 < n, has1 = i1 < n, two = n > 32;
   const double lo0 = has0 ? lo[i0] : 0, hi0 = has0 ? hi[i0] : 0, lo1 = has1 ? lo[i1] : 0, hi1 = has1 ? hi[i1] : 0;
   const double c0 = has0 ? c[i0] : 0, c1 = has1 ? c[i1] : 0;
-  int st0 = 0, st1 = 0;                 // 0 free, -1 at lower, +1 at upper
-  unsigned long long act = 0;           // warp-uniform active mask
+  const int cb0 = colbase(n, i0), cb1 = colbase(n, i1);
+  // 0 free, -1 at lower, +1 at upper; a seed is only honoured where the bound is finite
+  int st0 = 0, st1 = 0;
+  if (has0) st0 = ((act_lo >> i0) & 1ull) && lo0 > -INFINITY ? -1 : (((act_hi >> i0) & 1ull) && hi0 < INFINITY ? 1 : 0);
+  if (has1) st1 = ((act_lo >> i1) & 1ull) && lo1 > -INFINITY ? -1 : (((act_hi >> i1) & 1ull) && hi1 < INFINITY ? 1 : 0);
+  unsigned long long act = (unsigned long long)__ballot_sync(GMR_FULL, st0 != 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 != 0) << 32);
   int best = n + 1, p = 3, nfact = 0;
   bool spd = true;
+  double r0 = 0, r1 = 0;
+#pragma unroll 1
   for (int it = 0; it < 400; it++) {
     // ---- right-hand side: active rows carry their bound, free rows -c_F - H_FA x_A
-    double xa0 = st0 < 0 ? lo0 : (st0 > 0 ? hi0 : 0.0), xa1 = st1 < 0 ? lo1 : (st1 > 0 ? hi1 : 0.0);
+    const double xa0 = st0 < 0 ? lo0 : (st0 > 0 ? hi0 : 0.0), xa1 = st1 < 0 ? lo1 : (st1 > 0 ? hi1 : 0.0);
+    r0 = st0 ? xa0 : -c0;
+    r1 = st1 ? xa1 : -c1;
     if (act) {
       if (has0) x[i0] = xa0;
       if (has1) x[i1] = xa1;
       __syncwarp();
+#pragma unroll 1
+      for (unsigned long long mk = act; mk; mk &= mk - 1) {
+        const int j = __ffsll((long long)mk) - 1;
+        const double xj = x[j];
+        if (has0 && !st0) r0 -= sym_at(H, n, i0, j) * xj;
+        if (has1 && !st1) r1 -= sym_at(H, n, i1, j) * xj;
+      }
+      __syncwarp();
     }
-    double r0 = st0 ? xa0 : -c0, r1 = st1 ? xa1 : -c1;
-    for (unsigned long long mk = act; mk; mk &= mk - 1) {
-      const int j = __ffsll((long long)mk) - 1;
-      const double xj = x[j];
-      if (has0 && !st0) r0 -= H[i0 >= j ? tri(i0) + j : tri(j) + i0] * xj;
-      if (has1 && !st1) r1 -= H[i1 >= j ? tri(i1) + j : tri(j) + i1] * xj;
-    }
-    __syncwarp();
-    // ---- Cholesky, left-looking, identity on the active set
-    const double* Hr0 = H + tri(i0);
-    const double* Hr1 = H + tri(i1);
-    double* Lr0 = L + tri(i0);
-    double* Lr1 = L + tri(i1);
+    // ---- Cholesky, left-looking by columns, identity on the active set
+#pragma unroll 1
     for (int k = 0; k < n; k++) {
       const bool ak = (act >> k) & 1ull;
-      const double* Lk = L + tri(k);
-      double s0 = 0, s1 = 0;
-      if (!ak) {
-        if (has0 && i0 >= k && !st0) {
-          double a = Hr0[k], b = 0;
-          int j = 0;
-          for (; j + 1 < k; j += 2) { a -= Lr0[j] * Lk[j]; b -= Lr0[j + 1] * Lk[j + 1]; }
-          if (j < k) a -= Lr0[j] * Lk[j];
-          s0 = a + b;
+      double* Lk = L + colbase(n, k);
+      const int npass = (n - k > 32) ? 2 : 1;
+      if (ak) {                                    // warp-uniform
+#pragma unroll 1
+        for (int ps = 0; ps < npass; ps++) {
+          const int i = k + lane + 32 * ps;
+          if (i < n) Lk[i] = (i == k) ? 1.0 : 0.0;
         }
-        if (has1 && i1 >= k && !st1) {
-          double a = Hr1[k], b = 0;
-          int j = 0;
-          for (; j + 1 < k; j += 2) { a -= Lr1[j] * Lk[j]; b -= Lr1[j + 1] * Lk[j + 1]; }
-          if (j < k) a -= Lr1[j] * Lk[j];
-          s1 = a + b;
+      } else {
+        double inv = 0;
+#pragma unroll 1
+        for (int ps = 0; ps < npass; ps++) {
+          const int i = k + lane + 32 * ps;
+          const bool in = i < n;
+          const int ic = in ? i : k;               // clamp: idle lanes recompute the pivot row
+          double a = H[colbase(n, k) + ic], b = 0;
+          const double* Lj = L;
+          int j = 0, step = n - 1;
+#pragma unroll 2
+          for (; j + 1 < k; j += 2) {
+            const double* Lj1 = Lj + step;
+            a -= Lj[ic] * Lj[k];
+            b -= Lj1[ic] * Lj1[k];
+            Lj = Lj1 + step - 1;
+            step -= 2;
+          }
+          if (j < k) a -= Lj[ic] * Lj[k];
+          const double s = a + b;
+          if (ps == 0) {
+            double piv = __shfl_sync(GMR_FULL, s, 0);
+            if (!(piv > 0.0)) { spd = false; piv = 1.0; }
+            inv = rsqrt(piv);
+          }
+          if (in) Lk[i] = (i == k) ? inv : (((act >> i) & 1ull) ? 0.0 : s * inv);   // diagonal stores 1/L_kk
         }
       }
-      double piv = __shfl_sync(GMR_FULL, (k < 32) ? s0 : s1, k & 31);
-      if (ak) piv = 1.0;
-      if (!(piv > 0.0)) { spd = false; piv = 1.0; }
-      const double inv = rsqrt(piv);
-      if (has0 && i0 >= k) Lr0[k] = (i0 == k) ? inv : s0 * inv;     // diagonal stores 1/L_kk
-      if (has1 && i1 >= k) Lr1[k] = (i1 == k) ? inv : s1 * inv;
       __syncwarp();
     }
     nfact++;
-    // ---- forward solve L y = r (column oriented), then L' x = y (row oriented)
+    // ---- forward solve L y = r (column oriented), then L' x = y
+#pragma unroll 1
     for (int k = 0; k < n; k++) {
-      const double yk = __shfl_sync(GMR_FULL, (k < 32) ? r0 : r1, k & 31) * L[tri(k) + k];
-      if (i0 == k) r0 = yk; else if (has0 && i0 > k) r0 -= Lr0[k] * yk;
-      if (i1 == k) r1 = yk; else if (has1 && i1 > k) r1 -= Lr1[k] * yk;
+      const double* Lk = L + colbase(n, k);
+      const double yk = __shfl_sync(GMR_FULL, (k < 32) ? r0 : r1, k & 31) * Lk[k];
+      if (i0 == k) r0 = yk; else if (has0 && i0 > k) r0 -= Lk[i0] * yk;
+      if (two) { if (i1 == k) r1 = yk; else if (has1 && i1 > k) r1 -= Lk[i1] * yk; }
     }
+#pragma unroll 1
     for (int k = n - 1; k >= 0; k--) {
-      const double* Lk = L + tri(k);
-      const double xk = __shfl_sync(GMR_FULL, (k < 32) ? r0 : r1, k & 31) * Lk[k];
-      if (i0 == k) r0 = xk; else if (i0 < k) r0 -= Lk[i0] * xk;
-      if (i1 == k) r1 = xk; else if (i1 < k) r1 -= Lk[i1] * xk;
+      const double xk = __shfl_sync(GMR_FULL, (k < 32) ? r0 : r1, k & 31) * L[colbase(n, k) + k];
+      if (i0 == k) r0 = xk; else if (i0 < k) r0 -= L[cb0 + k] * xk;
+      if (two) { if (i1 == k) r1 = xk; else if (has1 && i1 < k) r1 -= L[cb1 + k] * xk; }
     }
     // exact bounds on the active set (the solve reproduces them up to rounding)
     if (st0) r0 = xa0;
@@ -458,12 +488,14 @@ __device__ __forceinline__ int qp_solve(int n, const double* __restrict__ H, con
     if (act) {
       if (has0 && st0) {
         double g = c0;
-        for (int j = 0; j < n; j++) g += H[i0 >= j ? tri(i0) + j : tri(j) + i0] * x[j];
+#pragma unroll 1
+        for (int j = 0; j < n; j++) g += sym_at(H, n, i0, j) * x[j];
         bad0 = st0 < 0 ? (g < -QP_DTOL) : (g > QP_DTOL);
       }
       if (has1 && st1) {
         double g = c1;
-        for (int j = 0; j < n; j++) g += H[i1 >= j ? tri(i1) + j : tri(j) + i1] * x[j];
+#pragma unroll 1
+        for (int j = 0; j < n; j++) g += sym_at(H, n, i1, j) * x[j];
         bad1 = st1 < 0 ? (g < -QP_DTOL) : (g > QP_DTOL);
       }
     }
@@ -479,6 +511,8 @@ __device__ __forceinline__ int qp_solve(int n, const double* __restrict__ H, con
     if (bad1 && (all || i1 == last)) st1 = st1 ? 0 : (r1 < lo1 ? -1 : 1);
     act = (unsigned long long)__ballot_sync(GMR_FULL, st0 != 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 != 0) << 32);
   }
+  act_lo = (unsigned long long)__ballot_sync(GMR_FULL, st0 < 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 < 0) << 32);
+  act_hi = (unsigned long long)__ballot_sync(GMR_FULL, st0 > 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 > 0) << 32);
   __syncwarp();
   return spd ? nfact : -nfact;
 }
@@ -486,7 +520,7 @@ __device__ __forceinline__ int qp_solve(int n, const double* __restrict__ H, con
 // ------------------------------------------------------------------ Kernel 4: integrate
 // solve_ik returns v = dq/dt and integrate_inplace applies q <- q (+) v dt (mj_integratePos);
 // the divide/multiply is kept so rounding follows the reference.
-__device__ __forceinline__ void stage_integrate(const DevModel& M, const Lay& lay, double* sm, int lane) {
+__device__ __noinline__ void stage_integrate(const DevModel& M, const Lay& lay, double* sm, int lane) {
   double* q = sm + lay.q;
   const double* x = sm + lay.x;
   const double dt = M.timestep;
