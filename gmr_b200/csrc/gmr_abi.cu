@@ -2,6 +2,7 @@
 // kernel launches.  No torch types, no exceptions across the boundary.
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <cmath>
 #include <string>
 #include <vector>
@@ -38,7 +39,7 @@ struct gmr_batch {
   double* d_scale = nullptr;    // [B, s_max]
   int* d_counter = nullptr;
   int* d_order = nullptr;
-  int nq_max = 0, s_max = 0, h_max = 0, nbody_max = 0, nv_max = 0, m_max = 0;
+  int nq_max = 0, s_max = 0, h_max = 0, nbody_max = 0, nv_max = 0, m_max = 0, nnz_max = 0;
   Lay lay{};
   int warps_per_cta = 4, grid = 0;
   size_t smem_bytes = 0;
@@ -120,6 +121,25 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   }
   for (int i = 0; i < nv; i++)
     if (dof_parent[i] >= i) return fail(-4, "dofs must be ordered parent-before-child");
+  // branch-induced sparsity tables (see DevModel)
+  std::vector<int> dof_depth(nv, 0), dof_rowptr(nv + 1, 0);
+  int max_depth = 0;
+  for (int i = 0; i < nv; i++) {
+    dof_depth[i] = dof_parent[i] < 0 ? 0 : dof_depth[dof_parent[i]] + 1;
+    max_depth = std::max(max_depth, dof_depth[i]);
+    dof_rowptr[i + 1] = dof_rowptr[i] + dof_depth[i] + 1;
+  }
+  if (max_depth > 31) return fail(-4, "kinematic chains longer than 32 dofs are unsupported");
+  const int nnz = dof_rowptr[nv];
+  std::vector<short> dof_anc(nnz, 0), dof_ancrow(nnz, 0);
+  for (int i = 0; i < nv; i++) {
+    int k = i;
+    for (int a = dof_depth[i]; a >= 0; a--) {
+      dof_anc[dof_rowptr[i] + a] = (short)k;
+      dof_ancrow[dof_rowptr[i] + a] = (short)dof_rowptr[k];
+      k = dof_parent[k];
+    }
+  }
   // levels (level 1 first)
   std::vector<int> level_start(nlevel + 1, 0), level_body;
   for (int lv = 1; lv <= nlevel; lv++) {
@@ -159,7 +179,8 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
          o_tm = bl.push(taskmask), o_si = bl.push(vec(d->scaled_human_index, d->n_scaled)),
          o_sc = bl.push(vec(d->scale, d->n_scaled)), o_po = bl.push(vec(d->pos_off, 3 * d->n_scaled)),
          o_ro = bl.push(vec(d->rot_off, 4 * d->n_scaled)), o_ft = bl.push(vec(d->is_foot, d->n_scaled)),
-         o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot);
+         o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot),
+         o_dd = bl.push(dof_depth), o_rp = bl.push(dof_rowptr), o_an = bl.push(dof_anc), o_ar = bl.push(dof_ancrow);
 
   // FK tail tables (KinematicsModel semantics: bodies under the first top-level body, float32, xyzw)
   const int nbt = nb - 1;
@@ -221,6 +242,9 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.scale = (const double*)(B0 + o_sc); h.pos_off = (const double*)(B0 + o_po); h.rot_off = (const double*)(B0 + o_ro);
   h.is_foot = (const int*)(B0 + o_ft); h.task_body = (const int*)(B0 + o_tb); h.task_src = (const int*)(B0 + o_ts);
   h.task_wpos = (const double*)(B0 + o_wp); h.task_wrot = (const double*)(B0 + o_wr);
+  h.nnz = nnz; h.max_depth = max_depth;
+  h.dof_depth = (const int*)(B0 + o_dd); h.dof_rowptr = (const int*)(B0 + o_rp);
+  h.dof_anc = (const short*)(B0 + o_an); h.dof_ancrow = (const short*)(B0 + o_ar);
   m->max_task = std::max(h.n_task[0], h.n_task[1]);
   char* T0 = m->tail_blob;
   m->tail.nbody = nbt; m->tail.parent = (const int*)(T0 + t_p); m->tail.trans = (const float*)(T0 + t_t);
@@ -243,17 +267,18 @@ extern "C" int gmr_model_destroy(gmr_model* m) {
 }
 
 // ---------------------------------------------------------------- batch
-static Lay make_layout(int nq, int s, int nv, int nbody, int m) {
+static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz) {
   Lay L{};
   int o = 0;
   auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };   // keep 16-byte alignment
   L.q = take(nq); L.scaled = take(7 * s); L.c = take(nv); L.x = take(nv); L.lo = take(nv); L.hi = take(nv);
-  L.H = take(nv * (nv + 1) / 2);
+  L.rv = take(nv); L.H = take(nnz);
   const int region = o;
   L.xpos = take(3 * nbody); L.xquat = take(4 * nbody); L.S = take(6 * nv); L.e = take(6 * m);
   L.K = take(21 * m); L.g = take(6 * m);
-  L.L = region;                                  // Cholesky factor overlays the kinematics scratch
-  o = std::max(o, region + ((nv * (nv + 1) / 2 + 1) & ~1));
+  L.L = region;                                  // the factor overlays the kinematics scratch
+  L.lrow = region + ((nnz + 1) & ~1);
+  o = std::max(o, L.lrow + 32);
   L.total = o;
   L.maxt = GMR_MAX_TASKS;
   return L;
@@ -276,11 +301,12 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
     b->nq_max = std::max(b->nq_max, m->host.nq); b->s_max = std::max(b->s_max, m->host.n_scaled);
     b->h_max = std::max(b->h_max, m->host.n_human); b->nbody_max = std::max(b->nbody_max, m->host.nbody);
     b->nv_max = std::max(b->nv_max, m->host.nv); b->m_max = std::max(b->m_max, m->max_task);
+    b->nnz_max = std::max(b->nnz_max, m->host.nnz);
   }
   if (model_of_instance)
     for (int i = 0; i < B; i++)
       if (model_of_instance[i] < 0 || model_of_instance[i] >= n_models) { delete b; return fail(-1, "model_of_instance out of range"); }
-  b->lay = make_layout(b->nq_max, b->s_max, b->nv_max, b->nbody_max, std::max(b->m_max, 1));
+  b->lay = make_layout(b->nq_max, b->s_max, b->nv_max, b->nbody_max, std::max(b->m_max, 1), b->nnz_max);
   int prev = 0;
   cudaGetDevice(&prev);
   cudaError_t e = cudaSetDevice(b->device);
@@ -299,9 +325,11 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, b->device);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device);
   if (e == cudaSuccess) {
-    // one CTA per SM, all its warps in lockstep through the tick loop (shared instruction stream);
-    // 12 warps = 384 threads keeps the 168-register kernel at one CTA of 64K registers
-    b->warps_per_cta = (int)std::min<size_t>({(size_t)12, (size_t)dev_smem / per_warp, (size_t)B});
+    // CTAs of 4 warps that run the tick loop in lockstep (shared instruction stream), as many CTAs
+    // per SM as shared memory and registers allow (measured: 3 x 4 warps beats 1 x 12 by 12 %)
+    size_t want = 4;
+    if (const char* ev = getenv("GMR_DEBUG_WARPS")) want = (size_t)std::max(1, atoi(ev));
+    b->warps_per_cta = (int)std::min<size_t>({want, (size_t)dev_smem / per_warp, (size_t)B});
     if (b->warps_per_cta < 1) b->warps_per_cta = 1;
     b->smem_bytes = per_warp * b->warps_per_cta;
     if (b->smem_bytes > (size_t)dev_smem) e = cudaErrorInvalidConfiguration;
@@ -425,6 +453,10 @@ static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const in
   a.qpos_out = qpos_out; a.scaled_out = scaled_out;
   a.err_out = diag ? diag->err_dev : nullptr; a.iters_out = diag ? diag->iters_dev : nullptr; a.nfact_out = diag ? diag->nfact_dev : nullptr;
   a.counter = b->d_counter; a.order = b->d_order; a.B = b->B; a.lay = b->lay;
+  a.sync_mask = 0;
+  if (const char* ev = getenv("GMR_DEBUG_SYNC_MASK")) a.sync_mask = atoi(ev);
+  a.sync_period = 2;
+  if (const char* ev = getenv("GMR_DEBUG_SYNC_PERIOD")) a.sync_period = std::max(1, atoi(ev));
   CU(cudaMemsetAsync(b->d_counter, 0, sizeof(int), b->stream));
   if (dtype == GMR_F32) clip_kernel<float><<<b->grid, 32 * b->warps_per_cta, b->smem_bytes, b->stream>>>(a);
   else clip_kernel<double><<<b->grid, 32 * b->warps_per_cta, b->smem_bytes, b->stream>>>(a);
@@ -486,6 +518,16 @@ extern "C" int gmr_build_qp(gmr_batch* b, int stage, const double* scaled_dev, d
   a.stage = stage; a.scaled = scaled_dev; a.e_out = e_out_dev; a.H_out = H_out_dev; a.c_out = c_out_dev;
   a.lo_out = lo_out_dev; a.hi_out = hi_out_dev;
   STAGE_LAUNCH(build_qp_kernel, b, a);
+  return 0;
+}
+
+extern "C" int gmr_solve_ik(gmr_batch* b, int stage, const double* scaled_dev, double* dq_out_dev, int32_t* nfact_out_dev) {
+  if (!b || !scaled_dev || !dq_out_dev) return fail(-1, "null argument");
+  if (stage < 0 || stage > 1) return fail(-1, "stage must be 0 or 1");
+  DevGuard g(b->device);
+  StageArgs a = stage_args(b);
+  a.stage = stage; a.scaled = scaled_dev; a.dq_out = dq_out_dev; a.nfact_out = nfact_out_dev;
+  STAGE_LAUNCH(solve_ik_kernel, b, a);
   return 0;
 }
 

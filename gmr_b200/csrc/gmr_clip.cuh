@@ -31,6 +31,8 @@ struct RunArgs {
   int* counter;                  // work queue head
   const int* order;              // [B] or null
   int B;
+  int sync_mask;                 // bit 0/1: CTA barrier after phase 1/2 (lockstep tuning)
+  int sync_period;               // CTA barrier at the top of every sync_period-th tick
   Lay lay;
 };
 
@@ -80,14 +82,18 @@ __device__ __noinline__ void begin_frame(const RunArgs& a, const DevModel& M, co
 }
 
 template <typename TIn>
-__global__ void __launch_bounds__(384, 1) clip_kernel(const RunArgs a) {
+__global__ void __launch_bounds__(128, 4) clip_kernel(const RunArgs a) {
   extern __shared__ double smem[];
+  __shared__ unsigned short pair_tab[PAIR_TAB_SIZE];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const Lay lay = a.lay;
   double* sm = smem + (size_t)warp * lay.total;
+  fill_pair_tab(pair_tab);
+  __syncthreads();
   Slot s;
   s.inst = -1; s.t = s.T = 0; s.stage = 2; s.it = 0; s.nfact = 0; s.curr = 0; s.act_lo = s.act_hi = 0;
   bool drained = false;
+  int tick = 0;
   const DevModel* Mp = a.models;
   for (;;) {
     // ---- phase 0: warps without an instance pull the next clip from the queue
@@ -111,7 +117,8 @@ __global__ void __launch_bounds__(384, 1) clip_kernel(const RunArgs a) {
         (void)inst;
       }
     }
-    if (!__syncthreads_or(s.inst >= 0)) break;
+    if (tick % a.sync_period == 0) { if (!__syncthreads_or(s.inst >= 0)) break; }
+    tick++;
     const DevModel& M = *Mp;
     const bool on = s.inst >= 0;
     // ---- phase 1: task stiffness + QP assembly (mink build_ik)
@@ -119,13 +126,14 @@ __global__ void __launch_bounds__(384, 1) clip_kernel(const RunArgs a) {
       const double mu = stage_stiffness(M, lay, sm, s.stage, lane);
       stage_assemble(M, lay, sm, s.stage, mu, lane);
     }
-    __syncthreads();
+    if (a.sync_mask & 1) __syncthreads();
     // ---- phase 2: box QP
     if (on) {
-      const int nf = qp_solve(M.nv, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.x, lane, s.act_lo, s.act_hi);
+      const int nf = qp_solve_tree(M, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
+                                   sm + lay.x, pair_tab, lane, s.act_lo, s.act_hi);
       s.nfact = (nf < 0 || s.nfact < 0) ? -abs(s.nfact) - abs(nf) : s.nfact + nf;
     }
-    __syncthreads();
+    if (a.sync_mask & 2) __syncthreads();
     // ---- phase 3: integrate, FK, error, and the control decisions of motion_retarget.py:143-185
     if (on) {
       stage_integrate(M, lay, sm, lane);
@@ -188,6 +196,8 @@ struct StageArgs {
   const double* q;        // [B,nq_max]
   const double* scaled;   // [B,s_max,7]
   double *scaled_out, *xpos_out, *xquat_out, *e_out, *H_out, *c_out, *lo_out, *hi_out;
+  double* dq_out;         // [B,nv_max]
+  int* nfact_out;         // [B]
 };
 
 template <typename TIn>
@@ -238,13 +248,39 @@ __global__ void build_qp_kernel(const StageArgs a) {
   double* Ho = a.H_out + (size_t)inst * a.nv_max * a.nv_max;
   for (int idx = lane; idx < n * n; idx += 32) {
     const int i = idx / n, j = idx % n;
-    Ho[i * a.nv_max + j] = sym_at(sm + lay.H, n, i, j);
+    Ho[i * a.nv_max + j] = tree_at(M, sm + lay.H, i, j);
   }
   for (int i = lane; i < n; i += 32) {
     a.c_out[(size_t)inst * a.nv_max + i] = sm[lay.c + i];
     a.lo_out[(size_t)inst * a.nv_max + i] = sm[lay.lo + i];
     a.hi_out[(size_t)inst * a.nv_max + i] = sm[lay.hi + i];
   }
+}
+
+// one mink.solve_ik call on the batch state: dq = argmin of the stage's QP (tree solver)
+__global__ void solve_ik_kernel(const StageArgs a) {
+  extern __shared__ double smem[];
+  __shared__ unsigned short pair_tab[PAIR_TAB_SIZE];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
+  fill_pair_tab(pair_tab);
+  __syncthreads();
+  if (inst >= a.B) return;
+  const Lay& lay = a.lay;
+  double* sm = smem + (size_t)warp * lay.total;
+  const DevModel& M = a.models[a.model_of ? a.model_of[inst] : 0];
+  for (int i = lane; i < M.nq; i += 32) sm[lay.q + i] = a.q[(size_t)inst * a.nq_max + i];
+  for (int i = lane; i < M.n_scaled * 7; i += 32) sm[lay.scaled + i] = a.scaled[(size_t)inst * a.s_max * 7 + i];
+  __syncwarp();
+  stage_fk(M, lay, sm, lane);
+  stage_errors(M, lay, sm, a.stage, lane);
+  const double mu = stage_stiffness(M, lay, sm, a.stage, lane);
+  stage_assemble(M, lay, sm, a.stage, mu, lane);
+  unsigned long long act_lo = 0, act_hi = 0;
+  const int nf = qp_solve_tree(M, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
+                               sm + lay.x, pair_tab, lane, act_lo, act_hi);
+  for (int i = lane; i < M.nv; i += 32) a.dq_out[(size_t)inst * a.nv_max + i] = sm[lay.x + i];
+  if (lane == 0 && a.nfact_out) a.nfact_out[inst] = nf;
 }
 
 // generic box QP: H [n_qp, n, n] full symmetric

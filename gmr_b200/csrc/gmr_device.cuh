@@ -46,6 +46,16 @@ struct DevModel {
   const double* dof_lo;      // [nv] joint range lower
   const double* dof_hi;      // [nv]
   const unsigned* dof_taskmask;  // [2*nv] bit t set: task t of the stage is in the dof's subtree
+  // branch-induced sparsity of H = J'WJ + mu I (Featherstone): H(i,k) != 0 only if k is an
+  // ancestor-or-self of i (or vice versa).  Row i of the packed lower triangle holds its
+  // depth[i]+1 entries in chain order: entry a (0 = topmost ancestor, depth[i] = i itself) is
+  // column anc[rowptr[i]+a], stored at rowptr[i]+a.  The ancestor at chain position a has depth a,
+  // so H(anc_a, anc_b), b <= a, sits at rowptr[anc_a] + b = ancrow[rowptr[i]+a] + b.
+  int nnz, max_depth;
+  const int* dof_depth;          // [nv]
+  const int* dof_rowptr;         // [nv+1]
+  const short* dof_anc;          // [nnz]
+  const short* dof_ancrow;       // [nnz] rowptr of that ancestor
   // target preparation
   const int* scaled_index;   // [s] body index inside a human frame
   const double* scale;       // [s]
@@ -61,9 +71,9 @@ struct DevModel {
 
 // Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
 struct Lay {
-  int q, scaled, c, x, lo, hi, H;         // persistent across the QP solve
+  int q, scaled, c, x, lo, hi, rv, H;     // persistent across the QP solve (H: nnz packed tree rows)
   int xpos, xquat, S, e, K, g;            // kinematics / assembly scratch ...
-  int L;                                  // ... overlaid by the Cholesky factor during the solve
+  int L, lrow;                            // ... overlaid by the factor (nnz) + one row (32) during the solve
   int total;                              // doubles per warp
   int maxt;                               // stride of the stage-major task tables
 };

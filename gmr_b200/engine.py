@@ -245,6 +245,18 @@ class BatchedRetargeter:
         return H, c, lo, hi, e
 
 
+def _solve_ik(self, stage, scaled):
+    """One solve_ik on the batch state -> (dq [B,nv_max], nfact [B]) (tree-structured QP of the fused path)."""
+    scaled = self._dev(scaled, torch.float64, (self.B, self.s_max, 7))
+    dq = torch.zeros((self.B, self.nv_max), dtype=torch.float64, device=self.tdev)
+    nf = torch.zeros((self.B,), dtype=torch.int32, device=self.tdev)
+    _lib.check(_lib.lib().gmr_solve_ik(self._h, int(stage), _ptr(scaled), _ptr(dq), _ptr(nf)), "gmr_solve_ik")
+    return dq, nf
+
+
+BatchedRetargeter.solve_ik = _solve_ik
+
+
 def qp_solve(H, c, lo, hi, device: int = 0):
     """Batched exact box QP on the device: H [N,n,n], c/lo/hi [N,n] -> x [N,n], nfact [N]."""
     dev = torch.device("cuda", device)

@@ -152,7 +152,11 @@ int gmr_fk(gmr_batch* b, const double* q_dev, double* xpos_out_dev, double* xqua
  * H [B,nv_max,nv_max] (full symmetric), c, lo, hi [B,nv_max]; targets = scaled_dev [B,s,7] */
 int gmr_build_qp(gmr_batch* b, int stage, const double* scaled_dev, double* e_out_dev,
                  double* H_out_dev, double* c_out_dev, double* lo_out_dev, double* hi_out_dev);
-/* Kernel 3 (solve): box QP for arbitrary SPD H: dq [n_qp,n] ; nfact [n_qp] or NULL */
+/* Kernel 2+3: one mink.solve_ik on the batch state (motion_retarget.py:147-149): assembly + the
+ * tree-structured box QP of the fused path; dq_out_dev [B,nv_max] (= v*dt), nfact [B] or NULL */
+int gmr_solve_ik(gmr_batch* b, int stage, const double* scaled_dev, double* dq_out_dev,
+                 int32_t* nfact_out_dev);
+/* Kernel 3 (dense variant): box QP for arbitrary SPD H: x [n_qp,n] ; nfact [n_qp] or NULL */
 int gmr_qp_solve(int device, void* stream, int n_qp, int n, const double* H_dev,
                  const double* c_dev, const double* lo_dev, const double* hi_dev,
                  double* x_out_dev, int32_t* nfact_out_dev);

@@ -116,6 +116,39 @@ def test_kernel23_build_qp(src, robot):
             np.testing.assert_allclose(hi[b, :m.nv][fin], hir[fin], atol=1e-14)
 
 
+@pytest.mark.parametrize("src,robot", PAIRS)
+def test_kernel3_tree_qp_solve_ik(src, robot):
+    """The tree-structured (L'L, no fill-in) box QP of the fused path against the oracle's dense
+    active-set solve of the oracle's own H, c, box - from states pushed against the joint limits."""
+    from oracle import oracle as oc
+    B = 32
+    m, t, dm, br, human, heights = _setup(src, robot, B, 2)
+    rng = np.random.default_rng(4)
+    q = _random_q(m, rng, B)
+    for j in range(m.njnt):          # park a third of the limited joints on / next to a limit
+        if m.jnt_type[j] != 0 and m.jnt_limited[j]:
+            qa = m.jnt_qposadr[j]
+            pick = rng.random(B) < 0.35
+            side = rng.random(B) < 0.5
+            eps = rng.uniform(0, 0.02, size=B)
+            q[pick, qa] = np.where(side, m.jnt_range[j, 0] + eps, m.jnt_range[j, 1] - eps)[pick]
+    br.reset(q)
+    scaled = br.target_prep(human[:, 0]).cpu().numpy()
+    n_active = 0
+    for stage in range(2):
+        if not t.use_table[stage]:
+            continue
+        dq, nf = br.solve_ik(stage, scaled)
+        dq, nf = dq.cpu().numpy(), nf.cpu().numpy()
+        assert (nf > 0).all()
+        for b in range(B):
+            Hr, cr, lor, hir, _ = oc.build_qp(dm.desc, q[b], stage, scaled[b, :t.n_scaled])
+            xr, _ = oc.box_qp(Hr, cr, lor, hir)
+            np.testing.assert_allclose(dq[b, :m.nv], xr, atol=1e-9)
+            n_active += int(((xr <= lor) | (xr >= hir)).sum())
+    assert n_active > 0, "test did not exercise the active set"
+
+
 @pytest.mark.parametrize("n", [5, 27, 35, 49, 64])
 def test_kernel3_qp_solve(n):
     from gmr_b200.engine import qp_solve
