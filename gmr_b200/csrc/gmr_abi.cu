@@ -42,7 +42,9 @@ struct gmr_batch {
   int nq_max = 0, s_max = 0, h_max = 0, nbody_max = 0, nv_max = 0, m_max = 0, nnz_max = 0;
   Lay lay{};
   int warps_per_cta = 4, grid = 0;
-  size_t smem_bytes = 0;
+  size_t smem_bytes = 0;          // per-warp blocks only (stage kernels)
+  size_t clip_smem_bytes = 0;     // + the staged model of the fused kernel
+  bool smem_model = false;
 };
 
 extern "C" const char* gmr_last_error(void) { return g_err.c_str(); }
@@ -175,7 +177,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
          o_jtype = bl.push(vec(d->jnt_type, nj)), o_jq = bl.push(vec(d->jnt_qposadr, nj)),
          o_jd = bl.push(vec(d->jnt_dofadr, nj)), o_jaxis = bl.push(vec(d->jnt_axis, 3 * nj)),
          o_q0 = bl.push(vec(d->qpos0, d->nq)), o_dk = bl.push(dof_kind), o_dq = bl.push(dof_qadr),
-         o_dp = bl.push(dof_parent), o_dl = bl.push(dof_limited), o_dlo = bl.push(dof_lo), o_dhi = bl.push(dof_hi),
+         o_dp = bl.push(dof_parent), o_db = bl.push(dof_body), o_dl = bl.push(dof_limited), o_dlo = bl.push(dof_lo), o_dhi = bl.push(dof_hi),
          o_tm = bl.push(taskmask), o_si = bl.push(vec(d->scaled_human_index, d->n_scaled)),
          o_sc = bl.push(vec(d->scale, d->n_scaled)), o_po = bl.push(vec(d->pos_off, 3 * d->n_scaled)),
          o_ro = bl.push(vec(d->rot_off, 4 * d->n_scaled)), o_ft = bl.push(vec(d->is_foot, d->n_scaled)),
@@ -237,6 +239,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.jnt_qposadr = (const int*)(B0 + o_jq); h.jnt_dofadr = (const int*)(B0 + o_jd);
   h.jnt_axis = (const double*)(B0 + o_jaxis); h.qpos0 = (const double*)(B0 + o_q0);
   h.dof_kind = (const int*)(B0 + o_dk); h.dof_qadr = (const int*)(B0 + o_dq); h.dof_parent = (const int*)(B0 + o_dp);
+  h.dof_body = (const int*)(B0 + o_db); h.blob = B0; h.blob_bytes = (int)bl.bytes.size();
   h.dof_limited = (const int*)(B0 + o_dl); h.dof_lo = (const double*)(B0 + o_dlo); h.dof_hi = (const double*)(B0 + o_dhi);
   h.dof_taskmask = (const unsigned*)(B0 + o_tm); h.scaled_index = (const int*)(B0 + o_si);
   h.scale = (const double*)(B0 + o_sc); h.pos_off = (const double*)(B0 + o_po); h.rot_off = (const double*)(B0 + o_ro);
@@ -276,6 +279,8 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz) {
   const int region = o;
   L.xpos = take(3 * nbody); L.xquat = take(4 * nbody); L.S = take(6 * nv); L.e = take(6 * m);
   L.K = take(21 * m); L.g = take(6 * m);
+  L.tl = L.K; L.ql = L.tl + ((3 * nbody + 1) & ~1);          // FK local transforms alias K/g
+  o = std::max(o, L.ql + ((4 * nbody + 1) & ~1));
   L.L = region;                                  // the factor overlays the kinematics scratch
   L.lrow = region + ((nnz + 1) & ~1);
   o = std::max(o, L.lrow + 32);
@@ -319,25 +324,33 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   if (e == cudaSuccess) e = cudaMemcpy(b->d_models, hm.data(), sizeof(DevModel) * n_models, cudaMemcpyHostToDevice);
   if (e == cudaSuccess && model_of_instance)
     e = cudaMemcpy(b->d_model_of, model_of_instance, sizeof(int) * (size_t)B, cudaMemcpyHostToDevice);
-  // launch geometry: one instance per warp, as many warps per SM as shared memory and registers allow
+  // launch geometry: one instance per warp; CTAs of 4 warps that run the tick loop in lockstep
+  // (shared instruction stream), as many CTAs per SM as shared memory and registers allow
+  // (measured: 3 x 4 warps beats 1 x 12 by 12 %).  Single-model batches stage the model tables in
+  // shared memory (one copy per CTA).
   const size_t per_warp = sizeof(double) * (size_t)b->lay.total;
   int dev_smem = 0, sms = 0;
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, b->device);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device);
   if (e == cudaSuccess) {
-    // CTAs of 4 warps that run the tick loop in lockstep (shared instruction stream), as many CTAs
-    // per SM as shared memory and registers allow (measured: 3 x 4 warps beats 1 x 12 by 12 %)
     size_t want = 4;
     if (const char* ev = getenv("GMR_DEBUG_WARPS")) want = (size_t)std::max(1, atoi(ev));
-    b->warps_per_cta = (int)std::min<size_t>({want, (size_t)dev_smem / per_warp, (size_t)B});
+    const size_t blob = n_models == 1 ? (((size_t)models[0]->blob_bytes + 15) & ~size_t(15)) : 0;
+    const size_t fixed = 4096;      // static shared memory of the kernel (pair table, DevModel copy) + slack
+    b->smem_model = n_models == 1 && per_warp + blob + fixed <= (size_t)dev_smem && !getenv("GMR_DEBUG_GLOBAL_MODEL");
+    const size_t avail = (size_t)dev_smem - fixed - (b->smem_model ? blob : 0);
+    b->warps_per_cta = (int)std::min<size_t>({want, avail / per_warp, (size_t)B});
     if (b->warps_per_cta < 1) b->warps_per_cta = 1;
     b->smem_bytes = per_warp * b->warps_per_cta;
-    if (b->smem_bytes > (size_t)dev_smem) e = cudaErrorInvalidConfiguration;
+    b->clip_smem_bytes = b->smem_bytes + (b->smem_model ? blob : 0);
+    if (b->clip_smem_bytes + fixed > (size_t)dev_smem) e = cudaErrorInvalidConfiguration;
   }
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(clip_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(clip_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes);
+  const void* kf = b->smem_model ? (const void*)clip_kernel<float, true> : (const void*)clip_kernel<float, false>;
+  const void* kd = b->smem_model ? (const void*)clip_kernel<double, true> : (const void*)clip_kernel<double, false>;
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->clip_smem_bytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(kd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->clip_smem_bytes);
   int per_sm = 0;
-  if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, clip_kernel<float>, 32 * b->warps_per_cta, b->smem_bytes);
+  if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kf, 32 * b->warps_per_cta, b->clip_smem_bytes);
   if (e == cudaSuccess) {
     if (per_sm < 1) per_sm = 1;
     const int need = (B + b->warps_per_cta - 1) / b->warps_per_cta;
@@ -434,7 +447,7 @@ extern "C" int gmr_batch_launch_info(const gmr_batch* b, int32_t* grid, int32_t*
   if (!b) return fail(-1, "null batch");
   if (grid) *grid = b->grid;
   if (warps_per_cta) *warps_per_cta = b->warps_per_cta;
-  if (smem_bytes) *smem_bytes = (int)b->smem_bytes;
+  if (smem_bytes) *smem_bytes = (int)b->clip_smem_bytes;
   if (smem_per_instance) *smem_per_instance = (int)(sizeof(double) * b->lay.total);
   return 0;
 }
@@ -453,13 +466,17 @@ static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const in
   a.qpos_out = qpos_out; a.scaled_out = scaled_out;
   a.err_out = diag ? diag->err_dev : nullptr; a.iters_out = diag ? diag->iters_dev : nullptr; a.nfact_out = diag ? diag->nfact_dev : nullptr;
   a.counter = b->d_counter; a.order = b->d_order; a.B = b->B; a.lay = b->lay;
-  a.sync_mask = 0;
-  if (const char* ev = getenv("GMR_DEBUG_SYNC_MASK")) a.sync_mask = atoi(ev);
   a.sync_period = 2;
   if (const char* ev = getenv("GMR_DEBUG_SYNC_PERIOD")) a.sync_period = std::max(1, atoi(ev));
   CU(cudaMemsetAsync(b->d_counter, 0, sizeof(int), b->stream));
-  if (dtype == GMR_F32) clip_kernel<float><<<b->grid, 32 * b->warps_per_cta, b->smem_bytes, b->stream>>>(a);
-  else clip_kernel<double><<<b->grid, 32 * b->warps_per_cta, b->smem_bytes, b->stream>>>(a);
+  const dim3 grid(b->grid), block(32 * b->warps_per_cta);
+  if (b->smem_model) {
+    if (dtype == GMR_F32) clip_kernel<float, true><<<grid, block, b->clip_smem_bytes, b->stream>>>(a);
+    else clip_kernel<double, true><<<grid, block, b->clip_smem_bytes, b->stream>>>(a);
+  } else {
+    if (dtype == GMR_F32) clip_kernel<float, false><<<grid, block, b->clip_smem_bytes, b->stream>>>(a);
+    else clip_kernel<double, false><<<grid, block, b->clip_smem_bytes, b->stream>>>(a);
+  }
   CU(cudaGetLastError());
   return 0;
 }

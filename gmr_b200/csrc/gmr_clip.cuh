@@ -31,7 +31,6 @@ struct RunArgs {
   int* counter;                  // work queue head
   const int* order;              // [B] or null
   int B;
-  int sync_mask;                 // bit 0/1: CTA barrier after phase 1/2 (lockstep tuning)
   int sync_period;               // CTA barrier at the top of every sync_period-th tick
   Lay lay;
 };
@@ -42,6 +41,7 @@ struct Slot {
   int t, T;                      // current frame, clip length
   int stage, it;                 // stage being solved, loop counter of motion_retarget.py:152/171
   int nfact;                     // factorisations in this frame (negative once H was not SPD)
+  bool new_frame, fresh, need_fk;
   double curr;                   // curr_error of the reference loop
   unsigned long long act_lo, act_hi;   // active set of the previous solve of this frame/stage
 };
@@ -52,133 +52,123 @@ __device__ __forceinline__ int next_stage(const DevModel& M, int stage) {
   return stage;
 }
 
-// Kernel 4 (control): what the reference does between two solve_ik calls, as a state machine.
-// Called once per tick by every warp that holds an instance, right after FK + error evaluation.
-// A "tick" is one solve_ik + integrate_inplace; the stage loop, the frame loop and the clip queue
-// advance here, so every warp of the CTA executes the same solver code in every tick whatever
-// frame, stage or iteration its own instance is in.
-template <typename TIn>
-__device__ __noinline__ void begin_frame(const RunArgs& a, const DevModel& M, const Lay& lay, double* sm, Slot& s, int lane) {
-  // frames without an enabled stage pass straight through (use_ik_match_table1/2 both false)
-  for (;;) {
-    const TIn* human = (const TIn*)a.human + (size_t)s.inst * a.human_inst_stride + (size_t)s.t * a.human_frame_stride;
-    stage_prep<TIn>(M, lay, sm, human, a.scale + (size_t)s.inst * a.s_max, a.to_ground != 0, lane);
-    const size_t o = (size_t)s.inst * a.T_max + s.t;
-    if (a.scaled_out) {
-      double* so = a.scaled_out + o * a.s_max * 7;
-      for (int i = lane; i < M.n_scaled * 7; i += 32) so[i] = sm[lay.scaled + i];
-    }
-    s.stage = next_stage(M, -1);
-    s.it = 0; s.nfact = 0; s.act_lo = s.act_hi = 0;
-    if (s.stage < 2) { s.curr = stage_errors(M, lay, sm, s.stage, lane); return; }
-    if (lane == 0) {
-      if (a.err_out) { a.err_out[2 * o] = 0; a.err_out[2 * o + 1] = 0; }
-      if (a.iters_out) { a.iters_out[2 * o] = 0; a.iters_out[2 * o + 1] = 0; }
-      if (a.nfact_out) a.nfact_out[o] = 0;
-    }
-    if (a.qpos_out) for (int i = lane; i < M.nq; i += 32) a.qpos_out[o * a.nq_max + i] = sm[lay.q + i];
-    if (++s.t >= s.T) { s.inst = -1; return; }
-  }
-}
-
-template <typename TIn>
-__global__ void __launch_bounds__(128, 4) clip_kernel(const RunArgs a) {
+// The fused kernel.  A "tick" is: [FK if q changed] -> control (Kernel 4) -> one solve_ik +
+// integrate_inplace.  The control block is what the reference does between two solve_ik calls
+// (motion_retarget.py:143-185), as a state machine: evaluate the stage error; first evaluation of a
+// stage -> it is curr_error, solve; otherwise compare with curr_error -> solve again, or close the
+// stage (next stage / next frame: Kernel 1 on the new frame / next clip from the queue).  Every warp
+// of the CTA therefore executes the same solver code in every tick, whatever frame, stage or
+// iteration its own instance is in, and each stage function has exactly one call site.
+// SM = true: single-model batch, model tables staged in shared memory.
+template <typename TIn, bool SM>
+__global__ void __launch_bounds__(128, 3) clip_kernel(const RunArgs a) {
   extern __shared__ double smem[];
   __shared__ unsigned short pair_tab[PAIR_TAB_SIZE];
+  __shared__ DevModel smodel;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const Lay lay = a.lay;
   double* sm = smem + (size_t)warp * lay.total;
   fill_pair_tab(pair_tab);
+  ModelView<SM> mv;
+  mv.m = a.models;
+  mv.sblob = nullptr;
+  if (SM) {   // stage the model: struct + table blob (16-byte words) behind the per-warp blocks
+    char* sb = (char*)(smem + (size_t)(blockDim.x >> 5) * lay.total);
+    const int4* src = (const int4*)a.models[0].blob;
+    int4* dst = (int4*)sb;
+    const int nw = (a.models[0].blob_bytes + 15) >> 4;
+    for (int i = threadIdx.x; i < nw; i += blockDim.x) dst[i] = src[i];
+    const int* ms = (const int*)a.models;
+    int* md = (int*)&smodel;
+    for (int i = threadIdx.x; i < (int)(sizeof(DevModel) / 4); i += blockDim.x) md[i] = ms[i];
+    mv.m = &smodel;
+    mv.sblob = sb;
+  }
   __syncthreads();
   Slot s;
   s.inst = -1; s.t = s.T = 0; s.stage = 2; s.it = 0; s.nfact = 0; s.curr = 0; s.act_lo = s.act_hi = 0;
+  s.new_frame = s.fresh = s.need_fk = false;
   bool drained = false;
   int tick = 0;
-  const DevModel* Mp = a.models;
   for (;;) {
-    // ---- phase 0: warps without an instance pull the next clip from the queue
+    // ---- warps without an instance pull the next clip from the queue
     while (s.inst < 0 && !drained) {
       int slot = 0;
       if (lane == 0) slot = atomicAdd(a.counter, 1);
       slot = __shfl_sync(GMR_FULL, slot, 0);
       if (slot >= a.B) { drained = true; break; }
       s.inst = a.order ? a.order[slot] : slot;
-      Mp = a.models + (a.model_of ? a.model_of[s.inst] : 0);
+      if (!SM) mv.m = a.models + (a.model_of ? a.model_of[s.inst] : 0);
       s.T = a.T_of ? min(a.T_of[s.inst], a.T_max) : a.T_max;
       s.t = 0;
       if (s.T <= 0) { s.inst = -1; continue; }
       const double* qs = a.q_state + (size_t)s.inst * a.nq_max;
-      for (int i = lane; i < Mp->nq; i += 32) sm[lay.q + i] = qs[i];
+      for (int i = lane; i < mv.M().nq; i += 32) sm[lay.q + i] = qs[i];
       __syncwarp();
-      stage_fk(*Mp, lay, sm, lane);
-      const int inst = s.inst;
-      begin_frame<TIn>(a, *Mp, lay, sm, s, lane);
-      if (s.inst < 0) {            // clip had no enabled stage: state unchanged
-        (void)inst;
-      }
+      s.new_frame = true; s.need_fk = true;
     }
     if (tick % a.sync_period == 0) { if (!__syncthreads_or(s.inst >= 0)) break; }
     tick++;
-    const DevModel& M = *Mp;
-    const bool on = s.inst >= 0;
-    // ---- phase 1: task stiffness + QP assembly (mink build_ik)
-    if (on) {
-      const double mu = stage_stiffness(M, lay, sm, s.stage, lane);
-      stage_assemble(M, lay, sm, s.stage, mu, lane);
-    }
-    if (a.sync_mask & 1) __syncthreads();
-    // ---- phase 2: box QP
-    if (on) {
-      const int nf = qp_solve_tree(M, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
-                                   sm + lay.x, pair_tab, lane, s.act_lo, s.act_hi);
-      s.nfact = (nf < 0 || s.nfact < 0) ? -abs(s.nfact) - abs(nf) : s.nfact + nf;
-    }
-    if (a.sync_mask & 2) __syncthreads();
-    // ---- phase 3: integrate, FK, error, and the control decisions of motion_retarget.py:143-185
-    if (on) {
-      stage_integrate(M, lay, sm, lane);
-      stage_fk(M, lay, sm, lane);
-      const double next = stage_errors(M, lay, sm, s.stage, lane);
-      if (s.curr - next > M.converge_eps && s.it < M.max_iter) {
-        s.curr = next;
-        s.it++;
-      } else {
-        const size_t o = (size_t)s.inst * a.T_max + s.t;
-        if (lane == 0) {
-          if (a.err_out) a.err_out[2 * o + s.stage] = next;
-          if (a.iters_out) a.iters_out[2 * o + s.stage] = s.it + 1;
+    if (s.inst < 0) continue;
+    const DevModel& M = mv.M();
+    // ---- Kernel 2: FK (q changed: integrate of the previous tick, or a new clip)
+    if (s.need_fk) { stage_fk(mv, lay, sm, lane); s.need_fk = false; }
+    // ---- Kernel 4: control
+    bool solve = false;
+    for (;;) {
+      const size_t o = (size_t)s.inst * a.T_max + s.t;
+      if (s.new_frame) {      // Kernel 1 on frame t
+        const TIn* human = (const TIn*)a.human + (size_t)s.inst * a.human_inst_stride + (size_t)s.t * a.human_frame_stride;
+        stage_prep<TIn>(mv, lay, sm, human, a.scale + (size_t)s.inst * a.s_max, a.to_ground != 0, lane);
+        if (a.scaled_out) {
+          double* so = a.scaled_out + o * a.s_max * 7;
+          for (int i = lane; i < M.n_scaled * 7; i += 32) so[i] = sm[lay.scaled + i];
         }
-        const int prev = s.stage;
-        s.stage = next_stage(M, s.stage);
-        s.it = 0; s.act_lo = s.act_hi = 0;
-        if (s.stage < 2) {
-          s.curr = stage_errors(M, lay, sm, s.stage, lane);
-        } else {
-          if (lane == 0) {
-            for (int k = 0; k < 2; k++)
-              if (!M.use[k]) {
-                if (a.err_out) a.err_out[2 * o + k] = 0;
-                if (a.iters_out) a.iters_out[2 * o + k] = 0;
-              }
-            if (a.nfact_out) a.nfact_out[o] = s.nfact;
-          }
-          (void)prev;
-          if (a.qpos_out) {
-            double* qo = a.qpos_out + o * a.nq_max;
-            for (int i = lane; i < M.nq; i += 32) qo[i] = sm[lay.q + i];
-          }
-          if (++s.t < s.T) {
-            begin_frame<TIn>(a, M, lay, sm, s, lane);
-          } else {
-            double* qs = a.q_state + (size_t)s.inst * a.nq_max;
-            for (int i = lane; i < M.nq; i += 32) qs[i] = sm[lay.q + i];
-            __syncwarp();
-            s.inst = -1;
-          }
+        s.new_frame = false;
+        s.stage = next_stage(M, -1);
+        s.fresh = true; s.it = 0; s.nfact = 0; s.act_lo = s.act_hi = 0;
+        if (lane == 0) {      // stages that are switched off report zeros
+          for (int k = 0; k < 2; k++)
+            if (!M.use[k]) {
+              if (a.err_out) a.err_out[2 * o + k] = 0;
+              if (a.iters_out) a.iters_out[2 * o + k] = 0;
+            }
         }
       }
+      if (s.stage < 2) {
+        const double err = stage_errors(mv, lay, sm, s.stage, lane);
+        if (s.fresh) { s.curr = err; s.fresh = false; solve = true; break; }                           // :145 / :165
+        if (s.curr - err > M.converge_eps && s.it < M.max_iter) { s.curr = err; s.it++; solve = true; break; }   // :153 / :172
+        if (lane == 0) {
+          if (a.err_out) a.err_out[2 * o + s.stage] = err;
+          if (a.iters_out) a.iters_out[2 * o + s.stage] = s.it + 1;
+        }
+        s.stage = next_stage(M, s.stage);
+        s.it = 0; s.act_lo = s.act_hi = 0;
+        if (s.stage < 2) { s.fresh = true; continue; }
+      }
+      // frame finished (:185)
+      if (lane == 0 && a.nfact_out) a.nfact_out[o] = s.nfact;
+      if (a.qpos_out) {
+        double* qo = a.qpos_out + o * a.nq_max;
+        for (int i = lane; i < M.nq; i += 32) qo[i] = sm[lay.q + i];
+      }
+      if (++s.t < s.T) { s.new_frame = true; continue; }
+      double* qs = a.q_state + (size_t)s.inst * a.nq_max;
+      for (int i = lane; i < M.nq; i += 32) qs[i] = sm[lay.q + i];
+      __syncwarp();
+      s.inst = -1;
+      break;
     }
-    // (phase 0 of the next tick follows; its barrier closes this phase)
+    if (!solve) continue;
+    // ---- Kernel 2+3: task stiffness, QP assembly (mink build_ik), box QP; Kernel 4: integrate
+    const double mu = stage_stiffness(mv, lay, sm, s.stage, lane);
+    stage_assemble(mv, lay, sm, s.stage, mu, lane);
+    const int nf = qp_solve_tree(mv, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
+                                 sm + lay.x, pair_tab, lane, s.act_lo, s.act_hi);
+    s.nfact = (nf < 0 || s.nfact < 0) ? -abs(s.nfact) - abs(nf) : s.nfact + nf;
+    stage_integrate(mv, lay, sm, lane);
+    s.need_fk = true;
   }
 }
 
@@ -207,8 +197,9 @@ __global__ void prep_kernel(const StageArgs a) {
   const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
   if (inst >= a.B) return;
   double* sm = smem + (size_t)warp * a.lay.total;
-  const DevModel& M = a.models[a.model_of ? a.model_of[inst] : 0];
-  stage_prep<TIn>(M, a.lay, sm, (const TIn*)a.human + (size_t)inst * a.human_inst_stride,
+  ModelView<false> mv{a.models + (a.model_of ? a.model_of[inst] : 0), nullptr};
+  const DevModel& M = mv.M();
+  stage_prep<TIn>(mv, a.lay, sm, (const TIn*)a.human + (size_t)inst * a.human_inst_stride,
                   a.scale + (size_t)inst * a.s_max, a.to_ground != 0, lane);
   double* so = a.scaled_out + (size_t)inst * a.s_max * 7;
   for (int i = lane; i < M.n_scaled * 7; i += 32) so[i] = sm[a.lay.scaled + i];
@@ -220,10 +211,11 @@ __global__ void fk_kernel(const StageArgs a) {
   const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
   if (inst >= a.B) return;
   double* sm = smem + (size_t)warp * a.lay.total;
-  const DevModel& M = a.models[a.model_of ? a.model_of[inst] : 0];
+  ModelView<false> mv{a.models + (a.model_of ? a.model_of[inst] : 0), nullptr};
+  const DevModel& M = mv.M();
   for (int i = lane; i < M.nq; i += 32) sm[a.lay.q + i] = a.q[(size_t)inst * a.nq_max + i];
   __syncwarp();
-  stage_fk(M, a.lay, sm, lane);
+  stage_fk(mv, a.lay, sm, lane);
   for (int i = lane; i < M.nbody * 3; i += 32) a.xpos_out[(size_t)inst * a.nbody_max * 3 + i] = sm[a.lay.xpos + i];
   for (int i = lane; i < M.nbody * 4; i += 32) a.xquat_out[(size_t)inst * a.nbody_max * 4 + i] = sm[a.lay.xquat + i];
 }
@@ -235,20 +227,21 @@ __global__ void build_qp_kernel(const StageArgs a) {
   if (inst >= a.B) return;
   const Lay& lay = a.lay;
   double* sm = smem + (size_t)warp * lay.total;
-  const DevModel& M = a.models[a.model_of ? a.model_of[inst] : 0];
+  ModelView<false> mv{a.models + (a.model_of ? a.model_of[inst] : 0), nullptr};
+  const DevModel& M = mv.M();
   for (int i = lane; i < M.nq; i += 32) sm[lay.q + i] = a.q[(size_t)inst * a.nq_max + i];
   for (int i = lane; i < M.n_scaled * 7; i += 32) sm[lay.scaled + i] = a.scaled[(size_t)inst * a.s_max * 7 + i];
   __syncwarp();
-  stage_fk(M, lay, sm, lane);
-  stage_errors(M, lay, sm, a.stage, lane);
-  const double mu = stage_stiffness(M, lay, sm, a.stage, lane);
-  stage_assemble(M, lay, sm, a.stage, mu, lane);
+  stage_fk(mv, lay, sm, lane);
+  stage_errors(mv, lay, sm, a.stage, lane);
+  const double mu = stage_stiffness(mv, lay, sm, a.stage, lane);
+  stage_assemble(mv, lay, sm, a.stage, mu, lane);
   const int n = M.nv, m = M.n_task[a.stage];
   if (a.e_out) for (int i = lane; i < 6 * m; i += 32) a.e_out[(size_t)inst * a.m_max * 6 + i] = sm[lay.e + i];
   double* Ho = a.H_out + (size_t)inst * a.nv_max * a.nv_max;
   for (int idx = lane; idx < n * n; idx += 32) {
     const int i = idx / n, j = idx % n;
-    Ho[i * a.nv_max + j] = tree_at(M, sm + lay.H, i, j);
+    Ho[i * a.nv_max + j] = tree_at(mv, sm + lay.H, i, j);
   }
   for (int i = lane; i < n; i += 32) {
     a.c_out[(size_t)inst * a.nv_max + i] = sm[lay.c + i];
@@ -268,16 +261,17 @@ __global__ void solve_ik_kernel(const StageArgs a) {
   if (inst >= a.B) return;
   const Lay& lay = a.lay;
   double* sm = smem + (size_t)warp * lay.total;
-  const DevModel& M = a.models[a.model_of ? a.model_of[inst] : 0];
+  ModelView<false> mv{a.models + (a.model_of ? a.model_of[inst] : 0), nullptr};
+  const DevModel& M = mv.M();
   for (int i = lane; i < M.nq; i += 32) sm[lay.q + i] = a.q[(size_t)inst * a.nq_max + i];
   for (int i = lane; i < M.n_scaled * 7; i += 32) sm[lay.scaled + i] = a.scaled[(size_t)inst * a.s_max * 7 + i];
   __syncwarp();
-  stage_fk(M, lay, sm, lane);
-  stage_errors(M, lay, sm, a.stage, lane);
-  const double mu = stage_stiffness(M, lay, sm, a.stage, lane);
-  stage_assemble(M, lay, sm, a.stage, mu, lane);
+  stage_fk(mv, lay, sm, lane);
+  stage_errors(mv, lay, sm, a.stage, lane);
+  const double mu = stage_stiffness(mv, lay, sm, a.stage, lane);
+  stage_assemble(mv, lay, sm, a.stage, mu, lane);
   unsigned long long act_lo = 0, act_hi = 0;
-  const int nf = qp_solve_tree(M, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
+  const int nf = qp_solve_tree(mv, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
                                sm + lay.x, pair_tab, lane, act_lo, act_hi);
   for (int i = lane; i < M.nv; i += 32) a.dq_out[(size_t)inst * a.nv_max + i] = sm[lay.x + i];
   if (lane == 0 && a.nfact_out) a.nfact_out[inst] = nf;

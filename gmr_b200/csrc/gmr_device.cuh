@@ -20,6 +20,8 @@ enum : int { DOF_FREE_T = 0, DOF_FREE_R = 1, DOF_SLIDE = 2, DOF_HINGE = 3 };
 // Kinematic tree replaces mj.MjModel (motion_retarget.py:27); task tables replace the
 // FrameTask lists (:78-114); prep tables replace pos/rot_offsets1 + human_scale_table.
 struct DevModel {
+  const char* blob;          // the one device allocation every table pointer below points into
+  int blob_bytes;
   int nbody, njnt, nq, nv, n_human, n_scaled, nlevel, ref_body;
   int use[2], n_task[2];
   int max_iter;
@@ -42,6 +44,7 @@ struct DevModel {
   const int* dof_kind;       // [nv]
   const int* dof_qadr;       // [nv] qpos index (free rot dofs: index of the quaternion w)
   const int* dof_parent;     // [nv] parent dof in the kinematic tree, -1 at the top
+  const int* dof_body;       // [nv] body that owns the dof's joint
   const int* dof_limited;    // [nv]
   const double* dof_lo;      // [nv] joint range lower
   const double* dof_hi;      // [nv]
@@ -69,10 +72,27 @@ struct DevModel {
   const double* task_wrot;
 };
 
+// Table access of the kernels.  SM = true: the CTA staged the model blob into shared memory at
+// `sblob` (single-model batches); a table pointer is rebased into that copy, and because `sblob`
+// derives from the kernel's __shared__ array the compiler emits LDS with 32-bit addresses.
+// SM = false (heterogeneous launches, stage kernels): the tables are read from global memory.
+template <bool SM>
+struct ModelView {
+  const DevModel* m;
+  const char* sblob;
+  __device__ __forceinline__ const DevModel& M() const { return *m; }
+  template <typename T>
+  __device__ __forceinline__ const T* operator()(const T* g) const {
+    if (SM) return (const T*)(sblob + ((const char*)g - m->blob));
+    return g;
+  }
+};
+
 // Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
 struct Lay {
   int q, scaled, c, x, lo, hi, rv, H;     // persistent across the QP solve (H: nnz packed tree rows)
   int xpos, xquat, S, e, K, g;            // kinematics / assembly scratch ...
+  int tl, ql;                             // FK local transforms (alias K/g: dead before the stiffness pass)
   int L, lrow;                            // ... overlaid by the factor (nnz) + one row (32) during the solve
   int total;                              // doubles per warp
   int maxt;                               // stride of the stage-major task tables

@@ -5,12 +5,16 @@
 //   stage_errors    Kernel 2  FrameTask.compute_error         motion_retarget.py:188-200
 //   stage_stiffness Kernel 2  FrameTask.compute_jacobian, folded into a 6x6 stiffness
 //   stage_assemble  Kernel 3  mink build_ik: H, c, box
-//   qp_solve        Kernel 3  exact box QP (stands in for daqp)
+//   qp_solve_tree   Kernel 3  exact box QP on the kinematic tree (stands in for daqp)
 //   stage_integrate Kernel 4  mj_integratePos
 // Kernel 4's convergence control lives in gmr_clip.cuh.
 //
-// Every function is called by all 32 lanes of the owning warp with warp-uniform
-// arguments; `sm` is the warp's private shared-memory block laid out by `Lay`.
+// Every function is called by all 32 lanes of the owning warp with warp-uniform arguments; `sm` is
+// the warp's private shared-memory block laid out by `Lay`; `mv` gives the model tables (staged in
+// shared memory or read from global memory, see ModelView).  Everything is force-inlined into ONE
+// call site per stage of the tick loop, so that the compiler sees every pointer derive from the
+// kernel's __shared__ array (LDS/STS with 32-bit addresses) and the instruction stream holds one
+// copy of each stage.
 #pragma once
 #include "gmr_device.cuh"
 
@@ -21,13 +25,14 @@ namespace gmr {
 // ------------------------------------------------------------------ Kernel 1: target preparation
 // lane i < s handles scaled body i (entry 0 = human root).  Reads one frame of the human
 // stream (7 numbers per body, float or double), writes sm[scaled + 7*i .. +7] = pos, quat wxyz.
-template <typename TIn>
-__device__ __forceinline__ void stage_prep(const DevModel& M, const Lay& lay, double* sm, const TIn* frame,
+template <typename TIn, class MV>
+__device__ __forceinline__ void stage_prep(const MV& mv, const Lay& lay, double* sm, const TIn* frame,
                                            const double* scale, bool to_ground, int lane) {
+  const DevModel& M = mv.M();
   const int s = M.n_scaled;
   double p[3] = {0, 0, 0}, q[4] = {1, 0, 0, 0};
   if (lane < s) {
-    const TIn* b = frame + 7 * __ldg(M.scaled_index + lane);
+    const TIn* b = frame + 7 * mv(M.scaled_index)[lane];
     p[0] = (double)b[0]; p[1] = (double)b[1]; p[2] = (double)b[2];
     q[0] = (double)b[3]; q[1] = (double)b[4]; q[2] = (double)b[5]; q[3] = (double)b[6];
   }
@@ -42,18 +47,20 @@ __device__ __forceinline__ void stage_prep(const DevModel& M, const Lay& lay, do
     // scipy Rotation normalises on from_quat and the product is unit again
     double n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
     q[0] /= n; q[1] /= n; q[2] /= n; q[3] /= n;
-    double ro[4] = {__ldg(M.rot_off + 4 * lane), __ldg(M.rot_off + 4 * lane + 1), __ldg(M.rot_off + 4 * lane + 2), __ldg(M.rot_off + 4 * lane + 3)};
+    const double* rop = mv(M.rot_off) + 4 * lane;
+    double ro[4] = {rop[0], rop[1], rop[2], rop[3]};
     double uq[4];
     qmul(q, ro, uq);
     n = sqrt(uq[0] * uq[0] + uq[1] * uq[1] + uq[2] * uq[2] + uq[3] * uq[3]);
     uq[0] /= n; uq[1] /= n; uq[2] /= n; uq[3] /= n;
-    double po[3] = {__ldg(M.pos_off + 3 * lane), __ldg(M.pos_off + 3 * lane + 1), __ldg(M.pos_off + 3 * lane + 2)}, off[3];
+    const double* pop = mv(M.pos_off) + 3 * lane;
+    double po[3] = {pop[0], pop[1], pop[2]}, off[3];
     qrot(uq, po, off);
     out[0] = pos[0] + off[0]; out[1] = pos[1] + off[1]; out[2] = pos[2] + off[2];
     out[3] = uq[0]; out[4] = uq[1]; out[5] = uq[2]; out[6] = uq[3];
   }
   if (to_ground) {   // motion_retarget.py:252-270
-    double z = (lane < s && __ldg(M.is_foot + lane)) ? out[2] : INFINITY;
+    double z = (lane < s && mv(M.is_foot)[lane]) ? out[2] : INFINITY;
     double lowest = warp_min(z);
     out[2] = out[2] - lowest + 0.1;
   }
@@ -66,77 +73,119 @@ __device__ __forceinline__ void stage_prep(const DevModel& M, const Lay& lay, do
 }
 
 // ------------------------------------------------------------------ Kernel 2: forward kinematics
-// Level-synchronous mj_kinematics: bodies of one depth in parallel (one lane each), levels in
-// sequence.  Also writes the spatial axis S[dof] = (v_O, w): twist of the dof expressed at the
-// reference point O = origin of the floating base (world origin if there is none), so that the
-// geometric Jacobian column of ANY descendant frame at x is [v_O + w x (x - O); w].
-__device__ __noinline__ void stage_fk(const DevModel& M, const Lay& lay, double* sm, int lane) {
+// mj_kinematics in three passes:
+//   A (lane = body, all bodies at once): the body's LOCAL transform, joints included -
+//       tl = body_pos + R(body_quat) sum(slide axis * value),  ql = body_quat (x) prod(hinge rotations),
+//       and each joint axis expressed in the PARENT frame (al, parked in S[6k+3..5]);
+//   B (levels in sequence, lane = body of the level): x = x_p + R(Q_p) tl,  Q = normalize(Q_p (x) ql)
+//       - the only sequential part, ~60 flops per level;
+//   C (lane = dof): spatial axis S_k = (v_O, w): twist of the dof expressed at the reference point O =
+//       origin of the floating base (world origin if there is none), so that the geometric Jacobian
+//       column of ANY descendant frame at x is [v_O + w x (x - O); w].
+// Joint anchors are the body origin (jnt_pos = 0, checked at model creation) and slides precede
+// hinges inside a body, which is what makes the local transform independent of the parent.
+template <class MV>
+__device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* sm, int lane) {
+  const DevModel& M = mv.M();
   const double* q = sm + lay.q;
   double* xpos = sm + lay.xpos;
   double* xquat = sm + lay.xquat;
   double* S = sm + lay.S;
-  if (lane == 0) { xpos[0] = xpos[1] = xpos[2] = 0; xquat[0] = 1; xquat[1] = xquat[2] = xquat[3] = 0; }
+  double* tl = sm + lay.tl;
+  double* ql = sm + lay.ql;
+  const int nb = M.nbody;
+  // ---- pass A
+  for (int b = lane; b < nb; b += 32) {
+    if (b == 0) { xpos[0] = xpos[1] = xpos[2] = 0; xquat[0] = 1; xquat[1] = xquat[2] = xquat[3] = 0; continue; }
+    const int jadr = mv(M.body_jntadr)[b], jnum = mv(M.body_jntnum)[b];
+    if (jnum == 1 && mv(M.jnt_type)[jadr] == 0) continue;              // free joint: pose comes from q in pass B
+    const double* bpp = mv(M.body_pos) + 3 * b;
+    const double* bqp = mv(M.body_quat) + 4 * b;
+    double t[3] = {bpp[0], bpp[1], bpp[2]}, qq[4] = {bqp[0], bqp[1], bqp[2], bqp[3]};
+    for (int j = jadr; j < jadr + jnum; j++) {
+      const int qa = mv(M.jnt_qposadr)[j], da = mv(M.jnt_dofadr)[j];
+      const double* axp = mv(M.jnt_axis) + 3 * j;
+      const double ax[3] = {axp[0], axp[1], axp[2]};
+      double al[3];
+      qrot(qq, ax, al);                                                 // axis in the parent frame
+      S[6 * da + 3] = al[0]; S[6 * da + 4] = al[1]; S[6 * da + 5] = al[2];
+      const double val = q[qa] - mv(M.qpos0)[qa];
+      if (mv(M.jnt_type)[j] == 2) {                                     // slide
+        t[0] += al[0] * val; t[1] += al[1] * val; t[2] += al[2] * val;
+      } else {                                                          // hinge about the body origin
+        double sh, ch;
+        sincos(0.5 * val, &sh, &ch);
+        const double qj[4] = {ch, sh * ax[0], sh * ax[1], sh * ax[2]};
+        double nq[4];
+        qmul(qq, qj, nq);
+        qq[0] = nq[0]; qq[1] = nq[1]; qq[2] = nq[2]; qq[3] = nq[3];
+      }
+    }
+    tl[3 * b] = t[0]; tl[3 * b + 1] = t[1]; tl[3 * b + 2] = t[2];
+    ql[4 * b] = qq[0]; ql[4 * b + 1] = qq[1]; ql[4 * b + 2] = qq[2]; ql[4 * b + 3] = qq[3];
+  }
   __syncwarp();
-  const int ref = M.ref_body;
+  // ---- pass B
+  const int* level_start = mv(M.level_start);
+  const int* level_body = mv(M.level_body);
   for (int lv = 0; lv < M.nlevel; lv++) {
-    const int beg = __ldg(M.level_start + lv), end = __ldg(M.level_start + lv + 1);
+    const int beg = level_start[lv], end = level_start[lv + 1];
     for (int idx = beg + lane; idx < end; idx += 32) {
-      const int b = __ldg(M.level_body + idx);
-      const int jadr = __ldg(M.body_jntadr + b), jnum = __ldg(M.body_jntnum + b);
+      const int b = level_body[idx];
+      const int jadr = mv(M.body_jntadr)[b];
       double pos[3], quat[4];
-      if (jnum == 1 && __ldg(M.jnt_type + jadr) == 0) {   // free joint
-        const int qa = __ldg(M.jnt_qposadr + jadr), da = __ldg(M.jnt_dofadr + jadr);
+      if (mv(M.body_jntnum)[b] == 1 && mv(M.jnt_type)[jadr] == 0) {    // free joint
+        const int qa = mv(M.jnt_qposadr)[jadr];
         pos[0] = q[qa]; pos[1] = q[qa + 1]; pos[2] = q[qa + 2];
         quat[0] = q[qa + 3]; quat[1] = q[qa + 4]; quat[2] = q[qa + 5]; quat[3] = q[qa + 6];
-        normalize4(quat);
-        double R[9];
-        q2mat(quat, R);
-#pragma unroll
-        for (int i = 0; i < 3; i++) {
-          double* st = S + 6 * (da + i);
-          st[0] = (i == 0); st[1] = (i == 1); st[2] = (i == 2); st[3] = st[4] = st[5] = 0;
-          double* sr = S + 6 * (da + 3 + i);
-          // O = this body's origin -> v_O = 0
-          sr[0] = sr[1] = sr[2] = 0; sr[3] = R[i]; sr[4] = R[3 + i]; sr[5] = R[6 + i];
-        }
       } else {
-        const int p = __ldg(M.body_parent + b);
-        double pq[4] = {xquat[4 * p], xquat[4 * p + 1], xquat[4 * p + 2], xquat[4 * p + 3]};
-        double bp[3] = {__ldg(M.body_pos + 3 * b), __ldg(M.body_pos + 3 * b + 1), __ldg(M.body_pos + 3 * b + 2)};
-        double bq[4] = {__ldg(M.body_quat + 4 * b), __ldg(M.body_quat + 4 * b + 1), __ldg(M.body_quat + 4 * b + 2), __ldg(M.body_quat + 4 * b + 3)};
+        const int p = mv(M.body_parent)[b];
+        const double pq[4] = {xquat[4 * p], xquat[4 * p + 1], xquat[4 * p + 2], xquat[4 * p + 3]};
+        const double lt[3] = {tl[3 * b], tl[3 * b + 1], tl[3 * b + 2]};
+        const double lq[4] = {ql[4 * b], ql[4 * b + 1], ql[4 * b + 2], ql[4 * b + 3]};
         double t[3];
-        qrot(pq, bp, t);
+        qrot(pq, lt, t);
         pos[0] = xpos[3 * p] + t[0]; pos[1] = xpos[3 * p + 1] + t[1]; pos[2] = xpos[3 * p + 2] + t[2];
-        qmul(pq, bq, quat);
-        double O[3] = {0, 0, 0};
-        if (jnum > 0 && ref > 0) { O[0] = xpos[3 * ref]; O[1] = xpos[3 * ref + 1]; O[2] = xpos[3 * ref + 2]; }
-        for (int j = jadr; j < jadr + jnum; j++) {
-          const int qa = __ldg(M.jnt_qposadr + j), da = __ldg(M.jnt_dofadr + j);
-          double ax[3] = {__ldg(M.jnt_axis + 3 * j), __ldg(M.jnt_axis + 3 * j + 1), __ldg(M.jnt_axis + 3 * j + 2)}, aw[3];
-          qrot(quat, ax, aw);
-          const double val = q[qa] - __ldg(M.qpos0 + qa);
-          double* sd = S + 6 * da;
-          if (__ldg(M.jnt_type + j) == 2) {   // slide
-            sd[0] = aw[0]; sd[1] = aw[1]; sd[2] = aw[2]; sd[3] = sd[4] = sd[5] = 0;
-            pos[0] += aw[0] * val; pos[1] += aw[1] * val; pos[2] += aw[2] * val;
-          } else {                            // hinge, anchor = body origin (jnt_pos = 0)
-            double r[3] = {O[0] - pos[0], O[1] - pos[1], O[2] - pos[2]}, v[3];
-            cross3(aw, r, v);
-            sd[0] = v[0]; sd[1] = v[1]; sd[2] = v[2]; sd[3] = aw[0]; sd[4] = aw[1]; sd[5] = aw[2];
-            double sh, ch;
-            sincos(0.5 * val, &sh, &ch);
-            double ql[4] = {ch, sh * ax[0], sh * ax[1], sh * ax[2]}, nq[4];
-            qmul(quat, ql, nq);
-            quat[0] = nq[0]; quat[1] = nq[1]; quat[2] = nq[2]; quat[3] = nq[3];
-          }
-        }
-        normalize4(quat);
+        qmul(pq, lq, quat);
       }
+      normalize4(quat);
       xpos[3 * b] = pos[0]; xpos[3 * b + 1] = pos[1]; xpos[3 * b + 2] = pos[2];
       xquat[4 * b] = quat[0]; xquat[4 * b + 1] = quat[1]; xquat[4 * b + 2] = quat[2]; xquat[4 * b + 3] = quat[3];
     }
     __syncwarp();
   }
+  // ---- pass C
+  const int ref = M.ref_body;
+  const double O[3] = {xpos[3 * ref], xpos[3 * ref + 1], xpos[3 * ref + 2]};    // world (body 0) has xpos = 0
+  for (int k = lane; k < M.nv; k += 32) {
+    const int kind = mv(M.dof_kind)[k], b = mv(M.dof_body)[k];
+    double* sk = S + 6 * k;
+    if (kind == DOF_FREE_T) {
+      const int i = k - mv(M.jnt_dofadr)[mv(M.body_jntadr)[b]];
+      sk[0] = (i == 0); sk[1] = (i == 1); sk[2] = (i == 2); sk[3] = sk[4] = sk[5] = 0;
+    } else {
+      double aw[3];
+      if (kind == DOF_FREE_R) {
+        const int i = k - mv(M.jnt_dofadr)[mv(M.body_jntadr)[b]] - 3;
+        double R[9];
+        q2mat(xquat + 4 * b, R);
+        aw[0] = R[i]; aw[1] = R[3 + i]; aw[2] = R[6 + i];
+      } else {
+        const int p = mv(M.body_parent)[b];
+        const double al[3] = {sk[3], sk[4], sk[5]};
+        qrot(xquat + 4 * p, al, aw);
+      }
+      if (kind == DOF_SLIDE) {
+        sk[0] = aw[0]; sk[1] = aw[1]; sk[2] = aw[2]; sk[3] = sk[4] = sk[5] = 0;
+      } else {                                                          // rotation about the body origin
+        const double r[3] = {O[0] - xpos[3 * b], O[1] - xpos[3 * b + 1], O[2] - xpos[3 * b + 2]};
+        double v[3];
+        cross3(aw, r, v);
+        sk[0] = v[0]; sk[1] = v[1]; sk[2] = v[2]; sk[3] = aw[0]; sk[4] = aw[1]; sk[5] = aw[2];
+      }
+    }
+  }
+  __syncwarp();
 }
 
 // ------------------------------------------------------------------ mink SO3/SE3 log
@@ -168,12 +217,14 @@ __device__ __forceinline__ void se3_log_dev(const double* q, const double* p, do
 // ------------------------------------------------------------------ Kernel 2: task errors
 // lane t < m: e_t = log(T_b^-1 T_t) -> sm[e + 6t]; returns ||concat e|| (unweighted, :188-200),
 // bitwise identical on all lanes.
-__device__ __noinline__ double stage_errors(const DevModel& M, const Lay& lay, double* sm, int stage, int lane) {
+template <class MV>
+__device__ __forceinline__ double stage_errors(const MV& mv, const Lay& lay, double* sm, int stage, int lane) {
+  const DevModel& M = mv.M();
   const int m = M.n_task[stage];
   double ss = 0;
   if (lane < m) {
-    const int body = __ldg(M.task_body + stage * lay.maxt + lane);
-    const double* tgt = sm + lay.scaled + 7 * __ldg(M.task_src + stage * lay.maxt + lane);
+    const int body = mv(M.task_body)[stage * lay.maxt + lane];
+    const double* tgt = sm + lay.scaled + 7 * mv(M.task_src)[stage * lay.maxt + lane];
     const double* xp = sm + lay.xpos + 3 * body;
     const double* xq = sm + lay.xquat + 4 * body;
     double qi[4] = {xq[0], -xq[1], -xq[2], -xq[3]}, qbt[4], d[3] = {tgt[0] - xp[0], tgt[1] - xp[1], tgt[2] - xp[2]}, pbt[3], e[6];
@@ -198,12 +249,14 @@ __device__ __noinline__ double stage_errors(const DevModel& M, const Lay& lay, d
 // where Jl^-1(e) = [[Ji, B],[0, Ji]].  Lane t stores K_t = N_t^T N_t (21 packed) and
 // g_t = N_t^T W e_t (6); the assembly then needs only S_k^T (sum K_t) S_l - no 6 x nv Jacobian.
 // Returns sum_t mu_t = sum_t ||W e_t||^2 (all lanes).
-__device__ __noinline__ double stage_stiffness(const DevModel& M, const Lay& lay, double* sm, int stage, int lane) {
+template <class MV>
+__device__ __forceinline__ double stage_stiffness(const MV& mv, const Lay& lay, double* sm, int stage, int lane) {
+  const DevModel& M = mv.M();
   const int m = M.n_task[stage];
   double mu = 0;
   if (lane < m) {
-    const int body = __ldg(M.task_body + stage * lay.maxt + lane);
-    const double wp = __ldg(M.task_wpos + stage * lay.maxt + lane), wr = __ldg(M.task_wrot + stage * lay.maxt + lane);
+    const int body = mv(M.task_body)[stage * lay.maxt + lane];
+    const double wp = mv(M.task_wpos)[stage * lay.maxt + lane], wr = mv(M.task_wrot)[stage * lay.maxt + lane];
     const double a = wp * wp, b = wr * wr;
     const double* e = sm + lay.e + 6 * lane;
     const double ev[3] = {e[0], e[1], e[2]}, w[3] = {e[3], e[4], e[5]};
@@ -298,13 +351,15 @@ __device__ __noinline__ double stage_stiffness(const DevModel& M, const Lay& lay
 // lane l = dof l:  Kc = sum of K_t over tasks in the subtree of dof l,  F = Kc S_l,
 // H(l,k) = S_k . F for every ancestor-or-self k of l (all other entries are structurally 0 and not stored),
 // c[l] = S_l . sum g_t.  diag += damping + lm_damping * sum mu.  Also the ConfigurationLimit box.
-__device__ __noinline__ void stage_assemble(const DevModel& M, const Lay& lay, double* sm, int stage, double mu_sum, int lane) {
+template <class MV>
+__device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, double* sm, int stage, double mu_sum, int lane) {
+  const DevModel& M = mv.M();
   const int n = M.nv;
   double* H = sm + lay.H;
   const double diag = M.damping + M.lm_damping * mu_sum;
   const double* q = sm + lay.q;
   for (int l = lane; l < n; l += 32) {
-    unsigned mask = __ldg(M.dof_taskmask + stage * n + l);
+    unsigned mask = mv(M.dof_taskmask)[stage * n + l];
     double Kc[21], gc[6];
 #pragma unroll
     for (int i = 0; i < 21; i++) Kc[i] = 0;
@@ -335,10 +390,10 @@ __device__ __noinline__ void stage_assemble(const DevModel& M, const Lay& lay, d
 #pragma unroll
     for (int i = 0; i < 6; i++) cl += s[i] * gc[i];
     sm[lay.c + l] = cl;
-    const int dl = M.dof_depth[l], rp = M.dof_rowptr[l];
+    const int dl = mv(M.dof_depth)[l], rp = mv(M.dof_rowptr)[l];
 #pragma unroll 1
     for (int a2 = 0; a2 <= dl; a2++) {                       // tree row l: its ancestors top-down, then itself
-      const double* Sk = sm + lay.S + 6 * M.dof_anc[rp + a2];
+      const double* Sk = sm + lay.S + 6 * mv(M.dof_anc)[rp + a2];
       double h = 0;
 #pragma unroll
       for (int i = 0; i < 6; i++) h += Sk[i] * F[i];
@@ -346,10 +401,10 @@ __device__ __noinline__ void stage_assemble(const DevModel& M, const Lay& lay, d
     }
     // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs
     double lo = -INFINITY, hi = INFINITY;
-    if (__ldg(M.dof_limited + l)) {
-      const double qv = q[__ldg(M.dof_qadr + l)];
-      hi = M.limit_gain * (__ldg(M.dof_hi + l) - qv);
-      lo = -M.limit_gain * (qv - __ldg(M.dof_lo + l));
+    if (mv(M.dof_limited)[l]) {
+      const double qv = q[mv(M.dof_qadr)[l]];
+      hi = M.limit_gain * (mv(M.dof_hi)[l] - qv);
+      lo = -M.limit_gain * (qv - mv(M.dof_lo)[l]);
     }
     sm[lay.lo + l] = lo;
     sm[lay.hi + l] = hi;
@@ -540,25 +595,33 @@ __device__ __forceinline__ void fill_pair_tab(unsigned short* pair_tab) {
 }
 
 // H(i,j) of the tree layout (0 if neither dof is an ancestor of the other)
-__device__ __forceinline__ double tree_at(const DevModel& M, const double* H, int i, int j) {
-  const int di = M.dof_depth[i], dj = M.dof_depth[j];
-  if (dj <= di) { const int e = M.dof_rowptr[i] + dj; return M.dof_anc[e] == j ? H[e] : 0.0; }
-  const int e = M.dof_rowptr[j] + di;
-  return M.dof_anc[e] == i ? H[e] : 0.0;
+template <class MV>
+__device__ __forceinline__ double tree_at(const MV& mv, const double* H, int i, int j) {
+  const DevModel& M = mv.M();
+  const int di = mv(M.dof_depth)[i], dj = mv(M.dof_depth)[j];
+  if (dj <= di) { const int e = mv(M.dof_rowptr)[i] + dj; return mv(M.dof_anc)[e] == j ? H[e] : 0.0; }
+  const int e = mv(M.dof_rowptr)[j] + di;
+  return mv(M.dof_anc)[e] == i ? H[e] : 0.0;
 }
 
-__device__ __noinline__ int qp_solve_tree(const DevModel& M, const double* __restrict__ H, const double* __restrict__ c,
+template <class MV>
+__device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restrict__ H, const double* __restrict__ c,
                                           const double* __restrict__ lo, const double* __restrict__ hi,
                                           double* __restrict__ W, double* __restrict__ lrow, double* __restrict__ rv,
                                           double* __restrict__ x, const unsigned short* __restrict__ pair_tab, int lane,
                                           unsigned long long& act_lo, unsigned long long& act_hi) {
+  const DevModel& M = mv.M();
   const int n = M.nv, nnz = M.nnz;
+  const short* anc = mv(M.dof_anc);
+  const short* ancrow = mv(M.dof_ancrow);
+  const int* depth = mv(M.dof_depth);
+  const int* rowptr = mv(M.dof_rowptr);
   const int i0 = lane, i1 = lane + 32;
   const bool has0 = i0 < n, has1 = i1 < n, two = n > 32;
   const double lo0 = has0 ? lo[i0] : 0, hi0 = has0 ? hi[i0] : 0, lo1 = has1 ? lo[i1] : 0, hi1 = has1 ? hi[i1] : 0;
   const double c0 = has0 ? c[i0] : 0, c1 = has1 ? c[i1] : 0;
-  const int d0 = has0 ? M.dof_depth[i0] : -1, d1 = has1 ? M.dof_depth[i1] : -1;
-  const int rp0 = has0 ? M.dof_rowptr[i0] : 0, rp1 = has1 ? M.dof_rowptr[i1] : 0;
+  const int d0 = has0 ? depth[i0] : -1, d1 = has1 ? depth[i1] : -1;
+  const int rp0 = has0 ? rowptr[i0] : 0, rp1 = has1 ? rowptr[i1] : 0;
   int st0 = 0, st1 = 0;      // 0 free, -1 at lower, +1 at upper; a seed is only honoured where the bound is finite
   if (has0) st0 = ((act_lo >> i0) & 1ull) && lo0 > -INFINITY ? -1 : (((act_hi >> i0) & 1ull) && hi0 < INFINITY ? 1 : 0);
   if (has1) st1 = ((act_lo >> i1) & 1ull) && lo1 > -INFINITY ? -1 : (((act_hi >> i1) & 1ull) && hi1 < INFINITY ? 1 : 0);
@@ -577,8 +640,8 @@ __device__ __noinline__ int qp_solve_tree(const DevModel& M, const double* __res
       for (unsigned long long mk = act; mk; mk &= mk - 1) {
         const int j = __ffsll((long long)mk) - 1;
         const double xj = __shfl_sync(GMR_FULL, j < 32 ? xa0 : xa1, j & 31);
-        if (has0 && !st0) r0 -= tree_at(M, H, i0, j) * xj;
-        if (has1 && !st1) r1 -= tree_at(M, H, i1, j) * xj;
+        if (has0 && !st0) r0 -= tree_at(mv, H, i0, j) * xj;
+        if (has1 && !st1) r1 -= tree_at(mv, H, i1, j) * xj;
       }
     }
     if (has0) rv[i0] = r0;
@@ -588,7 +651,7 @@ __device__ __noinline__ int qp_solve_tree(const DevModel& M, const double* __res
     // ---- L'L factorisation, leaves to root
 #pragma unroll 1
     for (int i = n - 1; i >= 0; i--) {
-      const int d = M.dof_depth[i], rp = M.dof_rowptr[i];
+      const int d = depth[i], rp = rowptr[i];
       double* Wi = W + rp;
       if ((act >> i) & 1ull) {                        // warp-uniform: identity row
         if (lane <= d) Wi[lane] = (lane == d) ? 1.0 : 0.0;
@@ -600,7 +663,7 @@ __device__ __noinline__ int qp_solve_tree(const DevModel& M, const double* __res
       if (!(piv > 0.0)) { spd = false; piv = 1.0; }
       const double inv = rsqrt(piv);
       if (lane <= d) {
-        const int col = M.dof_anc[rp + lane];
+        const int col = anc[rp + lane];
         const double l = (lane == d) ? inv : (((act >> col) & 1ull) ? 0.0 : w * inv);
         Wi[lane] = l;                                  // diagonal stores 1/L_ii
         lrow[lane] = l;
@@ -610,7 +673,7 @@ __device__ __noinline__ int qp_solve_tree(const DevModel& M, const double* __res
 #pragma unroll 1
       for (int q = lane; q < P; q += 32) {
         const int ab = pair_tab[q], a = ab & 0xff, b = ab >> 8;
-        double* t = W + M.dof_ancrow[rp + a] + b;
+        double* t = W + ancrow[rp + a] + b;
         *t -= lrow[a] * lrow[b];
       }
       __syncwarp();
@@ -619,10 +682,10 @@ __device__ __noinline__ int qp_solve_tree(const DevModel& M, const double* __res
     // ---- L' y = r
 #pragma unroll 1
     for (int i = n - 1; i >= 0; i--) {
-      const int d = M.dof_depth[i], rp = M.dof_rowptr[i];
+      const int d = depth[i], rp = rowptr[i];
       const double yi = rv[i] * W[rp + d];
       __syncwarp();
-      if (lane < d) rv[M.dof_anc[rp + lane]] -= W[rp + lane] * yi;
+      if (lane < d) rv[anc[rp + lane]] -= W[rp + lane] * yi;
       else if (lane == d) rv[i] = yi;
       __syncwarp();
     }
@@ -634,8 +697,8 @@ __device__ __noinline__ int qp_solve_tree(const DevModel& M, const double* __res
       if (d0 == a) { r0 *= W[rp0 + a]; rv[i0] = r0; }
       if (two && d1 == a) { r1 *= W[rp1 + a]; rv[i1] = r1; }
       __syncwarp();
-      if (d0 > a) r0 -= W[rp0 + a] * rv[M.dof_anc[rp0 + a]];
-      if (two && d1 > a) r1 -= W[rp1 + a] * rv[M.dof_anc[rp1 + a]];
+      if (d0 > a) r0 -= W[rp0 + a] * rv[anc[rp0 + a]];
+      if (two && d1 > a) r1 -= W[rp1 + a] * rv[anc[rp1 + a]];
     }
     // exact bounds on the active set (the solve reproduces them up to rounding)
     if (st0) r0 = xa0;
@@ -651,13 +714,13 @@ __device__ __noinline__ int qp_solve_tree(const DevModel& M, const double* __res
       if (has0 && st0) {
         double g = c0;
 #pragma unroll 1
-        for (int j = 0; j < n; j++) g += tree_at(M, H, i0, j) * x[j];
+        for (int j = 0; j < n; j++) g += tree_at(mv, H, i0, j) * x[j];
         bad0 = st0 < 0 ? (g < -QP_DTOL) : (g > QP_DTOL);
       }
       if (has1 && st1) {
         double g = c1;
 #pragma unroll 1
-        for (int j = 0; j < n; j++) g += tree_at(M, H, i1, j) * x[j];
+        for (int j = 0; j < n; j++) g += tree_at(mv, H, i1, j) * x[j];
         bad1 = st1 < 0 ? (g < -QP_DTOL) : (g > QP_DTOL);
       }
     }
@@ -682,12 +745,14 @@ __device__ __noinline__ int qp_solve_tree(const DevModel& M, const double* __res
 // ------------------------------------------------------------------ Kernel 4: integrate
 // solve_ik returns v = dq/dt and integrate_inplace applies q <- q (+) v dt (mj_integratePos);
 // the divide/multiply is kept so rounding follows the reference.
-__device__ __noinline__ void stage_integrate(const DevModel& M, const Lay& lay, double* sm, int lane) {
+template <class MV>
+__device__ __forceinline__ void stage_integrate(const MV& mv, const Lay& lay, double* sm, int lane) {
+  const DevModel& M = mv.M();
   double* q = sm + lay.q;
   const double* x = sm + lay.x;
   const double dt = M.timestep;
   for (int i = lane; i < M.nv; i += 32) {
-    const int kind = __ldg(M.dof_kind + i), qa = __ldg(M.dof_qadr + i);
+    const int kind = mv(M.dof_kind)[i], qa = mv(M.dof_qadr)[i];
     if (kind == DOF_FREE_R) {
       if (qa >= 0) {     // first rotational dof of the free joint updates the quaternion
         double w[3] = {x[i] / dt, x[i + 1] / dt, x[i + 2] / dt};
