@@ -11,7 +11,7 @@ import os
 from .abi import gmr_diag, gmr_model_desc
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libgmr_b200.so")
+LIB_PATH = os.environ.get("GMR_B200_LIB") or os.path.join(HERE, "libgmr_b200.so")
 
 EXPORTS = [
     "gmr_last_error", "gmr_abi_version", "gmr_model_create", "gmr_model_destroy", "gmr_batch_create",

@@ -333,17 +333,24 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, b->device);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device);
   if (e == cudaSuccess) {
-    size_t want = 4;
-    if (const char* ev = getenv("GMR_DEBUG_WARPS")) want = (size_t)std::max(1, atoi(ev));
+    // the fused kernel is compiled for 256 threads x 2 CTAs (128 registers): pick the CTA width
+    // (<= 8 warps) that puts the most warps on an SM; ties go to the narrower CTA
     const size_t blob = n_models == 1 ? (((size_t)models[0]->blob_bytes + 15) & ~size_t(15)) : 0;
-    const size_t fixed = 4096;      // static shared memory of the kernel (pair table, DevModel copy) + slack
+    const size_t fixed = 2048 + 1024;   // static shared memory of the kernel + the per-CTA reservation
+    const size_t sm_total = 228 * 1024;
     b->smem_model = n_models == 1 && per_warp + blob + fixed <= (size_t)dev_smem && !getenv("GMR_DEBUG_GLOBAL_MODEL");
-    const size_t avail = (size_t)dev_smem - fixed - (b->smem_model ? blob : 0);
-    b->warps_per_cta = (int)std::min<size_t>({want, avail / per_warp, (size_t)B});
-    if (b->warps_per_cta < 1) b->warps_per_cta = 1;
+    const size_t extra = fixed + (b->smem_model ? blob : 0);
+    int best_w = 1, best_total = 0;
+    for (int w = 1; w <= 8; w++) {
+      if ((size_t)w * per_warp + extra > (size_t)dev_smem + 1024) break;
+      int ctas = (int)std::min<size_t>(sm_total / ((size_t)w * per_warp + extra), (size_t)(16 / w));
+      if (ctas * w > best_total) { best_total = ctas * w; best_w = w; }
+    }
+    if (const char* ev = getenv("GMR_DEBUG_WARPS")) best_w = std::max(1, std::min(8, atoi(ev)));
+    b->warps_per_cta = std::min(best_w, B);
     b->smem_bytes = per_warp * b->warps_per_cta;
     b->clip_smem_bytes = b->smem_bytes + (b->smem_model ? blob : 0);
-    if (b->clip_smem_bytes + fixed > (size_t)dev_smem) e = cudaErrorInvalidConfiguration;
+    if (b->clip_smem_bytes + 2048 > (size_t)dev_smem) e = cudaErrorInvalidConfiguration;
   }
   const void* kf = b->smem_model ? (const void*)clip_kernel<float, true> : (const void*)clip_kernel<float, false>;
   const void* kd = b->smem_model ? (const void*)clip_kernel<double, true> : (const void*)clip_kernel<double, false>;
@@ -353,6 +360,7 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kf, 32 * b->warps_per_cta, b->clip_smem_bytes);
   if (e == cudaSuccess) {
     if (per_sm < 1) per_sm = 1;
+    if (const char* ev = getenv("GMR_DEBUG_CTAS_PER_SM")) per_sm = std::max(1, std::min(per_sm, atoi(ev)));
     const int need = (B + b->warps_per_cta - 1) / b->warps_per_cta;
     b->grid = std::min(need, per_sm * sms);
   }
@@ -468,6 +476,8 @@ static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const in
   a.counter = b->d_counter; a.order = b->d_order; a.B = b->B; a.lay = b->lay;
   a.sync_period = 2;
   if (const char* ev = getenv("GMR_DEBUG_SYNC_PERIOD")) a.sync_period = std::max(1, atoi(ev));
+  a.group_warps = 2;
+  if (const char* ev = getenv("GMR_DEBUG_GROUP_WARPS")) a.group_warps = std::max(1, atoi(ev));
   CU(cudaMemsetAsync(b->d_counter, 0, sizeof(int), b->stream));
   const dim3 grid(b->grid), block(32 * b->warps_per_cta);
   if (b->smem_model) {

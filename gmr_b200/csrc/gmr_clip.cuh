@@ -10,6 +10,11 @@
 
 namespace gmr {
 
+#ifndef GMR_MIN_CTAS
+#define GMR_MIN_CTAS 2
+#define GMR_CTA_THREADS 256
+#endif
+
 struct RunArgs {
   const DevModel* models;        // [n_models]
   const int* model_of;           // [B] or null (all 0)
@@ -31,7 +36,8 @@ struct RunArgs {
   int* counter;                  // work queue head
   const int* order;              // [B] or null
   int B;
-  int sync_period;               // CTA barrier at the top of every sync_period-th tick
+  int sync_period;               // lockstep-group barrier at the top of every sync_period-th tick
+  int group_warps;               // warps per lockstep group (named barrier 1 + group index)
   Lay lay;
 };
 
@@ -45,6 +51,14 @@ struct Slot {
   double curr;                   // curr_error of the reference loop
   unsigned long long act_lo, act_hi;   // active set of the previous solve of this frame/stage
 };
+
+// OR-reduction + barrier over one lockstep group of the CTA (named barrier `id`, `nthreads` threads)
+__device__ __forceinline__ bool group_barrier_or(int id, int nthreads, bool pred) {
+  int r;
+  asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.s32 q, %3, 0;\n\tbarrier.red.or.pred p, %1, %2, q;\n\tselp.s32 %0, 1, 0, p;\n\t}"
+               : "=r"(r) : "r"(id), "r"(nthreads), "r"((int)pred) : "memory");
+  return r != 0;
+}
 
 __device__ __forceinline__ int next_stage(const DevModel& M, int stage) {
   stage++;
@@ -61,7 +75,7 @@ __device__ __forceinline__ int next_stage(const DevModel& M, int stage) {
 // iteration its own instance is in, and each stage function has exactly one call site.
 // SM = true: single-model batch, model tables staged in shared memory.
 template <typename TIn, bool SM>
-__global__ void __launch_bounds__(128, 3) clip_kernel(const RunArgs a) {
+__global__ void __launch_bounds__(GMR_CTA_THREADS, GMR_MIN_CTAS) clip_kernel(const RunArgs a) {
   extern __shared__ double smem[];
   __shared__ unsigned short pair_tab[PAIR_TAB_SIZE];
   __shared__ DevModel smodel;
@@ -90,6 +104,10 @@ __global__ void __launch_bounds__(128, 3) clip_kernel(const RunArgs a) {
   s.new_frame = s.fresh = s.need_fk = false;
   bool drained = false;
   int tick = 0;
+  // lockstep group: `group_warps` consecutive warps re-converge every sync_period ticks so that they
+  // walk the instruction stream together; groups (and CTAs) drift freely against each other
+  const int nwarps = blockDim.x >> 5, grp = warp / a.group_warps;
+  const int grp_threads = 32 * min(a.group_warps, nwarps - grp * a.group_warps);
   for (;;) {
     // ---- warps without an instance pull the next clip from the queue
     while (s.inst < 0 && !drained) {
@@ -107,7 +125,7 @@ __global__ void __launch_bounds__(128, 3) clip_kernel(const RunArgs a) {
       __syncwarp();
       s.new_frame = true; s.need_fk = true;
     }
-    if (tick % a.sync_period == 0) { if (!__syncthreads_or(s.inst >= 0)) break; }
+    if (tick % a.sync_period == 0) { if (!group_barrier_or(1 + grp, grp_threads, s.inst >= 0)) break; }
     tick++;
     if (s.inst < 0) continue;
     const DevModel& M = mv.M();

@@ -134,7 +134,7 @@ __device__ __forceinline__ void q2mat(const double* q, double* m) {
 __device__ __forceinline__ void normalize4(double* q) {   // mju_normalize4
   double n2 = q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
   if (n2 < 1e-30) { q[0] = 1; q[1] = q[2] = q[3] = 0; return; }
-  double inv = 1.0 / sqrt(n2);
+  double inv = rsqrt(n2);
   q[0] *= inv; q[1] *= inv; q[2] *= inv; q[3] *= inv;
 }
 __device__ __forceinline__ void cross3(const double* a, const double* b, double* o) {

@@ -77,7 +77,7 @@ __device__ __forceinline__ void stage_prep(const MV& mv, const Lay& lay, double*
 //   A (lane = body, all bodies at once): the body's LOCAL transform, joints included -
 //       tl = body_pos + R(body_quat) sum(slide axis * value),  ql = body_quat (x) prod(hinge rotations),
 //       and each joint axis expressed in the PARENT frame (al, parked in S[6k+3..5]);
-//   B (levels in sequence, lane = body of the level): x = x_p + R(Q_p) tl,  Q = normalize(Q_p (x) ql)
+//   B (levels in sequence, lane = body of the level): x = x_p + R(Q_p) tl,  Q = Q_p (x) ql
 //       - the only sequential part, ~60 flops per level;
 //   C (lane = dof): spatial axis S_k = (v_O, w): twist of the dof expressed at the reference point O =
 //       origin of the floating base (world origin if there is none), so that the geometric Jacobian
@@ -138,6 +138,7 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
         const int qa = mv(M.jnt_qposadr)[jadr];
         pos[0] = q[qa]; pos[1] = q[qa + 1]; pos[2] = q[qa + 2];
         quat[0] = q[qa + 3]; quat[1] = q[qa + 4]; quat[2] = q[qa + 5]; quat[3] = q[qa + 6];
+        normalize4(quat);          // qpos may hold any quaternion; everything below needs a rotation
       } else {
         const int p = mv(M.body_parent)[b];
         const double pq[4] = {xquat[4 * p], xquat[4 * p + 1], xquat[4 * p + 2], xquat[4 * p + 3]};
@@ -148,12 +149,15 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
         pos[0] = xpos[3 * p] + t[0]; pos[1] = xpos[3 * p + 1] + t[1]; pos[2] = xpos[3 * p + 2] + t[2];
         qmul(pq, lq, quat);
       }
-      normalize4(quat);
       xpos[3 * b] = pos[0]; xpos[3 * b + 1] = pos[1]; xpos[3 * b + 2] = pos[2];
       xquat[4 * b] = quat[0]; xquat[4 * b + 1] = quat[1]; xquat[4 * b + 2] = quat[2]; xquat[4 * b + 3] = quat[3];
     }
     __syncwarp();
   }
+  // mju_normalize4 of every body quaternion, all bodies at once (the products above keep unit norm
+  // to rounding, so normalising after the sweep instead of inside it changes results by ~1e-16)
+  for (int b = 1 + lane; b < nb; b += 32) normalize4(xquat + 4 * b);
+  __syncwarp();
   // ---- pass C
   const int ref = M.ref_body;
   const double O[3] = {xpos[3 * ref], xpos[3 * ref + 1], xpos[3 * ref + 2]};    // world (body 0) has xpos = 0
@@ -629,6 +633,7 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
   int best = n + 1, p = 3, nfact = 0;
   bool spd = true;
   double r0 = 0, r1 = 0;
+  int* isact = (int*)x;           // x is written only after the solve: its storage holds the active flags meanwhile
 #pragma unroll 1
   for (int it = 0; it < 400; it++) {
     // ---- right-hand side: active rows carry their bound, free rows -c_F - H_FA x_A
@@ -648,26 +653,30 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
     if (has1) rv[i1] = r1;
     for (int e = lane; e < nnz; e += 32) W[e] = H[e];
     __syncwarp();
-    // ---- L'L factorisation, leaves to root
+    // ---- L'L factorisation, leaves to root, with the sweep L'y = r folded in: when row i is
+    // final, y_i = r_i / L_ii and r_a -= L(i,a) y_i for its ancestors (same lanes as the row scaling)
+    if (has0) isact[i0] = st0 != 0;
+    if (has1) isact[i1] = st1 != 0;
+    __syncwarp();
 #pragma unroll 1
     for (int i = n - 1; i >= 0; i--) {
       const int d = depth[i], rp = rowptr[i];
       double* Wi = W + rp;
-      if ((act >> i) & 1ull) {                        // warp-uniform: identity row
+      if (isact[i]) {                                 // warp-uniform: identity row, y_i = the bound
         if (lane <= d) Wi[lane] = (lane == d) ? 1.0 : 0.0;
-        __syncwarp();
         continue;
       }
       const double w = lane <= d ? Wi[lane] : 0.0;
+      const double ri = rv[i];
+      const int col = lane < d ? anc[rp + lane] : i;
       double piv = __shfl_sync(GMR_FULL, w, d);
       if (!(piv > 0.0)) { spd = false; piv = 1.0; }
       const double inv = rsqrt(piv);
-      if (lane <= d) {
-        const int col = anc[rp + lane];
-        const double l = (lane == d) ? inv : (((act >> col) & 1ull) ? 0.0 : w * inv);
-        Wi[lane] = l;                                  // diagonal stores 1/L_ii
-        lrow[lane] = l;
-      }
+      const double yi = ri * inv;
+      const double l = isact[col] ? 0.0 : w * inv;
+      __syncwarp();
+      if (lane < d) { Wi[lane] = l; lrow[lane] = l; rv[col] -= l * yi; }
+      else if (lane == d) { Wi[d] = inv; rv[i] = yi; }          // diagonal stores 1/L_ii
       __syncwarp();
       const int P = (d * (d + 1)) >> 1;
 #pragma unroll 1
@@ -679,16 +688,6 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
       __syncwarp();
     }
     nfact++;
-    // ---- L' y = r
-#pragma unroll 1
-    for (int i = n - 1; i >= 0; i--) {
-      const int d = depth[i], rp = rowptr[i];
-      const double yi = rv[i] * W[rp + d];
-      __syncwarp();
-      if (lane < d) rv[anc[rp + lane]] -= W[rp + lane] * yi;
-      else if (lane == d) rv[i] = yi;
-      __syncwarp();
-    }
     // ---- L x = y, wavefront over depth
     r0 = has0 ? rv[i0] : 0.0;
     r1 = has1 ? rv[i1] : 0.0;
