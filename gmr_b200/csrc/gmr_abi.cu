@@ -133,10 +133,11 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   }
   if (max_depth > 31) return fail(-4, "kinematic chains longer than 32 dofs are unsupported");
   const int nnz = dof_rowptr[nv];
-  std::vector<short> dof_anc(nnz, 0), dof_ancrow(nnz, 0);
+  std::vector<short> dof_anc(nnz, 0), dof_ancrow(nnz, 0), ent_row(nnz, 0);
   for (int i = 0; i < nv; i++) {
     int k = i;
     for (int a = dof_depth[i]; a >= 0; a--) {
+      ent_row[dof_rowptr[i] + a] = (short)i;
       dof_anc[dof_rowptr[i] + a] = (short)k;
       dof_ancrow[dof_rowptr[i] + a] = (short)dof_rowptr[k];
       k = dof_parent[k];
@@ -166,6 +167,45 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       for (int i = body_lastdof[body]; i >= 0; i = dof_parent[i]) taskmask[k * nv + i] |= 1u << t;
     }
   }
+  // task tree per stage: parent = the task on the nearest proper-ancestor body that carries one
+  std::vector<unsigned> topmask(2 * nv, 0u), childmask(2 * MT, 0u);
+  std::vector<int> tasklev_start(2 * (MT + 1), 0), tasklev_task(2 * MT, 0);
+  int n_tasklev[2] = {0, 0};
+  for (int k = 0; k < 2; k++) {
+    if (!d->use_table[k]) continue;
+    const int m_k = d->n_task[k];
+    std::vector<int> task_of_body(nb, -1), tparent(m_k, -1), height(m_k, 0);
+    for (int t = 0; t < m_k; t++) {
+      if (task_of_body[task_body[k * MT + t]] >= 0) return fail(-5, "two tasks of one stage on the same robot body");
+      task_of_body[task_body[k * MT + t]] = t;
+    }
+    for (int t = 0; t < m_k; t++)
+      for (int p = d->body_parentid[task_body[k * MT + t]]; p > 0; p = d->body_parentid[p])
+        if (task_of_body[p] >= 0) { tparent[t] = task_of_body[p]; break; }
+    // heights: process tasks by decreasing body depth so children come first
+    std::vector<int> order(m_k);
+    for (int t = 0; t < m_k; t++) order[t] = t;
+    std::sort(order.begin(), order.end(), [&](int x, int y) { return depth[task_body[k * MT + x]] > depth[task_body[k * MT + y]]; });
+    int hmax = 0;
+    for (int t : order)
+      if (tparent[t] >= 0) {
+        childmask[k * MT + tparent[t]] |= 1u << t;
+        height[tparent[t]] = std::max(height[tparent[t]], height[t] + 1);
+        hmax = std::max(hmax, height[tparent[t]]);
+      }
+    n_tasklev[k] = hmax;
+    int pos = 0;
+    for (int h = 1; h <= hmax; h++) {
+      tasklev_start[k * (MT + 1) + h - 1] = pos;
+      for (int t = 0; t < m_k; t++) if (height[t] == h) tasklev_task[k * MT + pos++] = t;
+    }
+    tasklev_start[k * (MT + 1) + hmax] = pos;
+    for (int l = 0; l < nv; l++) {
+      const unsigned mk = taskmask[k * nv + l];
+      for (int t = 0; t < m_k; t++)
+        if (((mk >> t) & 1u) && (tparent[t] < 0 || !((mk >> tparent[t]) & 1u))) topmask[k * nv + l] |= 1u << t;
+    }
+  }
   for (int i = 0; i < d->n_scaled; i++)
     if (d->scaled_human_index[i] < 0 || d->scaled_human_index[i] >= d->n_human) return fail(-5, "scaled_human_index out of range");
 
@@ -182,7 +222,9 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
          o_sc = bl.push(vec(d->scale, d->n_scaled)), o_po = bl.push(vec(d->pos_off, 3 * d->n_scaled)),
          o_ro = bl.push(vec(d->rot_off, 4 * d->n_scaled)), o_ft = bl.push(vec(d->is_foot, d->n_scaled)),
          o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot),
-         o_dd = bl.push(dof_depth), o_rp = bl.push(dof_rowptr), o_an = bl.push(dof_anc), o_ar = bl.push(dof_ancrow);
+         o_dd = bl.push(dof_depth), o_rp = bl.push(dof_rowptr), o_an = bl.push(dof_anc), o_ar = bl.push(dof_ancrow),
+         o_er = bl.push(ent_row), o_tpm = bl.push(topmask), o_chm = bl.push(childmask), o_tls = bl.push(tasklev_start),
+         o_tlt = bl.push(tasklev_task);
 
   // FK tail tables (KinematicsModel semantics: bodies under the first top-level body, float32, xyzw)
   const int nbt = nb - 1;
@@ -248,6 +290,9 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.nnz = nnz; h.max_depth = max_depth;
   h.dof_depth = (const int*)(B0 + o_dd); h.dof_rowptr = (const int*)(B0 + o_rp);
   h.dof_anc = (const short*)(B0 + o_an); h.dof_ancrow = (const short*)(B0 + o_ar);
+  h.ent_row = (const short*)(B0 + o_er); h.dof_topmask = (const unsigned*)(B0 + o_tpm);
+  h.task_childmask = (const unsigned*)(B0 + o_chm); h.tasklev_start = (const int*)(B0 + o_tls);
+  h.tasklev_task = (const int*)(B0 + o_tlt); h.n_tasklev[0] = n_tasklev[0]; h.n_tasklev[1] = n_tasklev[1];
   m->max_task = std::max(h.n_task[0], h.n_task[1]);
   char* T0 = m->tail_blob;
   m->tail.nbody = nbt; m->tail.parent = (const int*)(T0 + t_p); m->tail.trans = (const float*)(T0 + t_t);
@@ -274,13 +319,15 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz) {
   Lay L{};
   int o = 0;
   auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };   // keep 16-byte alignment
-  L.q = take(nq); L.scaled = take(7 * s); L.c = take(nv); L.x = take(nv); L.lo = take(nv); L.hi = take(nv);
+  L.q = take(nq); L.scaled = take(7 * s); L.x = take(nv);
   L.rv = take(nv); L.H = take(nnz);
   const int region = o;
   L.xpos = take(3 * nbody); L.xquat = take(4 * nbody); L.S = take(6 * nv); L.e = take(6 * m);
   L.K = take(21 * m); L.g = take(6 * m);
   L.tl = L.K; L.ql = L.tl + ((3 * nbody + 1) & ~1);          // FK local transforms alias K/g
   o = std::max(o, L.ql + ((4 * nbody + 1) & ~1));
+  if (6 * nv <= L.S - L.xpos) L.F = L.xpos;                   // F_l aliases the body poses when it fits
+  else L.F = take(6 * nv);
   L.L = region;                                  // the factor overlays the kinematics scratch
   L.lrow = region + ((nnz + 1) & ~1);
   o = std::max(o, L.lrow + 32);

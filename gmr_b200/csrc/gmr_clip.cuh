@@ -181,8 +181,9 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, GMR_MIN_CTAS) clip_kernel(con
     if (!solve) continue;
     // ---- Kernel 2+3: task stiffness, QP assembly (mink build_ik), box QP; Kernel 4: integrate
     const double mu = stage_stiffness(mv, lay, sm, s.stage, lane);
-    stage_assemble(mv, lay, sm, s.stage, mu, lane);
-    const int nf = qp_solve_tree(mv, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
+    double qc[2], qlo[2], qhi[2];
+    stage_assemble(mv, lay, sm, s.stage, mu, lane, qc, qlo, qhi);
+    const int nf = qp_solve_tree(mv, sm + lay.H, qc, qlo, qhi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
                                  sm + lay.x, pair_tab, lane, s.act_lo, s.act_hi);
     s.nfact = (nf < 0 || s.nfact < 0) ? -abs(s.nfact) - abs(nf) : s.nfact + nf;
     stage_integrate(mv, lay, sm, lane);
@@ -253,7 +254,8 @@ __global__ void build_qp_kernel(const StageArgs a) {
   stage_fk(mv, lay, sm, lane);
   stage_errors(mv, lay, sm, a.stage, lane);
   const double mu = stage_stiffness(mv, lay, sm, a.stage, lane);
-  stage_assemble(mv, lay, sm, a.stage, mu, lane);
+  double qc[2], qlo[2], qhi[2];
+  stage_assemble(mv, lay, sm, a.stage, mu, lane, qc, qlo, qhi);
   const int n = M.nv, m = M.n_task[a.stage];
   if (a.e_out) for (int i = lane; i < 6 * m; i += 32) a.e_out[(size_t)inst * a.m_max * 6 + i] = sm[lay.e + i];
   double* Ho = a.H_out + (size_t)inst * a.nv_max * a.nv_max;
@@ -261,10 +263,13 @@ __global__ void build_qp_kernel(const StageArgs a) {
     const int i = idx / n, j = idx % n;
     Ho[i * a.nv_max + j] = tree_at(mv, sm + lay.H, i, j);
   }
-  for (int i = lane; i < n; i += 32) {
-    a.c_out[(size_t)inst * a.nv_max + i] = sm[lay.c + i];
-    a.lo_out[(size_t)inst * a.nv_max + i] = sm[lay.lo + i];
-    a.hi_out[(size_t)inst * a.nv_max + i] = sm[lay.hi + i];
+  for (int r = 0; r < 2; r++) {
+    const int i = lane + 32 * r;
+    if (i < n) {
+      a.c_out[(size_t)inst * a.nv_max + i] = qc[r];
+      a.lo_out[(size_t)inst * a.nv_max + i] = qlo[r];
+      a.hi_out[(size_t)inst * a.nv_max + i] = qhi[r];
+    }
   }
 }
 
@@ -287,9 +292,10 @@ __global__ void solve_ik_kernel(const StageArgs a) {
   stage_fk(mv, lay, sm, lane);
   stage_errors(mv, lay, sm, a.stage, lane);
   const double mu = stage_stiffness(mv, lay, sm, a.stage, lane);
-  stage_assemble(mv, lay, sm, a.stage, mu, lane);
+  double qc[2], qlo[2], qhi[2];
+  stage_assemble(mv, lay, sm, a.stage, mu, lane, qc, qlo, qhi);
   unsigned long long act_lo = 0, act_hi = 0;
-  const int nf = qp_solve_tree(mv, sm + lay.H, sm + lay.c, sm + lay.lo, sm + lay.hi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
+  const int nf = qp_solve_tree(mv, sm + lay.H, qc, qlo, qhi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
                                sm + lay.x, pair_tab, lane, act_lo, act_hi);
   for (int i = lane; i < M.nv; i += 32) a.dq_out[(size_t)inst * a.nv_max + i] = sm[lay.x + i];
   if (lane == 0 && a.nfact_out) a.nfact_out[inst] = nf;

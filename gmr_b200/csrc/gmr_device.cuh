@@ -49,6 +49,12 @@ struct DevModel {
   const double* dof_lo;      // [nv] joint range lower
   const double* dof_hi;      // [nv]
   const unsigned* dof_taskmask;  // [2*nv] bit t set: task t of the stage is in the dof's subtree
+  const unsigned* dof_topmask;   // [2*nv] the top-most of those tasks (no other task of the subtree above them)
+  // task tree of each stage (task t's parent = the task on the nearest ancestor body that has one)
+  int n_tasklev[2];              // heights 1..n of parent tasks
+  const int* tasklev_start;      // [2*(MAXT+1)] into tasklev_task, per height
+  const int* tasklev_task;       // [2*MAXT] parent tasks sorted by height (children first)
+  const unsigned* task_childmask;// [2*MAXT] bit c set: task c is a child of this task
   // branch-induced sparsity of H = J'WJ + mu I (Featherstone): H(i,k) != 0 only if k is an
   // ancestor-or-self of i (or vice versa).  Row i of the packed lower triangle holds its
   // depth[i]+1 entries in chain order: entry a (0 = topmost ancestor, depth[i] = i itself) is
@@ -59,6 +65,7 @@ struct DevModel {
   const int* dof_rowptr;         // [nv+1]
   const short* dof_anc;          // [nnz]
   const short* dof_ancrow;       // [nnz] rowptr of that ancestor
+  const short* ent_row;          // [nnz] row (dof) of each stored entry
   // target preparation
   const int* scaled_index;   // [s] body index inside a human frame
   const double* scale;       // [s]
@@ -90,9 +97,10 @@ struct ModelView {
 
 // Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
 struct Lay {
-  int q, scaled, c, x, lo, hi, rv, H;     // persistent across the QP solve (H: nnz packed tree rows)
+  int q, scaled, x, rv, H;                // persistent across the QP solve (H: nnz packed tree rows)
   int xpos, xquat, S, e, K, g;            // kinematics / assembly scratch ...
   int tl, ql;                             // FK local transforms (alias K/g: dead before the stiffness pass)
+  int F;                                  // F_l = Kc_l S_l of the assembly (aliases xpos/xquat: dead after the stiffness pass)
   int L, lrow;                            // ... overlaid by the factor (nnz) + one row (32) during the solve
   int total;                              // doubles per warp
   int maxt;                               // stride of the stage-major task tables

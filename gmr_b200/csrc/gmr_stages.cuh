@@ -352,18 +352,52 @@ __device__ __forceinline__ double stage_stiffness(const MV& mv, const Lay& lay, 
 }
 
 // ------------------------------------------------------------------ Kernel 3: assembly (mink build_ik)
-// lane l = dof l:  Kc = sum of K_t over tasks in the subtree of dof l,  F = Kc S_l,
-// H(l,k) = S_k . F for every ancestor-or-self k of l (all other entries are structurally 0 and not stored),
-// c[l] = S_l . sum g_t.  diag += damping + lm_damping * sum mu.  Also the ConfigurationLimit box.
+//   H(l,k) = S_k' Kc_l S_l  for k an ancestor-or-self of l,   c_l = S_l . gc_l,
+// where Kc_l / gc_l sum K_t / g_t over the tasks in the subtree of dof l; everything else is
+// structurally zero and not stored.  diag += damping + lm_damping * sum mu.  Three passes:
+//   1. subtree sums on the TASK tree, in place: bottom-up, K_t += K_child for every task whose body
+//      hangs below t's body (lane = (parent task, one of the 27 numbers); a handful of passes);
+//   2. lane = dof l: Kc_l = sum over the few top-most tasks of l's subtree (1-3 for a humanoid),
+//      F_l = Kc_l S_l -> shared memory, c_l, and the ConfigurationLimit box (registers);
+//   3. lane = stored entry (l,k) of the tree layout: H = S_k . F_l (+ diag) - all nnz entries in
+//      nnz/32 passes, whatever the depth of their row.
 template <class MV>
-__device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, double* sm, int stage, double mu_sum, int lane) {
+__device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, double* sm, int stage, double mu_sum, int lane,
+                                               double (&c_out)[2], double (&lo_out)[2], double (&hi_out)[2]) {
   const DevModel& M = mv.M();
   const int n = M.nv;
   double* H = sm + lay.H;
+  double* Kt = sm + lay.K;
+  double* gt = sm + lay.g;
+  double* F = sm + lay.F;
   const double diag = M.damping + M.lm_damping * mu_sum;
   const double* q = sm + lay.q;
-  for (int l = lane; l < n; l += 32) {
-    unsigned mask = mv(M.dof_taskmask)[stage * n + l];
+  // ---- 1. subtree sums over the task tree (parents sorted by height, children as bit masks)
+  const int* tl_start = mv(M.tasklev_start) + stage * (lay.maxt + 1);
+  const int* tl_task = mv(M.tasklev_task) + stage * lay.maxt;
+  const unsigned* child_mask = mv(M.task_childmask) + stage * lay.maxt;
+  const int nlev = M.n_tasklev[stage];
+  for (int lv = 0; lv < nlev; lv++) {
+    const int beg = tl_start[lv], cnt = (tl_start[lv + 1] - beg) * 27;
+    for (int it = lane; it < cnt; it += 32) {
+      const int t = tl_task[beg + it / 27], e = it % 27;
+      double* dst = e < 21 ? Kt + 21 * t + e : gt + 6 * t + (e - 21);
+      const int stride = e < 21 ? 21 : 6;
+      const double* src0 = e < 21 ? Kt + e : gt + (e - 21);
+      double acc = *dst;
+      for (unsigned cm = child_mask[t]; cm; cm &= cm - 1) acc += src0[stride * (__ffs(cm) - 1)];
+      *dst = acc;
+    }
+    __syncwarp();
+  }
+  // ---- 2. per dof: F_l, c_l, box (c, lo, hi stay in registers: lane l / l+32 is the lane that owns
+  //         dof l in the QP)
+#pragma unroll
+  for (int r = 0; r < 2; r++) {
+    const int l = lane + 32 * r;
+    c_out[r] = 0; lo_out[r] = -INFINITY; hi_out[r] = INFINITY;
+    if (l >= n) continue;
+    unsigned mask = mv(M.dof_topmask)[stage * n + l];
     double Kc[21], gc[6];
 #pragma unroll
     for (int i = 0; i < 21; i++) Kc[i] = 0;
@@ -372,15 +406,15 @@ __device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, dou
     while (mask) {
       const int t = __ffs(mask) - 1;
       mask &= mask - 1;
-      const double* K = sm + lay.K + 21 * t;
-      const double* g = sm + lay.g + 6 * t;
+      const double* K = Kt + 21 * t;
+      const double* g = gt + 6 * t;
 #pragma unroll
       for (int i = 0; i < 21; i++) Kc[i] += K[i];
 #pragma unroll
       for (int i = 0; i < 6; i++) gc[i] += g[i];
     }
     const double* Sl = sm + lay.S + 6 * l;
-    double s[6], F[6];
+    double s[6];
 #pragma unroll
     for (int i = 0; i < 6; i++) s[i] = Sl[i];
 #pragma unroll
@@ -388,21 +422,12 @@ __device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, dou
       double acc = 0;
 #pragma unroll
       for (int j = 0; j < 6; j++) acc += Kc[i >= j ? i * (i + 1) / 2 + j : j * (j + 1) / 2 + i] * s[j];
-      F[i] = acc;
+      F[6 * l + i] = acc;
     }
     double cl = 0;
 #pragma unroll
     for (int i = 0; i < 6; i++) cl += s[i] * gc[i];
-    sm[lay.c + l] = cl;
-    const int dl = mv(M.dof_depth)[l], rp = mv(M.dof_rowptr)[l];
-#pragma unroll 1
-    for (int a2 = 0; a2 <= dl; a2++) {                       // tree row l: its ancestors top-down, then itself
-      const double* Sk = sm + lay.S + 6 * mv(M.dof_anc)[rp + a2];
-      double h = 0;
-#pragma unroll
-      for (int i = 0; i < 6; i++) h += Sk[i] * F[i];
-      H[rp + a2] = h + (a2 == dl ? diag : 0.0);
-    }
+    c_out[r] = cl;
     // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs
     double lo = -INFINITY, hi = INFINITY;
     if (mv(M.dof_limited)[l]) {
@@ -410,8 +435,21 @@ __device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, dou
       hi = M.limit_gain * (mv(M.dof_hi)[l] - qv);
       lo = -M.limit_gain * (qv - mv(M.dof_lo)[l]);
     }
-    sm[lay.lo + l] = lo;
-    sm[lay.hi + l] = hi;
+    lo_out[r] = lo;
+    hi_out[r] = hi;
+  }
+  __syncwarp();
+  // ---- 3. every stored entry of H
+  const short* ent_row = mv(M.ent_row);
+  const short* anc = mv(M.dof_anc);
+  for (int e = lane; e < M.nnz; e += 32) {
+    const int l = ent_row[e], k = anc[e];
+    const double* Sk = sm + lay.S + 6 * k;
+    const double* Fl = F + 6 * l;
+    double h = 0;
+#pragma unroll
+    for (int i = 0; i < 6; i++) h += Sk[i] * Fl[i];
+    H[e] = h + (k == l ? diag : 0.0);
   }
   __syncwarp();
 }
@@ -609,8 +647,8 @@ __device__ __forceinline__ double tree_at(const MV& mv, const double* H, int i, 
 }
 
 template <class MV>
-__device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restrict__ H, const double* __restrict__ c,
-                                          const double* __restrict__ lo, const double* __restrict__ hi,
+__device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restrict__ H, const double (&c)[2],
+                                          const double (&lo)[2], const double (&hi)[2],
                                           double* __restrict__ W, double* __restrict__ lrow, double* __restrict__ rv,
                                           double* __restrict__ x, const unsigned short* __restrict__ pair_tab, int lane,
                                           unsigned long long& act_lo, unsigned long long& act_hi) {
@@ -622,8 +660,7 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
   const int* rowptr = mv(M.dof_rowptr);
   const int i0 = lane, i1 = lane + 32;
   const bool has0 = i0 < n, has1 = i1 < n, two = n > 32;
-  const double lo0 = has0 ? lo[i0] : 0, hi0 = has0 ? hi[i0] : 0, lo1 = has1 ? lo[i1] : 0, hi1 = has1 ? hi[i1] : 0;
-  const double c0 = has0 ? c[i0] : 0, c1 = has1 ? c[i1] : 0;
+  const double lo0 = lo[0], hi0 = hi[0], lo1 = lo[1], hi1 = hi[1], c0 = c[0], c1 = c[1];    // lane l owns dofs l and l+32
   const int d0 = has0 ? depth[i0] : -1, d1 = has1 ? depth[i1] : -1;
   const int rp0 = has0 ? rowptr[i0] : 0, rp1 = has1 ? rowptr[i1] : 0;
   int st0 = 0, st1 = 0;      // 0 free, -1 at lower, +1 at upper; a seed is only honoured where the bound is finite
