@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 #include <algorithm>
+#include <map>
 
 #include "../../include/gmr_b200.h"
 #include "gmr_clip.cuh"
@@ -22,6 +23,7 @@ struct gmr_model {
   DevModel host{};           // device pointers inside
   char* blob = nullptr;      // one device allocation holding every table
   size_t blob_bytes = 0;
+  size_t staged_bytes = 0;   // leading part of the blob that the fused kernel stages in shared memory
   int max_task = 0;
   // FK tail tables
   FkTailModel tail{};
@@ -143,6 +145,63 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       k = dof_parent[k];
     }
   }
+  // ---- static elimination program of the L'L factorisation (see qp_solve_tree):
+  // dofs of equal height (longest path to a leaf) are pairwise unrelated and all their descendants
+  // have lower height, so they can be eliminated in the same step; a step packs up to 4 such rows
+  // side by side into the 32 lanes (lane = one stored entry of a row).  The updates
+  // W(anc_a, anc_b) -= L(i,a) L(i,b) and r(anc_a) -= L(i,a) y_i of the rows of one step are merged
+  // per target (rows of different branches meet in their common ancestors), one op per target:
+  //   op = {target(16) | n(2)<<16,  n x (lane_a(5) | lane_b(5)<<5) in 10-bit fields},  target < nnz: W entry,
+  //   else r[target-nnz]; the ops of a step are sorted by n (descending) so that the lanes of a pass agree on n
+  std::vector<int> elim_lane, elim_opstart;
+  std::vector<int> elim_ops;            // int2 per op
+  int n_elim_step = 0;
+  {
+    std::vector<int> hgt(nv, 0);
+    int hmax = 0;
+    for (int i = nv - 1; i >= 0; i--) {
+      if (dof_parent[i] >= 0) hgt[dof_parent[i]] = std::max(hgt[dof_parent[i]], hgt[i] + 1);
+      hmax = std::max(hmax, hgt[i]);
+    }
+    elim_opstart.push_back(0);
+    for (int hh = 0; hh <= hmax; hh++) {
+      std::vector<int> todo;
+      for (int i = nv - 1; i >= 0; i--) if (hgt[i] == hh) todo.push_back(i);
+      size_t pos = 0;
+      while (pos < todo.size()) {
+        std::vector<int> rows, base;
+        int used = 0;
+        while (pos < todo.size() && rows.size() < 3 && used + dof_depth[todo[pos]] + 1 <= 32) {
+          rows.push_back(todo[pos]); base.push_back(used); used += dof_depth[todo[pos]] + 1; pos++;
+        }
+        std::vector<int> lt(64, 0);            // per lane: w0 = ent | diag_lane<<16 | is_diag<<21 | valid<<22, w1 = col | row<<8
+        for (int l = 0; l < 32; l++) lt[2 * l] = l << 16;
+        std::map<int, std::vector<int>> tgt;   // target -> contributions (la | lb<<5)
+        for (size_t r = 0; r < rows.size(); r++) {
+          const int i = rows[r], dd = dof_depth[i], rp = dof_rowptr[i], b0 = base[r];
+          for (int a2 = 0; a2 <= dd; a2++) {
+            lt[2 * (b0 + a2)] = (rp + a2) | ((b0 + dd) << 16) | ((a2 == dd ? 1 : 0) << 21) | (1 << 22);
+            lt[2 * (b0 + a2) + 1] = dof_anc[rp + a2] | (i << 8);
+          }
+          for (int a2 = 0; a2 < dd; a2++) {
+            for (int b2 = 0; b2 <= a2; b2++) tgt[dof_ancrow[rp + a2] + b2].push_back((b0 + a2) | ((b0 + b2) << 5));
+            tgt[nnz + dof_anc[rp + a2]].push_back((b0 + a2) | ((b0 + dd) << 5));
+          }
+        }
+        elim_lane.insert(elim_lane.end(), lt.begin(), lt.end());
+        for (int want = 3; want >= 1; want--)
+          for (auto& kv : tgt) {
+            if ((int)kv.second.size() != want) continue;
+            int cw = 0;
+            for (size_t c2 = 0; c2 < kv.second.size(); c2++) cw |= kv.second[c2] << (10 * c2);
+            elim_ops.push_back(kv.first | (want << 16));
+            elim_ops.push_back(cw);
+          }
+        elim_opstart.push_back((int)elim_ops.size() / 2);
+        n_elim_step++;
+      }
+    }
+  }
   // levels (level 1 first)
   std::vector<int> level_start(nlevel + 1, 0), level_body;
   for (int lv = 1; lv <= nlevel; lv++) {
@@ -224,7 +283,8 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
          o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot),
          o_dd = bl.push(dof_depth), o_rp = bl.push(dof_rowptr), o_an = bl.push(dof_anc), o_ar = bl.push(dof_ancrow),
          o_er = bl.push(ent_row), o_tpm = bl.push(topmask), o_chm = bl.push(childmask), o_tls = bl.push(tasklev_start),
-         o_tlt = bl.push(tasklev_task);
+         o_tlt = bl.push(tasklev_task), o_el = bl.push(elim_lane), o_eo = bl.push(elim_ops), o_es = bl.push(elim_opstart);
+  const size_t staged_bytes = (bl.bytes.size() + 15) & ~size_t(15);
 
   // FK tail tables (KinematicsModel semantics: bodies under the first top-level body, float32, xyzw)
   const int nbt = nb - 1;
@@ -267,6 +327,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
     return fail(-100, std::string("model upload: ") + cudaGetErrorString(e));
   }
   m->blob_bytes = bl.bytes.size();
+  m->staged_bytes = staged_bytes;
   DevModel& h = m->host;
   h.nbody = nb; h.njnt = nj; h.nq = d->nq; h.nv = nv; h.n_human = d->n_human; h.n_scaled = d->n_scaled;
   h.nlevel = nlevel; h.ref_body = ref_body;
@@ -281,7 +342,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.jnt_qposadr = (const int*)(B0 + o_jq); h.jnt_dofadr = (const int*)(B0 + o_jd);
   h.jnt_axis = (const double*)(B0 + o_jaxis); h.qpos0 = (const double*)(B0 + o_q0);
   h.dof_kind = (const int*)(B0 + o_dk); h.dof_qadr = (const int*)(B0 + o_dq); h.dof_parent = (const int*)(B0 + o_dp);
-  h.dof_body = (const int*)(B0 + o_db); h.blob = B0; h.blob_bytes = (int)bl.bytes.size();
+  h.dof_body = (const int*)(B0 + o_db); h.blob = B0; h.blob_bytes = (int)staged_bytes;
   h.dof_limited = (const int*)(B0 + o_dl); h.dof_lo = (const double*)(B0 + o_dlo); h.dof_hi = (const double*)(B0 + o_dhi);
   h.dof_taskmask = (const unsigned*)(B0 + o_tm); h.scaled_index = (const int*)(B0 + o_si);
   h.scale = (const double*)(B0 + o_sc); h.pos_off = (const double*)(B0 + o_po); h.rot_off = (const double*)(B0 + o_ro);
@@ -292,6 +353,8 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.dof_anc = (const short*)(B0 + o_an); h.dof_ancrow = (const short*)(B0 + o_ar);
   h.ent_row = (const short*)(B0 + o_er); h.dof_topmask = (const unsigned*)(B0 + o_tpm);
   h.task_childmask = (const unsigned*)(B0 + o_chm); h.tasklev_start = (const int*)(B0 + o_tls);
+  h.elim_lane = (const int2*)(B0 + o_el); h.elim_ops = (const int2*)(B0 + o_eo);
+  h.elim_opstart = (const int*)(B0 + o_es); h.n_elim_step = n_elim_step;
   h.tasklev_task = (const int*)(B0 + o_tlt); h.n_tasklev[0] = n_tasklev[0]; h.n_tasklev[1] = n_tasklev[1];
   m->max_task = std::max(h.n_task[0], h.n_task[1]);
   char* T0 = m->tail_blob;
@@ -319,8 +382,7 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz) {
   Lay L{};
   int o = 0;
   auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };   // keep 16-byte alignment
-  L.q = take(nq); L.scaled = take(7 * s); L.x = take(nv);
-  L.rv = take(nv); L.H = take(nnz);
+  L.q = take(nq); L.scaled = take(7 * s); L.x = take(nv); L.H = take(nnz);
   const int region = o;
   L.xpos = take(3 * nbody); L.xquat = take(4 * nbody); L.S = take(6 * nv); L.e = take(6 * m);
   L.K = take(21 * m); L.g = take(6 * m);
@@ -329,7 +391,8 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz) {
   if (6 * nv <= L.S - L.xpos) L.F = L.xpos;                   // F_l aliases the body poses when it fits
   else L.F = take(6 * nv);
   L.L = region;                                  // the factor overlays the kinematics scratch
-  L.lrow = region + ((nnz + 1) & ~1);
+  L.rv = region + nnz;                           // right-hand side directly behind the factor (one index space)
+  L.lrow = region + ((nnz + nv + 1) & ~1);
   o = std::max(o, L.lrow + 32);
   L.total = o;
   L.maxt = GMR_MAX_TASKS;
@@ -380,20 +443,21 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, b->device);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device);
   if (e == cudaSuccess) {
-    // the fused kernel is compiled for 256 threads x 2 CTAs (128 registers): pick the CTA width
-    // (<= 8 warps) that puts the most warps on an SM; ties go to the narrower CTA
-    const size_t blob = n_models == 1 ? (((size_t)models[0]->blob_bytes + 15) & ~size_t(15)) : 0;
+    // the fused kernel is compiled for 128 registers (16 warps per SM): pick the CTA width that puts
+    // the most warps on an SM (the staged model is per CTA, so wide CTAs amortise it); ties go to
+    // the narrower CTA
+    const size_t blob = n_models == 1 ? models[0]->staged_bytes : 0;
     const size_t fixed = 2048 + 1024;   // static shared memory of the kernel + the per-CTA reservation
     const size_t sm_total = 228 * 1024;
     b->smem_model = n_models == 1 && per_warp + blob + fixed <= (size_t)dev_smem && !getenv("GMR_DEBUG_GLOBAL_MODEL");
     const size_t extra = fixed + (b->smem_model ? blob : 0);
     int best_w = 1, best_total = 0;
-    for (int w = 1; w <= 8; w++) {
+    for (int w = 1; w <= 16; w++) {
       if ((size_t)w * per_warp + extra > (size_t)dev_smem + 1024) break;
       int ctas = (int)std::min<size_t>(sm_total / ((size_t)w * per_warp + extra), (size_t)(16 / w));
       if (ctas * w > best_total) { best_total = ctas * w; best_w = w; }
     }
-    if (const char* ev = getenv("GMR_DEBUG_WARPS")) best_w = std::max(1, std::min(8, atoi(ev)));
+    if (const char* ev = getenv("GMR_DEBUG_WARPS")) best_w = std::max(1, std::min(16, atoi(ev)));
     b->warps_per_cta = std::min(best_w, B);
     b->smem_bytes = per_warp * b->warps_per_cta;
     b->clip_smem_bytes = b->smem_bytes + (b->smem_model ? blob : 0);

@@ -11,8 +11,8 @@
 namespace gmr {
 
 #ifndef GMR_MIN_CTAS
-#define GMR_MIN_CTAS 2
-#define GMR_CTA_THREADS 256
+#define GMR_MIN_CTAS 1
+#define GMR_CTA_THREADS 512
 #endif
 
 struct RunArgs {

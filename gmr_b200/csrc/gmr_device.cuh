@@ -21,7 +21,7 @@ enum : int { DOF_FREE_T = 0, DOF_FREE_R = 1, DOF_SLIDE = 2, DOF_HINGE = 3 };
 // FrameTask lists (:78-114); prep tables replace pos/rot_offsets1 + human_scale_table.
 struct DevModel {
   const char* blob;          // the one device allocation every table pointer below points into
-  int blob_bytes;
+  int blob_bytes;            // leading bytes of the blob that a CTA stages in shared memory (ModelView)
   int nbody, njnt, nq, nv, n_human, n_scaled, nlevel, ref_body;
   int use[2], n_task[2];
   int max_iter;
@@ -66,6 +66,11 @@ struct DevModel {
   const short* dof_anc;          // [nnz]
   const short* dof_ancrow;       // [nnz] rowptr of that ancestor
   const short* ent_row;          // [nnz] row (dof) of each stored entry
+  // static elimination program of the L'L factorisation (built by gmr_model_create)
+  int n_elim_step;
+  const int2* elim_lane;         // [n_elim_step*32] per lane: x = entry | diag_lane<<16 | is_diag<<21 | valid<<22, y = col | row<<8
+  const int2* elim_ops;          // merged updates: x = target(16) | n<<16, y = n x (lane_a(5) | lane_b(5)<<5), 10-bit fields
+  const int* elim_opstart;       // [n_elim_step+1]
   // target preparation
   const int* scaled_index;   // [s] body index inside a human frame
   const double* scale;       // [s]
@@ -97,11 +102,11 @@ struct ModelView {
 
 // Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
 struct Lay {
-  int q, scaled, x, rv, H;                // persistent across the QP solve (H: nnz packed tree rows)
+  int q, scaled, x, H;                    // persistent across the QP solve (H: nnz packed tree rows)
   int xpos, xquat, S, e, K, g;            // kinematics / assembly scratch ...
   int tl, ql;                             // FK local transforms (alias K/g: dead before the stiffness pass)
   int F;                                  // F_l = Kc_l S_l of the assembly (aliases xpos/xquat: dead after the stiffness pass)
-  int L, lrow;                            // ... overlaid by the factor (nnz) + one row (32) during the solve
+  int L, rv, lrow;                        // ... overlaid by the factor (nnz), the rhs (nv, = L + nnz) and one row (32)
   int total;                              // doubles per warp
   int maxt;                               // stride of the stage-major task tables
 };

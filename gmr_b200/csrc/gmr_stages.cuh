@@ -658,6 +658,10 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
   const short* ancrow = mv(M.dof_ancrow);
   const int* depth = mv(M.dof_depth);
   const int* rowptr = mv(M.dof_rowptr);
+  const int2* elim_lane = mv(M.elim_lane);
+  const int2* elim_ops = mv(M.elim_ops);
+  const int* elim_opstart = mv(M.elim_opstart);
+  rv = W + nnz;                   // the program addresses factor and right-hand side as one array
   const int i0 = lane, i1 = lane + 32;
   const bool has0 = i0 < n, has1 = i1 < n, two = n > 32;
   const double lo0 = lo[0], hi0 = hi[0], lo1 = lo[1], hi1 = hi[1], c0 = c[0], c1 = c[1];    // lane l owns dofs l and l+32
@@ -690,40 +694,52 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
     if (has1) rv[i1] = r1;
     for (int e = lane; e < nnz; e += 32) W[e] = H[e];
     __syncwarp();
-    // ---- L'L factorisation, leaves to root, with the sweep L'y = r folded in: when row i is
-    // final, y_i = r_i / L_ii and r_a -= L(i,a) y_i for its ancestors (same lanes as the row scaling)
+    // ---- L'L factorisation + the sweep L'y = r, driven by the model's static elimination program:
+    // a step scales up to 4 unrelated rows at once (lane = one stored entry; y_i = r_i / L_ii rides in
+    // the row's diagonal lane), then applies the merged updates of those rows, one target per lane.
     if (has0) isact[i0] = st0 != 0;
     if (has1) isact[i1] = st1 != 0;
     __syncwarp();
+    bool notpd = false;
+    int2 lt_next = elim_lane[lane];
+    int q0_next = elim_opstart[0];
 #pragma unroll 1
-    for (int i = n - 1; i >= 0; i--) {
-      const int d = depth[i], rp = rowptr[i];
-      double* Wi = W + rp;
-      if (isact[i]) {                                 // warp-uniform: identity row, y_i = the bound
-        if (lane <= d) Wi[lane] = (lane == d) ? 1.0 : 0.0;
-        continue;
-      }
-      const double w = lane <= d ? Wi[lane] : 0.0;
-      const double ri = rv[i];
-      const int col = lane < d ? anc[rp + lane] : i;
-      double piv = __shfl_sync(GMR_FULL, w, d);
-      if (!(piv > 0.0)) { spd = false; piv = 1.0; }
+    for (int sidx = 0; sidx < M.n_elim_step; sidx++) {
+      const int2 lt = lt_next;
+      const int q0 = q0_next, qend = elim_opstart[sidx + 1];
+      lt_next = elim_lane[min(sidx + 1, M.n_elim_step - 1) * 32 + lane];     // prefetch the next step's lane table
+      q0_next = qend;
+      const bool valid = (lt.x >> 22) & 1, isd = (lt.x >> 21) & 1;
+      const int ent = lt.x & 0xffff, dl = (lt.x >> 16) & 31, col = lt.y & 0xff, row = lt.y >> 8;
+      const double w = valid ? W[ent] : 1.0;
+      const double ri = valid ? rv[row] : 0.0;
+      const bool rowact = valid && isact[row], colact = valid && isact[col];
+      double piv = __shfl_sync(GMR_FULL, w, dl);
+      if (rowact) piv = 1.0;                                     // identity row, y_i = the bound
+      if (!(piv > 0.0)) { notpd = true; piv = 1.0; }
       const double inv = rsqrt(piv);
+      const double l = (rowact || colact) ? 0.0 : w * inv;
       const double yi = ri * inv;
-      const double l = isact[col] ? 0.0 : w * inv;
       __syncwarp();
-      if (lane < d) { Wi[lane] = l; lrow[lane] = l; rv[col] -= l * yi; }
-      else if (lane == d) { Wi[d] = inv; rv[i] = yi; }          // diagonal stores 1/L_ii
+      if (valid) {
+        W[ent] = isd ? inv : l;                                  // diagonal stores 1/L_ii
+        lrow[lane] = isd ? yi : l;
+        if (isd) rv[row] = yi;
+      }
       __syncwarp();
-      const int P = (d * (d + 1)) >> 1;
 #pragma unroll 1
-      for (int q = lane; q < P; q += 32) {
-        const int ab = pair_tab[q], a = ab & 0xff, b = ab >> 8;
-        double* t = W + ancrow[rp + a] + b;
-        *t -= lrow[a] * lrow[b];
+      for (int q = q0 + lane; q < qend; q += 32) {
+        const int2 op = elim_ops[q];
+        const int tgt = op.x & 0xffff, nc = op.x >> 16;
+        int cc = op.y;
+        double acc = lrow[cc & 31] * lrow[(cc >> 5) & 31];
+#pragma unroll 1
+        for (int k = 1; k < nc; k++) { cc >>= 10; acc += lrow[cc & 31] * lrow[(cc >> 5) & 31]; }
+        W[tgt] -= acc;
       }
       __syncwarp();
     }
+    if (__any_sync(GMR_FULL, notpd)) spd = false;
     nfact++;
     // ---- L x = y, wavefront over depth
     r0 = has0 ? rv[i0] : 0.0;
