@@ -145,6 +145,17 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       k = dof_parent[k];
     }
   }
+  // pointer-jumping table of the FK sweep: 2^r-th ancestor of every body (-1 = the world is reached)
+  int fk_rounds = 0;
+  while ((1 << fk_rounds) < nlevel) fk_rounds++;
+  std::vector<short> fk_jump((size_t)std::max(fk_rounds, 1) * nb, -1);
+  for (int b = 1; b < nb; b++) {
+    for (int r = 0; r < fk_rounds; r++) {
+      int a2 = b;
+      for (int k2 = 0; k2 < (1 << r) && a2 > 0; k2++) a2 = d->body_parentid[a2];
+      fk_jump[(size_t)r * nb + b] = (short)(a2 > 0 ? a2 : -1);
+    }
+  }
   // ---- static elimination program of the L'L factorisation (see qp_solve_tree):
   // dofs of equal height (longest path to a leaf) are pairwise unrelated and all their descendants
   // have lower height, so they can be eliminated in the same step; a step packs up to 4 such rows
@@ -283,7 +294,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
          o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot),
          o_dd = bl.push(dof_depth), o_rp = bl.push(dof_rowptr), o_an = bl.push(dof_anc), o_ar = bl.push(dof_ancrow),
          o_er = bl.push(ent_row), o_tpm = bl.push(topmask), o_chm = bl.push(childmask), o_tls = bl.push(tasklev_start),
-         o_tlt = bl.push(tasklev_task), o_el = bl.push(elim_lane), o_eo = bl.push(elim_ops), o_es = bl.push(elim_opstart);
+         o_tlt = bl.push(tasklev_task), o_fj = bl.push(fk_jump), o_el = bl.push(elim_lane), o_eo = bl.push(elim_ops), o_es = bl.push(elim_opstart);
   const size_t staged_bytes = (bl.bytes.size() + 15) & ~size_t(15);
 
   // FK tail tables (KinematicsModel semantics: bodies under the first top-level body, float32, xyzw)
@@ -355,6 +366,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.task_childmask = (const unsigned*)(B0 + o_chm); h.tasklev_start = (const int*)(B0 + o_tls);
   h.elim_lane = (const int2*)(B0 + o_el); h.elim_ops = (const int2*)(B0 + o_eo);
   h.elim_opstart = (const int*)(B0 + o_es); h.n_elim_step = n_elim_step;
+  h.fk_rounds = fk_rounds; h.fk_jump = (const short*)(B0 + o_fj);
   h.tasklev_task = (const int*)(B0 + o_tlt); h.n_tasklev[0] = n_tasklev[0]; h.n_tasklev[1] = n_tasklev[1];
   m->max_task = std::max(h.n_task[0], h.n_task[1]);
   char* T0 = m->tail_blob;

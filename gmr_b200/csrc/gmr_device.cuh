@@ -32,6 +32,8 @@ struct DevModel {
   const double* body_quat;   // [nbody*4]
   const int* body_jntadr;    // [nbody]
   const int* body_jntnum;    // [nbody]
+  int fk_rounds;             // ceil(log2(deepest body))
+  const short* fk_jump;      // [fk_rounds*nbody] 2^r-th ancestor of each body, -1 once that is the world
   const int* level_start;    // [nlevel+1] into level_body (level 1 = children of world)
   const int* level_body;     // [nbody-1] body ids sorted by depth
   // joints

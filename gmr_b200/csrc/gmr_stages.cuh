@@ -77,8 +77,8 @@ __device__ __forceinline__ void stage_prep(const MV& mv, const Lay& lay, double*
 //   A (lane = body, all bodies at once): the body's LOCAL transform, joints included -
 //       tl = body_pos + R(body_quat) sum(slide axis * value),  ql = body_quat (x) prod(hinge rotations),
 //       and each joint axis expressed in the PARENT frame (al, parked in S[6k+3..5]);
-//   B (levels in sequence, lane = body of the level): x = x_p + R(Q_p) tl,  Q = Q_p (x) ql
-//       - the only sequential part, ~60 flops per level;
+//   B (pointer jumping, lane = body): compose every body's transform with that of its 2^r-th ancestor,
+//       r = 0, 1, ...: ceil(log2(tree depth)) rounds over all bodies instead of one pass per level;
 //   C (lane = dof): spatial axis S_k = (v_O, w): twist of the dof expressed at the reference point O =
 //       origin of the floating base (world origin if there is none), so that the geometric Jacobian
 //       column of ANY descendant frame at x is [v_O + w x (x - O); w].
@@ -94,63 +94,77 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
   double* tl = sm + lay.tl;
   double* ql = sm + lay.ql;
   const int nb = M.nbody;
-  // ---- pass A
+  // pass B ping-pongs between (tl, ql) and (xpos, xquat); start where an even number of swaps ends in x
+  const int R = M.fk_rounds;
+  double* const T_even = (R & 1) ? tl : xpos;
+  double* const T_odd = (R & 1) ? xpos : tl;
+  double* const Q_even = (R & 1) ? ql : xquat;
+  double* const Q_odd = (R & 1) ? xquat : ql;
+  // ---- pass A: local transform of every body (relative to its parent)
   for (int b = lane; b < nb; b += 32) {
-    if (b == 0) { xpos[0] = xpos[1] = xpos[2] = 0; xquat[0] = 1; xquat[1] = xquat[2] = xquat[3] = 0; continue; }
-    const int jadr = mv(M.body_jntadr)[b], jnum = mv(M.body_jntnum)[b];
-    if (jnum == 1 && mv(M.jnt_type)[jadr] == 0) continue;              // free joint: pose comes from q in pass B
-    const double* bpp = mv(M.body_pos) + 3 * b;
-    const double* bqp = mv(M.body_quat) + 4 * b;
-    double t[3] = {bpp[0], bpp[1], bpp[2]}, qq[4] = {bqp[0], bqp[1], bqp[2], bqp[3]};
-    for (int j = jadr; j < jadr + jnum; j++) {
-      const int qa = mv(M.jnt_qposadr)[j], da = mv(M.jnt_dofadr)[j];
-      const double* axp = mv(M.jnt_axis) + 3 * j;
-      const double ax[3] = {axp[0], axp[1], axp[2]};
-      double al[3];
-      qrot(qq, ax, al);                                                 // axis in the parent frame
-      S[6 * da + 3] = al[0]; S[6 * da + 4] = al[1]; S[6 * da + 5] = al[2];
-      const double val = q[qa] - mv(M.qpos0)[qa];
-      if (mv(M.jnt_type)[j] == 2) {                                     // slide
-        t[0] += al[0] * val; t[1] += al[1] * val; t[2] += al[2] * val;
-      } else {                                                          // hinge about the body origin
-        double sh, ch;
-        sincos(0.5 * val, &sh, &ch);
-        const double qj[4] = {ch, sh * ax[0], sh * ax[1], sh * ax[2]};
-        double nq[4];
-        qmul(qq, qj, nq);
-        qq[0] = nq[0]; qq[1] = nq[1]; qq[2] = nq[2]; qq[3] = nq[3];
+    double t[3] = {0, 0, 0}, qq[4] = {1, 0, 0, 0};
+    if (b > 0) {
+      const int jadr = mv(M.body_jntadr)[b], jnum = mv(M.body_jntnum)[b];
+      if (jnum == 1 && mv(M.jnt_type)[jadr] == 0) {                     // free joint: pose straight from q
+        const int qa = mv(M.jnt_qposadr)[jadr];
+        t[0] = q[qa]; t[1] = q[qa + 1]; t[2] = q[qa + 2];
+        qq[0] = q[qa + 3]; qq[1] = q[qa + 4]; qq[2] = q[qa + 5]; qq[3] = q[qa + 6];
+        normalize4(qq);            // qpos may hold any quaternion; everything below needs a rotation
+      } else {
+        const double* bpp = mv(M.body_pos) + 3 * b;
+        const double* bqp = mv(M.body_quat) + 4 * b;
+        t[0] = bpp[0]; t[1] = bpp[1]; t[2] = bpp[2];
+        qq[0] = bqp[0]; qq[1] = bqp[1]; qq[2] = bqp[2]; qq[3] = bqp[3];
+        for (int j = jadr; j < jadr + jnum; j++) {
+          const int qa = mv(M.jnt_qposadr)[j], da = mv(M.jnt_dofadr)[j];
+          const double* axp = mv(M.jnt_axis) + 3 * j;
+          const double ax[3] = {axp[0], axp[1], axp[2]};
+          double al[3];
+          qrot(qq, ax, al);                                             // axis in the parent frame
+          S[6 * da + 3] = al[0]; S[6 * da + 4] = al[1]; S[6 * da + 5] = al[2];
+          const double val = q[qa] - mv(M.qpos0)[qa];
+          if (mv(M.jnt_type)[j] == 2) {                                 // slide
+            t[0] += al[0] * val; t[1] += al[1] * val; t[2] += al[2] * val;
+          } else {                                                      // hinge about the body origin
+            double sh, ch;
+            sincos(0.5 * val, &sh, &ch);
+            const double qj[4] = {ch, sh * ax[0], sh * ax[1], sh * ax[2]};
+            double nq[4];
+            qmul(qq, qj, nq);
+            qq[0] = nq[0]; qq[1] = nq[1]; qq[2] = nq[2]; qq[3] = nq[3];
+          }
+        }
       }
     }
-    tl[3 * b] = t[0]; tl[3 * b + 1] = t[1]; tl[3 * b + 2] = t[2];
-    ql[4 * b] = qq[0]; ql[4 * b + 1] = qq[1]; ql[4 * b + 2] = qq[2]; ql[4 * b + 3] = qq[3];
+    double* T0 = T_even + 3 * b;
+    double* Q0 = Q_even + 4 * b;
+    T0[0] = t[0]; T0[1] = t[1]; T0[2] = t[2];
+    Q0[0] = qq[0]; Q0[1] = qq[1]; Q0[2] = qq[2]; Q0[3] = qq[3];
   }
   __syncwarp();
-  // ---- pass B
-  const int* level_start = mv(M.level_start);
-  const int* level_body = mv(M.level_body);
-  for (int lv = 0; lv < M.nlevel; lv++) {
-    const int beg = level_start[lv], end = level_start[lv + 1];
-    for (int idx = beg + lane; idx < end; idx += 32) {
-      const int b = level_body[idx];
-      const int jadr = mv(M.body_jntadr)[b];
-      double pos[3], quat[4];
-      if (mv(M.body_jntnum)[b] == 1 && mv(M.jnt_type)[jadr] == 0) {    // free joint
-        const int qa = mv(M.jnt_qposadr)[jadr];
-        pos[0] = q[qa]; pos[1] = q[qa + 1]; pos[2] = q[qa + 2];
-        quat[0] = q[qa + 3]; quat[1] = q[qa + 4]; quat[2] = q[qa + 5]; quat[3] = q[qa + 6];
-        normalize4(quat);          // qpos may hold any quaternion; everything below needs a rotation
-      } else {
-        const int p = mv(M.body_parent)[b];
-        const double pq[4] = {xquat[4 * p], xquat[4 * p + 1], xquat[4 * p + 2], xquat[4 * p + 3]};
-        const double lt[3] = {tl[3 * b], tl[3 * b + 1], tl[3 * b + 2]};
-        const double lq[4] = {ql[4 * b], ql[4 * b + 1], ql[4 * b + 2], ql[4 * b + 3]};
-        double t[3];
-        qrot(pq, lt, t);
-        pos[0] = xpos[3 * p] + t[0]; pos[1] = xpos[3 * p + 1] + t[1]; pos[2] = xpos[3 * p + 2] + t[2];
-        qmul(pq, lq, quat);
+  // ---- pass B: pointer jumping.  Before round r a body's transform is relative to its 2^r-th
+  // ancestor (or already to the world); composing it with that ancestor's transform doubles the
+  // reach, so ceil(log2(depth)) rounds over ALL bodies replace `depth` sequential levels.
+  const short* jump = mv(M.fk_jump);
+  for (int r = 0; r < R; r++) {
+    const double* Ti = (r & 1) ? T_odd : T_even;
+    const double* Qi = (r & 1) ? Q_odd : Q_even;
+    double* To = (r & 1) ? T_even : T_odd;
+    double* Qo = (r & 1) ? Q_even : Q_odd;
+    for (int b = lane; b < nb; b += 32) {
+      const int anc2 = jump[r * nb + b];                                // 2^r-th ancestor, -1: already in the world frame
+      double t[3] = {Ti[3 * b], Ti[3 * b + 1], Ti[3 * b + 2]};
+      double qq[4] = {Qi[4 * b], Qi[4 * b + 1], Qi[4 * b + 2], Qi[4 * b + 3]};
+      if (anc2 >= 0) {
+        const double aq[4] = {Qi[4 * anc2], Qi[4 * anc2 + 1], Qi[4 * anc2 + 2], Qi[4 * anc2 + 3]};
+        double rt[3], nq[4];
+        qrot(aq, t, rt);
+        t[0] = Ti[3 * anc2] + rt[0]; t[1] = Ti[3 * anc2 + 1] + rt[1]; t[2] = Ti[3 * anc2 + 2] + rt[2];
+        qmul(aq, qq, nq);
+        qq[0] = nq[0]; qq[1] = nq[1]; qq[2] = nq[2]; qq[3] = nq[3];
       }
-      xpos[3 * b] = pos[0]; xpos[3 * b + 1] = pos[1]; xpos[3 * b + 2] = pos[2];
-      xquat[4 * b] = quat[0]; xquat[4 * b + 1] = quat[1]; xquat[4 * b + 2] = quat[2]; xquat[4 * b + 3] = quat[3];
+      To[3 * b] = t[0]; To[3 * b + 1] = t[1]; To[3 * b + 2] = t[2];
+      Qo[4 * b] = qq[0]; Qo[4 * b + 1] = qq[1]; Qo[4 * b + 2] = qq[2]; Qo[4 * b + 3] = qq[3];
     }
     __syncwarp();
   }
