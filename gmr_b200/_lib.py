@@ -17,7 +17,7 @@ EXPORTS = [
     "gmr_last_error", "gmr_abi_version", "gmr_model_create", "gmr_model_destroy", "gmr_batch_create",
     "gmr_batch_destroy", "gmr_batch_reset", "gmr_batch_set_scale", "gmr_batch_get_state",
     "gmr_batch_set_order", "gmr_batch_launch_info", "gmr_batch_dims", "gmr_batch_step", "gmr_batch_run",
-    "gmr_target_prep", "gmr_fk", "gmr_build_qp", "gmr_qp_solve", "gmr_fk_bodies_f32", "gmr_probe_fma_peak", "gmr_solve_ik",
+    "gmr_target_prep", "gmr_fk", "gmr_build_qp", "gmr_qp_solve", "gmr_fk_bodies_f32", "gmr_probe_fma_peak", "gmr_solve_ik", "gmr_batch_run_host",
 ]
 
 _lib = None
@@ -55,6 +55,7 @@ def lib():
     L.gmr_target_prep.argtypes = [vp, vp, C.c_int, C.c_int, vp]
     L.gmr_fk.argtypes = [vp, vp, vp, vp]
     L.gmr_build_qp.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp, vp]
+    L.gmr_batch_run_host.argtypes = [vp, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     L.gmr_solve_ik.argtypes = [vp, C.c_int, vp, vp, vp]
     L.gmr_qp_solve.argtypes = [C.c_int, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]
     L.gmr_fk_bodies_f32.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, vp]

@@ -46,6 +46,12 @@ struct gmr_batch {
   int warps_per_cta = 4, grid = 0;
   size_t smem_bytes = 0;          // per-warp blocks only (stage kernels)
   size_t clip_smem_bytes = 0;     // + the staged model of the fused kernel
+  // host-buffer pipeline (gmr_batch_run_host)
+  void* stage_in = nullptr; size_t stage_in_bytes = 0;
+  void* stage_out = nullptr; size_t stage_out_bytes = 0;
+  int* stage_T = nullptr;
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
   bool smem_model = false;
 };
 
@@ -507,6 +513,8 @@ extern "C" int gmr_batch_destroy(gmr_batch* b) {
   cudaSetDevice(b->device);
   cudaFree(b->d_models); cudaFree(b->d_q); cudaFree(b->d_scale); cudaFree(b->d_counter);
   cudaFree(b->d_model_of); cudaFree(b->d_order);
+  cudaFree(b->stage_in); cudaFree(b->stage_out); cudaFree(b->stage_T);
+  if (b->s_in) { cudaStreamDestroy(b->s_in); cudaStreamDestroy(b->s_out); for (int i = 0; i < 3; i++) cudaEventDestroy(b->ev[i]); }
   cudaSetDevice(prev);
   delete b;
   return 0;
@@ -584,7 +592,7 @@ extern "C" int gmr_batch_launch_info(const gmr_batch* b, int32_t* grid, int32_t*
 }
 
 static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const int32_t* T_of_dev, int T_max, int to_ground,
-                        double* qpos_out, double* scaled_out, const gmr_diag* diag) {
+                        double* qpos_out, double* scaled_out, const gmr_diag* diag, int t_begin = 0, int t_end = -1) {
   if (!b || !human_dev) return fail(-1, "null argument");
   if (dtype != GMR_F32 && dtype != GMR_F64) return fail(-1, "human_dtype must be GMR_F32 or GMR_F64");
   if (T_max < 1) return fail(-1, "T_max must be >= 1");
@@ -593,6 +601,7 @@ static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const in
   a.models = b->d_models; a.model_of = b->d_model_of;
   a.human = human_dev; a.human_frame_stride = (long long)b->h_max * 7; a.human_inst_stride = a.human_frame_stride * T_max;
   a.T_of = T_of_dev; a.T_max = T_max; a.to_ground = to_ground;
+  a.t_begin = t_begin; a.t_end = t_end < 0 ? T_max : std::min(t_end, T_max);
   a.scale = b->d_scale; a.s_max = b->s_max; a.q_state = b->d_q; a.nq_max = b->nq_max;
   a.qpos_out = qpos_out; a.scaled_out = scaled_out;
   a.err_out = diag ? diag->err_dev : nullptr; a.iters_out = diag ? diag->iters_dev : nullptr; a.nfact_out = diag ? diag->nfact_dev : nullptr;
@@ -622,6 +631,69 @@ extern "C" int gmr_batch_step(gmr_batch* b, const void* human_dev, int human_dty
 extern "C" int gmr_batch_run(gmr_batch* b, const void* human_dev, int human_dtype, const int32_t* T_of_instance_dev,
                              int T_max, int offset_to_ground, double* qpos_out_dev, const gmr_diag* diag) {
   return launch_clips(b, human_dev, human_dtype, T_of_instance_dev, T_max, offset_to_ground, qpos_out_dev, nullptr, diag);
+}
+
+// Host-buffer form of gmr_batch_run: the dataset drivers' loop (scripts/bvh_to_robot_dataset.py:96-113)
+// for B clips held in HOST memory.  The clips are cut into n_chunks frame ranges; range k+1 is copied
+// to the device (strided 2-D copy, one row per clip) while range k is being retargeted and range k-1
+// is copied back, on three streams chained by events.  The warm start crosses chunk boundaries through
+// the batch state, so the result is bit-identical to one launch over the whole clips.
+extern "C" int gmr_batch_run_host(gmr_batch* b, const void* human_host, int human_dtype, const int32_t* T_of_host,
+                                  int T_max, int offset_to_ground, int cold_start, int n_chunks, double* qpos_out_host) {
+  if (!b || !human_host || !qpos_out_host) return fail(-1, "null argument");
+  if (human_dtype != GMR_F32 && human_dtype != GMR_F64) return fail(-1, "human_dtype must be GMR_F32 or GMR_F64");
+  if (T_max < 1) return fail(-1, "T_max must be >= 1");
+  DevGuard g(b->device);
+  const size_t esz = human_dtype == GMR_F32 ? 4 : 8;
+  const size_t in_row = (size_t)T_max * b->h_max * 7 * esz, out_row = (size_t)T_max * b->nq_max * sizeof(double);
+  const size_t in_bytes = in_row * b->B, out_bytes = out_row * b->B;
+  if (b->stage_in_bytes < in_bytes) {
+    if (b->stage_in) cudaFree(b->stage_in);
+    b->stage_in = nullptr; b->stage_in_bytes = 0;
+    CU(cudaMalloc(&b->stage_in, in_bytes));
+    b->stage_in_bytes = in_bytes;
+  }
+  if (b->stage_out_bytes < out_bytes) {
+    if (b->stage_out) cudaFree(b->stage_out);
+    b->stage_out = nullptr; b->stage_out_bytes = 0;
+    CU(cudaMalloc(&b->stage_out, out_bytes));
+    b->stage_out_bytes = out_bytes;
+  }
+  if (T_of_host) {
+    if (!b->stage_T) CU(cudaMalloc(&b->stage_T, sizeof(int) * (size_t)b->B));
+    CU(cudaMemcpyAsync(b->stage_T, T_of_host, sizeof(int) * (size_t)b->B, cudaMemcpyHostToDevice, b->stream));
+  }
+  if (!b->s_in) {
+    CU(cudaStreamCreateWithFlags(&b->s_in, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&b->s_out, cudaStreamNonBlocking));
+    for (int i = 0; i < 3; i++) CU(cudaEventCreateWithFlags(&b->ev[i], cudaEventDisableTiming));
+  }
+  n_chunks = std::max(1, std::min(n_chunks, T_max));
+  if (cold_start) { int rc = gmr_batch_reset(b, nullptr); if (rc) return rc; }
+  // the copy streams start after everything already queued on the batch stream (buffer reuse)
+  CU(cudaEventRecord(b->ev[2], b->stream));
+  CU(cudaStreamWaitEvent(b->s_in, b->ev[2], 0));
+  CU(cudaStreamWaitEvent(b->s_out, b->ev[2], 0));
+  const size_t in_frame = (size_t)b->h_max * 7 * esz, out_frame = (size_t)b->nq_max * sizeof(double);
+  for (int k = 0; k < n_chunks; k++) {
+    const int t0 = (int)((long long)T_max * k / n_chunks), t1 = (int)((long long)T_max * (k + 1) / n_chunks);
+    if (t1 <= t0) continue;
+    CU(cudaMemcpy2DAsync((char*)b->stage_in + t0 * in_frame, in_row, (const char*)human_host + t0 * in_frame, in_row,
+                         (t1 - t0) * in_frame, b->B, cudaMemcpyHostToDevice, b->s_in));
+    CU(cudaEventRecord(b->ev[0], b->s_in));
+    CU(cudaStreamWaitEvent(b->stream, b->ev[0], 0));
+    int rc = launch_clips(b, b->stage_in, human_dtype, T_of_host ? b->stage_T : nullptr, T_max, offset_to_ground,
+                          (double*)b->stage_out, nullptr, nullptr, t0, t1);
+    if (rc) return rc;
+    CU(cudaEventRecord(b->ev[1], b->stream));
+    CU(cudaStreamWaitEvent(b->s_out, b->ev[1], 0));
+    CU(cudaMemcpy2DAsync((char*)qpos_out_host + t0 * out_frame, out_row, (const char*)b->stage_out + t0 * out_frame, out_row,
+                         (t1 - t0) * out_frame, b->B, cudaMemcpyDeviceToHost, b->s_out));
+  }
+  // the batch stream is done when the last copy-back is
+  CU(cudaEventRecord(b->ev[2], b->s_out));
+  CU(cudaStreamWaitEvent(b->stream, b->ev[2], 0));
+  return 0;
 }
 
 // ---------------------------------------------------------------- stage entry points

@@ -23,6 +23,7 @@ struct RunArgs {
   long long human_frame_stride;  // elements between frames
   const int* T_of;               // [B] or null
   int T_max;
+  int t_begin, t_end;            // frames [t_begin, min(T, t_end)) of every clip are processed by this launch
   int to_ground;
   const double* scale;           // [B, s_max]
   int s_max;
@@ -117,9 +118,9 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, GMR_MIN_CTAS) clip_kernel(con
       if (slot >= a.B) { drained = true; break; }
       s.inst = a.order ? a.order[slot] : slot;
       if (!SM) mv.m = a.models + (a.model_of ? a.model_of[s.inst] : 0);
-      s.T = a.T_of ? min(a.T_of[s.inst], a.T_max) : a.T_max;
-      s.t = 0;
-      if (s.T <= 0) { s.inst = -1; continue; }
+      s.T = min(a.T_of ? min(a.T_of[s.inst], a.T_max) : a.T_max, a.t_end);
+      s.t = a.t_begin;
+      if (s.T <= s.t) { s.inst = -1; continue; }
       const double* qs = a.q_state + (size_t)s.inst * a.nq_max;
       for (int i = lane; i < mv.M().nq; i += 32) sm[lay.q + i] = qs[i];
       __syncwarp();

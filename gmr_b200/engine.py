@@ -181,28 +181,38 @@ class BatchedRetargeter:
                                             C.byref(d) if d is not None else None), "gmr_batch_run")
         return (qpos, dout) if diag else qpos
 
-    def retarget_clips_host(self, human_host, qpos_host=None, T_of=None, offset_to_ground=False):
+    def retarget_clips_host(self, human_host, qpos_host=None, T_of=None, offset_to_ground=False, cold_start=True,
+                            n_chunks: int = 4):
         """Whole clips from HOST buffers to a HOST result: the call the dataset drivers make
         (scripts/bvh_to_robot_dataset.py:84-113: new retargeter per clip -> per-frame retarget ->
-        stacked qpos).  human_host [B,T,h,7] float32/float64 torch CPU tensor (pinned for full copy
-        speed); returns qpos [B,T,nq_max] float64 on the host (pinned, reused between calls when
-        qpos_host is given).  Cold start per clip like the reference; asynchronous on the batch's
-        stream - synchronise the stream (or call .cpu-side sync) before reading the result."""
+        stacked qpos).  human_host [B,T,h,7] float32/float64 torch CPU tensor (pinned for full overlap);
+        returns qpos [B,T,nq_max] float64 on the host (pinned; pass qpos_host to reuse it).
+        One C-ABI call (gmr_batch_run_host): the frames are cut into n_chunks ranges and H2D, retargeting
+        and D2H of consecutive ranges overlap on three streams; the result is bit-identical to run().
+        Asynchronous on the batch's stream - synchronise it before reading the result."""
         human_host = torch.as_tensor(human_host)
         if human_host.is_cuda:
             raise ValueError("retarget_clips_host takes host buffers; use run() for device tensors")
+        if human_host.dtype not in (torch.float32, torch.float64):
+            human_host = human_host.double()
+        human_host = human_host.contiguous()
+        if human_host.dim() != 4 or human_host.shape[0] != self.B or human_host.shape[2] != self.h_max or human_host.shape[3] != 7:
+            raise ValueError(f"human stream must be [B={self.B},T,h={self.h_max},7], got {tuple(human_host.shape)}")
         T = human_host.shape[1]
-        key = (tuple(human_host.shape), human_host.dtype)
-        if getattr(self, "_stage_key", None) != key:
-            self._stage_in = torch.empty(human_host.shape, dtype=human_host.dtype, device=self.tdev)
-            self._stage_out = torch.empty((self.B, T, self.nq_max), dtype=torch.float64, device=self.tdev)
-            self._stage_key = key
         if qpos_host is None:
-            qpos_host = torch.empty((self.B, T, self.nq_max), dtype=torch.float64, pin_memory=True)
-        self._stage_in.copy_(human_host, non_blocking=True)
-        self.reset()
-        self.run(self._stage_in, T_of=T_of, offset_to_ground=offset_to_ground, out=self._stage_out)
-        qpos_host.copy_(self._stage_out, non_blocking=True)
+            qpos_host = torch.zeros((self.B, T, self.nq_max), dtype=torch.float64, pin_memory=True)
+        if qpos_host.dtype != torch.float64 or tuple(qpos_host.shape) != (self.B, T, self.nq_max) or not qpos_host.is_contiguous():
+            raise ValueError("qpos_host must be a contiguous float64 [B,T,nq_max] host tensor")
+        t_of = None
+        if T_of is not None:
+            t_of = np.ascontiguousarray(T_of, np.int32)
+            if t_of.shape != (self.B,):
+                raise ValueError("T_of must have one entry per clip")
+        _lib.check(_lib.lib().gmr_batch_run_host(
+            self._h, C.c_void_p(human_host.data_ptr()), F32 if human_host.dtype == torch.float32 else F64,
+            None if t_of is None else t_of.ctypes.data_as(C.c_void_p), T, int(bool(offset_to_ground)), int(bool(cold_start)),
+            int(n_chunks), C.c_void_p(qpos_host.data_ptr())), "gmr_batch_run_host")
+        self._keep_host = (human_host, qpos_host)      # alive until the stream has consumed them
         return qpos_host
 
     def step(self, human, offset_to_ground=False, diag=False, want_scaled=False):

@@ -141,6 +141,16 @@ int gmr_batch_run(gmr_batch* b, const void* human_dev, int human_dtype,
                   const int32_t* T_of_instance_dev, int T_max, int offset_to_ground,
                   double* qpos_out_dev, const gmr_diag* diag);
 
+/* gmr_batch_run for clips held in HOST memory (pinned for full overlap): what the dataset drivers
+ * call per folder (scripts/bvh_to_robot_dataset.py:96-113, smplx_to_robot_dataset.py:83-104).
+ * human_host [B,T_max,h,7], T_of_host [B] or NULL, qpos_out_host [B,T_max,nq_max].  The frames are
+ * cut into n_chunks ranges; H2D of range k+1, retargeting of range k and D2H of range k-1 overlap.
+ * cold_start != 0 resets every instance to qpos0 first (a new retargeter object per clip).
+ * Asynchronous: synchronise the batch's stream before reading qpos_out_host. */
+int gmr_batch_run_host(gmr_batch* b, const void* human_host, int human_dtype, const int32_t* T_of_host,
+                       int T_max, int offset_to_ground, int cold_start, int n_chunks,
+                       double* qpos_out_host);
+
 /* --- stage entry points (same device code as the fused path; used for per-stage parity) --- */
 /* Kernel 1: scale + offset (+ground) -> scaled_out_dev [B,s,7] */
 int gmr_target_prep(gmr_batch* b, const void* human_dev, int human_dtype, int offset_to_ground,

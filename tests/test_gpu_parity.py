@@ -222,6 +222,26 @@ def test_step_equals_run_and_state_persists():
     np.testing.assert_array_equal(br.state().cpu().numpy(), full[:, -1])
 
 
+def test_host_pipeline_is_bit_identical_to_one_launch():
+    """gmr_batch_run_host: chunked H2D / retarget / D2H over three streams == one launch on resident data."""
+    import torch
+    B, T = 40, 37
+    m, t, dm, br, human, heights = _setup("bvh", "unitree_g1", B, T)
+    full = br.run(human).cpu().numpy()
+    T_of = np.random.default_rng(1).integers(1, T + 1, size=B).astype(np.int32)
+    for chunks in (1, 3, 37):
+        hh = torch.from_numpy(human).pin_memory()
+        out = br.retarget_clips_host(hh, n_chunks=chunks)
+        torch.cuda.synchronize()
+        np.testing.assert_array_equal(out.numpy(), full)
+    br.reset()
+    ragged = br.run(human, T_of=T_of).cpu().numpy()
+    out = br.retarget_clips_host(torch.from_numpy(human), T_of=T_of, n_chunks=4)     # pageable host memory works too
+    torch.cuda.synchronize()
+    for b in range(B):
+        np.testing.assert_array_equal(out.numpy()[b, :T_of[b]], ragged[b, :T_of[b]])
+
+
 def test_ragged_lengths_and_order():
     from gmr_b200 import synth
     from oracle import oracle as oc
