@@ -1,0 +1,91 @@
+#!/usr/bin/env python
+"""Drop-in for the reference's scripts/bvh_to_robot_dataset.py (same flags, same output pickles), with the
+per-file / per-frame Python loop replaced by ONE batched launch over every clip of the folder.
+
+  python scripts/bvh_to_robot_dataset.py --src_folder <bvh or npz folder> --tgt_folder <out> --robot unitree_g1 [--override]
+
+Inputs: *.bvh (parsed by the reference's own loader, utils/lafan1.py:8-71 - text parsing is outside the
+hot path and reused as is; needs GMR_ROOT=<GMR checkout>) or *.npz frame streams
+{frames [T,h,7] (pos xyz, quat wxyz), names [h], height, fps} as written by tools/bvh_to_npz.py.
+Outputs: <tgt_folder>/<relative path>.pkl with {root_pos, root_rot (xyzw), dof_pos, local_body_pos, fps,
+link_body_list} (reference :144-156); existing outputs are skipped unless --override (:70-72).
+"""
+import argparse
+import os
+import sys
+import types
+
+import numpy as np
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+from gmr_b200 import dataset, params  # noqa: E402
+
+
+def reference_bvh_loader():
+    root = params.get_gmr_root()
+    if root is None:
+        raise SystemExit("*.bvh input needs the reference's BVH parser: export GMR_ROOT=<GMR checkout> "
+                         "(or convert to *.npz frame streams first)")
+    # import the loader sub-package without running the reference's package __init__ (which imports mink/mujoco)
+    pkg = types.ModuleType("general_motion_retargeting")
+    pkg.__path__ = [os.path.join(str(root), "general_motion_retargeting")]
+    sys.modules.setdefault("general_motion_retargeting", pkg)
+    from general_motion_retargeting.utils.lafan1 import load_lafan1_file
+    return load_lafan1_file
+
+
+def frames_to_array(frames, names=None):
+    """list of {body: (pos, quat_wxyz)} -> ([T,h,7], names)"""
+    if names is None:
+        names = list(frames[0].keys())
+    arr = np.zeros((len(frames), len(names), 7), np.float32)
+    for t, fr in enumerate(frames):
+        for k, n in enumerate(names):
+            arr[t, k, :3], arr[t, k, 3:] = fr[n][0], fr[n][1]
+    return arr, names
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--src_folder", required=True, type=str, help="Folder containing BVH motion files to load.")
+    ap.add_argument("--tgt_folder", default="../../motion_data/LAFAN1_g1_gmr", help="Folder to save the retargeted motion files.")
+    ap.add_argument("--robot", default="unitree_g1")
+    ap.add_argument("--override", default=False, action="store_true")
+    ap.add_argument("--target_fps", default=30, type=int)
+    ap.add_argument("--device", default=0, type=int)
+    args = ap.parse_args()
+
+    todo = dataset.pending_files(args.src_folder, args.tgt_folder, (".bvh", ".npz"), args.override)
+    if not todo:
+        print("Nothing to do.")
+        return
+    load_bvh = None
+    clips, heights, names, fps, kept = [], [], None, [], []
+    for src, tgt in todo:
+        try:
+            if src.lower().endswith(".npz"):
+                z = np.load(src, allow_pickle=False)
+                arr, nm, hgt, f = z["frames"].astype(np.float32), [str(x) for x in z["names"]], float(z["height"]), float(z["fps"])
+            else:
+                load_bvh = load_bvh or reference_bvh_loader()
+                frames, hgt = load_bvh(src)
+                arr, nm = frames_to_array(frames, names)
+                f = float(args.target_fps)
+        except Exception as e:                           # reference: print and continue (:75-80)
+            print(f"Error loading {src}: {e}")
+            continue
+        if names is None:
+            names = nm
+        elif nm != names:
+            print(f"Skipping {src}: body list differs from the first file's")
+            continue
+        clips.append(arr); heights.append(hgt); fps.append(f); kept.append(tgt)
+    motions = dataset.retarget_clips("bvh", args.robot, clips, heights=heights, human_names=names, fps=fps,
+                                     height_adjust=False, root_origin_offset=False, device=args.device)
+    for tgt, m in zip(kept, motions):
+        dataset.save_motion(tgt, m)
+    print("Done. saved to ", args.tgt_folder)
+
+
+if __name__ == "__main__":
+    main()

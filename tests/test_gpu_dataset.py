@@ -1,0 +1,78 @@
+"""Dataset-driver tail (gmr_b200/dataset.py) against a numpy restatement of the reference drivers' post-processing
+(scripts/smplx_to_robot_dataset.py:93-146) and the structural checks of the reference's scripts/smoke_test.py."""
+import os
+import pickle
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _clips(src, robot, lengths, seed=9):
+    from gmr_b200 import model_pack, synth
+    m, t = model_pack.build_tables(src, robot)
+    human, heights, names = synth.synth_human_clips(m, t, src, B=len(lengths), T=max(lengths), seed=seed)
+    return m, t, [human[i, :n] for i, n in enumerate(lengths)], heights, names, human
+
+
+@pytest.mark.parametrize("adjust", [False, True])
+def test_motion_dicts_match_the_reference_tail(adjust, tmp_path):
+    import torch
+    from gmr_b200 import dataset, synth
+    from gmr_b200.engine import DeviceModel
+    from oracle import oracle as oc
+    lengths = [17, 5, 30, 1, 22]
+    m, t, clips, heights, names, human = _clips("bvh", "unitree_g1", lengths)
+    motions = dataset.retarget_clips("bvh", "unitree_g1", clips, heights=heights, human_names=names, fps=30,
+                                     height_adjust=adjust, root_origin_offset=adjust)
+    dm = DeviceModel.load("bvh", "unitree_g1", names)
+    ref = oc.run_clips(dm.desc, human, T_of=np.array(lengths, np.int32), scale=synth.clip_scales(t, heights), nthreads=4)["qpos"]
+    assert len(motions) == len(lengths)
+    for i, (mo, n) in enumerate(zip(motions, lengths)):
+        # smoke_test.py:19-72 structural checks
+        assert set(mo) == {"fps", "root_pos", "root_rot", "dof_pos", "local_body_pos", "link_body_list"}
+        assert mo["root_pos"].shape == (n, 3) and mo["root_rot"].shape == (n, 4) and mo["dof_pos"].shape == (n, m.nq - 7)
+        assert mo["local_body_pos"].shape == (n, m.nbody - 1, 3) and mo["local_body_pos"].dtype == np.float32
+        assert len(mo["link_body_list"]) == m.nbody - 1 and mo["fps"] == 30
+        norms = np.linalg.norm(mo["root_rot"], axis=-1)
+        assert (norms > 0.5).all() and (norms < 1.5).all()
+        q = ref[i, :n]
+        np.testing.assert_allclose(mo["root_rot"], q[:, [4, 5, 6, 3]], atol=1e-7)           # xyzw
+        np.testing.assert_allclose(mo["dof_pos"], q[:, 7:], atol=1e-7)
+        # FK tail with identity root == golden-tested kernel on the oracle's dof_pos
+        ident = torch.zeros((n, 4), device="cuda"); ident[:, 3] = 1
+        lbp, _ = dm.fk_bodies_f32(torch.zeros((n, 3), device="cuda"), ident, torch.from_numpy(q[:, 7:]).cuda().float(), want_rot=False)
+        np.testing.assert_allclose(mo["local_body_pos"], lbp.cpu().numpy(), atol=1e-5)
+        rp = q[:, :3].copy()
+        if adjust:
+            bp, _ = dm.fk_bodies_f32(torch.from_numpy(q[:, :3]).cuda().float(), torch.from_numpy(q[:, [4, 5, 6, 3]]).cuda().float(),
+                                     torch.from_numpy(q[:, 7:]).cuda().float(), want_rot=False)
+            rp[:, 2] -= float(bp[..., 2].min().item())
+            rp[:, :2] -= rp[0, :2].copy()
+            assert abs(mo["root_pos"][0, 0]) < 1e-12 and abs(mo["root_pos"][0, 1]) < 1e-12
+        np.testing.assert_allclose(mo["root_pos"], rp, atol=2e-6)
+    p = tmp_path / "a" / "b.pkl"
+    dataset.save_motion(str(p), motions[0])
+    back = pickle.load(open(p, "rb"))
+    np.testing.assert_array_equal(back["dof_pos"], motions[0]["dof_pos"])
+
+
+def test_pending_files_skip_logic(tmp_path):
+    from gmr_b200 import dataset
+    src, tgt = tmp_path / "src", tmp_path / "tgt"
+    (src / "sub").mkdir(parents=True)
+    for n in ("b.bvh", "a.bvh", "sub/c.npz", "notes.txt"):
+        (src / n).write_text("x")
+    (tgt / "sub").mkdir(parents=True)
+    (tgt / "a.pkl").write_text("done")
+    todo = dataset.pending_files(str(src), str(tgt), (".bvh", ".npz"))
+    assert [os.path.relpath(s, src) for s, _ in todo] == ["b.bvh", "sub/c.npz"]
+    assert len(dataset.pending_files(str(src), str(tgt), (".bvh", ".npz"), override=True)) == 3
+
+
+def test_robot_without_floating_base_is_refused():
+    from gmr_b200 import dataset
+    m, t, clips, heights, names, human = _clips("smplx", "galaxea_r1pro", [3, 4])
+    with pytest.raises(ValueError):
+        dataset.retarget_clips("smplx", "galaxea_r1pro", clips, heights=heights, human_names=names)
