@@ -40,6 +40,7 @@ struct gmr_batch {
   double* d_q = nullptr;        // [B, nq_max]
   double* d_scale = nullptr;    // [B, s_max]
   int* d_counter = nullptr;
+  int* d_done = nullptr;        // [B] per-clip range flags of the current launch
   int* d_order = nullptr;
   int nq_max = 0, s_max = 0, h_max = 0, nbody_max = 0, nv_max = 0, m_max = 0, nnz_max = 0;
   Lay lay{};
@@ -448,14 +449,13 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   alloc((void**)&b->d_q, sizeof(double) * (size_t)B * b->nq_max);
   alloc((void**)&b->d_scale, sizeof(double) * (size_t)B * b->s_max);
   alloc((void**)&b->d_counter, sizeof(int));
+  alloc((void**)&b->d_done, sizeof(int) * (size_t)B);
   if (model_of_instance) alloc((void**)&b->d_model_of, sizeof(int) * (size_t)B);
   if (e == cudaSuccess) e = cudaMemcpy(b->d_models, hm.data(), sizeof(DevModel) * n_models, cudaMemcpyHostToDevice);
   if (e == cudaSuccess && model_of_instance)
     e = cudaMemcpy(b->d_model_of, model_of_instance, sizeof(int) * (size_t)B, cudaMemcpyHostToDevice);
-  // launch geometry: one instance per warp; CTAs of 4 warps that run the tick loop in lockstep
-  // (shared instruction stream), as many CTAs per SM as shared memory and registers allow
-  // (measured: 3 x 4 warps beats 1 x 12 by 12 %).  Single-model batches stage the model tables in
-  // shared memory (one copy per CTA).
+  // launch geometry: one instance per warp, warps independent of each other (no CTA-wide barrier in the
+  // tick loop).  Single-model batches stage the model tables in shared memory (one copy per CTA).
   const size_t per_warp = sizeof(double) * (size_t)b->lay.total;
   int dev_smem = 0, sms = 0;
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, b->device);
@@ -511,7 +511,7 @@ extern "C" int gmr_batch_destroy(gmr_batch* b) {
   int prev = 0;
   cudaGetDevice(&prev);
   cudaSetDevice(b->device);
-  cudaFree(b->d_models); cudaFree(b->d_q); cudaFree(b->d_scale); cudaFree(b->d_counter);
+  cudaFree(b->d_models); cudaFree(b->d_q); cudaFree(b->d_scale); cudaFree(b->d_counter); cudaFree(b->d_done);
   cudaFree(b->d_model_of); cudaFree(b->d_order);
   cudaFree(b->stage_in); cudaFree(b->stage_out); cudaFree(b->stage_T);
   if (b->s_in) { cudaStreamDestroy(b->s_in); cudaStreamDestroy(b->s_out); for (int i = 0; i < 3; i++) cudaEventDestroy(b->ev[i]); }
@@ -606,10 +606,11 @@ static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const in
   a.qpos_out = qpos_out; a.scaled_out = scaled_out;
   a.err_out = diag ? diag->err_dev : nullptr; a.iters_out = diag ? diag->iters_dev : nullptr; a.nfact_out = diag ? diag->nfact_dev : nullptr;
   a.counter = b->d_counter; a.order = b->d_order; a.B = b->B; a.lay = b->lay;
-  a.sync_period = 2;
-  if (const char* ev = getenv("GMR_DEBUG_SYNC_PERIOD")) a.sync_period = std::max(1, atoi(ev));
-  a.group_warps = 2;
-  if (const char* ev = getenv("GMR_DEBUG_GROUP_WARPS")) a.group_warps = std::max(1, atoi(ev));
+  a.unit_frames = 32;
+  if (const char* ev = getenv("GMR_DEBUG_UNIT_FRAMES")) a.unit_frames = std::max(1, atoi(ev));
+  a.n_ranges = std::max(1, (a.t_end - a.t_begin + a.unit_frames - 1) / a.unit_frames);
+  a.done = b->d_done;
+  CU(cudaMemsetAsync(b->d_done, 0, sizeof(int) * (size_t)b->B, b->stream));
   CU(cudaMemsetAsync(b->d_counter, 0, sizeof(int), b->stream));
   const dim3 grid(b->grid), block(32 * b->warps_per_cta);
   if (b->smem_model) {

@@ -37,8 +37,9 @@ struct RunArgs {
   int* counter;                  // work queue head
   const int* order;              // [B] or null
   int B;
-  int sync_period;               // lockstep-group barrier at the top of every sync_period-th tick
-  int group_warps;               // warps per lockstep group (named barrier 1 + group index)
+  int unit_frames;               // frames per work unit (a clip is handed out in ranges of this many frames)
+  int n_ranges;                  // ceil((t_end - t_begin) / unit_frames)
+  int* done;                     // [B] ranges of each clip completed in this launch (zeroed by the host)
   Lay lay;
 };
 
@@ -52,14 +53,6 @@ struct Slot {
   double curr;                   // curr_error of the reference loop
   unsigned long long act_lo, act_hi;   // active set of the previous solve of this frame/stage
 };
-
-// OR-reduction + barrier over one lockstep group of the CTA (named barrier `id`, `nthreads` threads)
-__device__ __forceinline__ bool group_barrier_or(int id, int nthreads, bool pred) {
-  int r;
-  asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.s32 q, %3, 0;\n\tbarrier.red.or.pred p, %1, %2, q;\n\tselp.s32 %0, 1, 0, p;\n\t}"
-               : "=r"(r) : "r"(id), "r"(nthreads), "r"((int)pred) : "memory");
-  return r != 0;
-}
 
 __device__ __forceinline__ int next_stage(const DevModel& M, int stage) {
   stage++;
@@ -103,32 +96,38 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, GMR_MIN_CTAS) clip_kernel(con
   Slot s;
   s.inst = -1; s.t = s.T = 0; s.stage = 2; s.it = 0; s.nfact = 0; s.curr = 0; s.act_lo = s.act_hi = 0;
   s.new_frame = s.fresh = s.need_fk = false;
-  bool drained = false;
-  int tick = 0;
-  // lockstep group: `group_warps` consecutive warps re-converge every sync_period ticks so that they
-  // walk the instruction stream together; groups (and CTAs) drift freely against each other
-  const int nwarps = blockDim.x >> 5, grp = warp / a.group_warps;
-  const int grp_threads = 32 * min(a.group_warps, nwarps - grp * a.group_warps);
+  int range = 0;
+  const int n_units = a.n_ranges * a.B;
   for (;;) {
-    // ---- warps without an instance pull the next clip from the queue
-    while (s.inst < 0 && !drained) {
+    // ---- a warp without work pulls the next unit from the queue.  A unit is one range of
+    // `unit_frames` frames of one clip; units are handed out range-major (range 0 of every clip, then
+    // range 1, ...), so the queue balances the SMs at the granularity of a few frames and the tail of
+    // the launch is a unit, not a clip.  The warm start crosses units through q_state: the warp that
+    // takes range k of a clip waits (normally not at all: range k-1 was handed out B units earlier)
+    // until range k-1 is flagged done.  Warps never wait on one another in any other way.
+    while (s.inst < 0) {
       int slot = 0;
       if (lane == 0) slot = atomicAdd(a.counter, 1);
       slot = __shfl_sync(GMR_FULL, slot, 0);
-      if (slot >= a.B) { drained = true; break; }
-      s.inst = a.order ? a.order[slot] : slot;
-      if (!SM) mv.m = a.models + (a.model_of ? a.model_of[s.inst] : 0);
-      s.T = min(a.T_of ? min(a.T_of[s.inst], a.T_max) : a.T_max, a.t_end);
-      s.t = a.t_begin;
-      if (s.T <= s.t) { s.inst = -1; continue; }
-      const double* qs = a.q_state + (size_t)s.inst * a.nq_max;
-      for (int i = lane; i < mv.M().nq; i += 32) sm[lay.q + i] = qs[i];
+      if (slot >= n_units) return;
+      range = slot / a.B;
+      const int c = slot - range * a.B;
+      const int inst = a.order ? a.order[c] : c;
+      const int T_inst = min(a.T_of ? min(a.T_of[inst], a.T_max) : a.T_max, a.t_end);
+      const int t0 = a.t_begin + range * a.unit_frames;
+      if (t0 >= T_inst) continue;                      // the clip ended before this range
+      if (!SM) mv.m = a.models + (a.model_of ? a.model_of[inst] : 0);
+      if (range > 0) {
+        if (lane == 0) { while (*((volatile int*)a.done + inst) < range) { } }
+        __syncwarp();
+        __threadfence();
+      }
+      s.inst = inst; s.t = t0; s.T = min(T_inst, t0 + a.unit_frames);
+      const double* qs = a.q_state + (size_t)inst * a.nq_max;
+      for (int i = lane; i < mv.M().nq; i += 32) sm[lay.q + i] = __ldcg(qs + i);     // written by another SM: bypass L1
       __syncwarp();
       s.new_frame = true; s.need_fk = true;
     }
-    if (tick % a.sync_period == 0) { if (!group_barrier_or(1 + grp, grp_threads, s.inst >= 0)) break; }
-    tick++;
-    if (s.inst < 0) continue;
     const DevModel& M = mv.M();
     // ---- Kernel 2: FK (q changed: integrate of the previous tick, or a new clip)
     if (s.need_fk) { stage_fk(mv, lay, sm, lane); s.need_fk = false; }
@@ -175,7 +174,9 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, GMR_MIN_CTAS) clip_kernel(con
       if (++s.t < s.T) { s.new_frame = true; continue; }
       double* qs = a.q_state + (size_t)s.inst * a.nq_max;
       for (int i = lane; i < M.nq; i += 32) qs[i] = sm[lay.q + i];
+      __threadfence();
       __syncwarp();
+      if (lane == 0) *((volatile int*)a.done + s.inst) = range + 1;      // release the next range of this clip
       s.inst = -1;
       break;
     }
