@@ -52,7 +52,8 @@ def parse_args():
     ap.add_argument("--frames", type=int, default=300)
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--e2e-chunks", type=int, default=4, help="frame ranges of the host pipeline (gmr_batch_run_host)")
+    ap.add_argument("--e2e-chunks", type=int, default=0,
+                    help="gmr_batch_run_host mode: 0 = zero-copy on the pinned host buffers, k >= 1 = k staged frame ranges")
     return ap.parse_args()
 
 
@@ -336,7 +337,10 @@ def run_b200(args):
                        "synth_seconds": round(t_synth, 1)},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": human_host.numel() * 4 * world,
                     "d2h_bytes_per_step": qpos_host.numel() * 8 * world, "ms_per_step": ms_e2e / K,
-                    "api": f"BatchedRetargeter.retarget_clips_host -> gmr_batch_run_host (pinned host in, pinned host out; {args.e2e_chunks} frame ranges, H2D / retarget / D2H overlapped on 3 streams)"},
+                    "api": "BatchedRetargeter.retarget_clips_host -> gmr_batch_run_host, pinned host in / pinned host out; " + (
+                        "zero-copy: the kernel's warps pull each frame over PCIe from the pinned input and push each qpos row to the pinned output inside the one launch (no device staging)"
+                        if args.e2e_chunks == 0 else
+                        f"{args.e2e_chunks} frame ranges, H2D / retarget / D2H overlapped on 3 streams through device staging")},
             "gpu_launches": 2 * K, "gpu_launches_note": "per step: fill_rows_kernel (reset to qpos0) + clip_kernel",
             "clocks": clk, "roofline": roofline,
             "convergence": {"iters_per_frame": iters_per_frame, "frames_hitting_max_iter": hit_max,

@@ -397,7 +397,7 @@ extern "C" int gmr_model_destroy(gmr_model* m) {
 }
 
 // ---------------------------------------------------------------- batch
-static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz) {
+static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h) {
   Lay L{};
   int o = 0;
   auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };   // keep 16-byte alignment
@@ -407,6 +407,7 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz) {
   L.K = take(21 * m); L.g = take(6 * m);
   L.tl = L.K; L.ql = L.tl + ((3 * nbody + 1) & ~1);          // FK local transforms alias K/g
   o = std::max(o, L.ql + ((4 * nbody + 1) & ~1));
+  o = std::max(o, (L.K + 7 * h + 1) & ~1);                             // one frame of the human stream is staged in K/g
   if (6 * nv <= L.S - L.xpos) L.F = L.xpos;                   // F_l aliases the body poses when it fits
   else L.F = take(6 * nv);
   L.L = region;                                  // the factor overlays the kinematics scratch
@@ -440,7 +441,7 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   if (model_of_instance)
     for (int i = 0; i < B; i++)
       if (model_of_instance[i] < 0 || model_of_instance[i] >= n_models) { delete b; return fail(-1, "model_of_instance out of range"); }
-  b->lay = make_layout(b->nq_max, b->s_max, b->nv_max, b->nbody_max, std::max(b->m_max, 1), b->nnz_max);
+  b->lay = make_layout(b->nq_max, b->s_max, b->nv_max, b->nbody_max, std::max(b->m_max, 1), b->nnz_max, b->h_max);
   int prev = 0;
   cudaGetDevice(&prev);
   cudaError_t e = cudaSetDevice(b->device);
@@ -645,6 +646,24 @@ extern "C" int gmr_batch_run_host(gmr_batch* b, const void* human_host, int huma
   if (human_dtype != GMR_F32 && human_dtype != GMR_F64) return fail(-1, "human_dtype must be GMR_F32 or GMR_F64");
   if (T_max < 1) return fail(-1, "T_max must be >= 1");
   DevGuard g(b->device);
+  if (n_chunks <= 0) {
+    // zero-copy: the kernel reads the stream from, and writes qpos to, pinned host memory directly
+    // (one coalesced burst per frame in, one per frame out; ~5 GB/s each way at 7 M frames/s)
+    cudaPointerAttributes ai{}, ao{};
+    if (cudaPointerGetAttributes(&ai, human_host) != cudaSuccess || cudaPointerGetAttributes(&ao, qpos_out_host) != cudaSuccess ||
+        ai.type != cudaMemoryTypeHost || ao.type != cudaMemoryTypeHost || !ai.devicePointer || !ao.devicePointer) {
+      cudaGetLastError();
+      return fail(-6, "zero-copy (n_chunks = 0) needs pinned (page-locked) host buffers");
+    }
+    const int32_t* T_dev = nullptr;
+    if (T_of_host) {
+      if (!b->stage_T) CU(cudaMalloc(&b->stage_T, sizeof(int) * (size_t)b->B));
+      CU(cudaMemcpyAsync(b->stage_T, T_of_host, sizeof(int) * (size_t)b->B, cudaMemcpyHostToDevice, b->stream));
+      T_dev = b->stage_T;
+    }
+    if (cold_start) { int rc = gmr_batch_reset(b, nullptr); if (rc) return rc; }
+    return launch_clips(b, ai.devicePointer, human_dtype, T_dev, T_max, offset_to_ground, (double*)ao.devicePointer, nullptr, nullptr);
+  }
   const size_t esz = human_dtype == GMR_F32 ? 4 : 8;
   const size_t in_row = (size_t)T_max * b->h_max * 7 * esz, out_row = (size_t)T_max * b->nq_max * sizeof(double);
   const size_t in_bytes = in_row * b->B, out_bytes = out_row * b->B;
@@ -676,8 +695,21 @@ extern "C" int gmr_batch_run_host(gmr_batch* b, const void* human_host, int huma
   CU(cudaStreamWaitEvent(b->s_in, b->ev[2], 0));
   CU(cudaStreamWaitEvent(b->s_out, b->ev[2], 0));
   const size_t in_frame = (size_t)b->h_max * 7 * esz, out_frame = (size_t)b->nq_max * sizeof(double);
-  for (int k = 0; k < n_chunks; k++) {
-    const int t0 = (int)((long long)T_max * k / n_chunks), t1 = (int)((long long)T_max * (k + 1) / n_chunks);
+  // frame ranges: with 3 or more ranges the first and the last are short (about T/10, a whole number of
+  // work units): only the first range's upload and the last range's download are not hidden behind a
+  // kernel, so they are made cheap; the middle is split evenly
+  std::vector<int> cut(1, 0);
+  if (n_chunks >= 3 && T_max >= 96) {
+    const int edge = std::max(32, (T_max / 10 + 31) / 32 * 32);
+    cut.push_back(edge);
+    for (int k = 1; k < n_chunks - 2; k++) cut.push_back(edge + (int)((long long)(T_max - 2 * edge) * k / (n_chunks - 2)));
+    cut.push_back(T_max - edge);
+  } else {
+    for (int k = 1; k < n_chunks; k++) cut.push_back((int)((long long)T_max * k / n_chunks));
+  }
+  cut.push_back(T_max);
+  for (size_t k = 0; k + 1 < cut.size(); k++) {
+    const int t0 = cut[k], t1 = cut[k + 1];
     if (t1 <= t0) continue;
     CU(cudaMemcpy2DAsync((char*)b->stage_in + t0 * in_frame, in_row, (const char*)human_host + t0 * in_frame, in_row,
                          (t1 - t0) * in_frame, b->B, cudaMemcpyHostToDevice, b->s_in));

@@ -31,8 +31,14 @@ __device__ __forceinline__ void stage_prep(const MV& mv, const Lay& lay, double*
   const DevModel& M = mv.M();
   const int s = M.n_scaled;
   double p[3] = {0, 0, 0}, q[4] = {1, 0, 0, 0};
+  // the whole frame comes in with coalesced streaming loads (it may live in pinned host memory: one
+  // burst of full lines instead of per-body gathers), staged in the K/g scratch, which is dead here
+  TIn* fbuf = (TIn*)(sm + lay.K);
+  const int ne = 7 * M.n_human;
+  for (int i = lane; i < ne; i += 32) fbuf[i] = __ldcs(frame + i);
+  __syncwarp();
   if (lane < s) {
-    const TIn* b = frame + 7 * mv(M.scaled_index)[lane];
+    const TIn* b = fbuf + 7 * mv(M.scaled_index)[lane];
     p[0] = (double)b[0]; p[1] = (double)b[1]; p[2] = (double)b[2];
     q[0] = (double)b[3]; q[1] = (double)b[4]; q[2] = (double)b[5]; q[3] = (double)b[6];
   }

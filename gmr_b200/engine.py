@@ -182,13 +182,16 @@ class BatchedRetargeter:
         return (qpos, dout) if diag else qpos
 
     def retarget_clips_host(self, human_host, qpos_host=None, T_of=None, offset_to_ground=False, cold_start=True,
-                            n_chunks: int = 4):
+                            n_chunks=None):
         """Whole clips from HOST buffers to a HOST result: the call the dataset drivers make
         (scripts/bvh_to_robot_dataset.py:84-113: new retargeter per clip -> per-frame retarget ->
         stacked qpos).  human_host [B,T,h,7] float32/float64 torch CPU tensor (pinned for full overlap);
         returns qpos [B,T,nq_max] float64 on the host (pinned; pass qpos_host to reuse it).
-        One C-ABI call (gmr_batch_run_host): the frames are cut into n_chunks ranges and H2D, retargeting
-        and D2H of consecutive ranges overlap on three streams; the result is bit-identical to run().
+        One C-ABI call (gmr_batch_run_host).  n_chunks = 0: zero-copy - one launch whose warps read each frame
+        from, and write each qpos row to, the pinned host buffers directly (needs both pinned).  n_chunks >= 1:
+        the frames are cut into n_chunks ranges and H2D, retargeting and D2H of consecutive ranges overlap on
+        three streams through device staging (any host memory).  None: zero-copy when both buffers are pinned,
+        else 3 ranges.  Either way the result is bit-identical to run().
         Asynchronous on the batch's stream - synchronise it before reading the result."""
         human_host = torch.as_tensor(human_host)
         if human_host.is_cuda:
@@ -208,6 +211,8 @@ class BatchedRetargeter:
             t_of = np.ascontiguousarray(T_of, np.int32)
             if t_of.shape != (self.B,):
                 raise ValueError("T_of must have one entry per clip")
+        if n_chunks is None:
+            n_chunks = 0 if (human_host.is_pinned() and qpos_host.is_pinned()) else 3
         _lib.check(_lib.lib().gmr_batch_run_host(
             self._h, C.c_void_p(human_host.data_ptr()), F32 if human_host.dtype == torch.float32 else F64,
             None if t_of is None else t_of.ctypes.data_as(C.c_void_p), T, int(bool(offset_to_ground)), int(bool(cold_start)),

@@ -143,8 +143,12 @@ int gmr_batch_run(gmr_batch* b, const void* human_dev, int human_dtype,
 
 /* gmr_batch_run for clips held in HOST memory (pinned for full overlap): what the dataset drivers
  * call per folder (scripts/bvh_to_robot_dataset.py:96-113, smplx_to_robot_dataset.py:83-104).
- * human_host [B,T_max,h,7], T_of_host [B] or NULL, qpos_out_host [B,T_max,nq_max].  The frames are
- * cut into n_chunks ranges; H2D of range k+1, retargeting of range k and D2H of range k-1 overlap.
+ * human_host [B,T_max,h,7], T_of_host [B] or NULL, qpos_out_host [B,T_max,nq_max].
+ * n_chunks >= 1: the frames are cut into n_chunks ranges; H2D of range k+1, retargeting of range k and
+ * D2H of range k-1 overlap on three streams through device staging buffers (any host memory).
+ * n_chunks == 0: zero-copy - one launch; each warp reads its frame from human_host and writes its qpos row
+ * to qpos_out_host over the bus directly (both must be page-locked: cudaHostAlloc / cudaHostRegister;
+ * -6 otherwise).  Same result bit for bit either way.
  * cold_start != 0 resets every instance to qpos0 first (a new retargeter object per clip).
  * Asynchronous: synchronise the batch's stream before reading qpos_out_host. */
 int gmr_batch_run_host(gmr_batch* b, const void* human_host, int human_dtype, const int32_t* T_of_host,

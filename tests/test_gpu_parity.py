@@ -223,19 +223,27 @@ def test_step_equals_run_and_state_persists():
 
 
 def test_host_pipeline_is_bit_identical_to_one_launch():
-    """gmr_batch_run_host: chunked H2D / retarget / D2H over three streams == one launch on resident data."""
+    """gmr_batch_run_host: zero-copy (0) and chunked H2D / retarget / D2H over three streams (>= 1) == one
+    launch on resident data."""
     import torch
     B, T = 40, 37
     m, t, dm, br, human, heights = _setup("bvh", "unitree_g1", B, T)
     full = br.run(human).cpu().numpy()
     T_of = np.random.default_rng(1).integers(1, T + 1, size=B).astype(np.int32)
-    for chunks in (1, 3, 37):
+    for chunks in (None, 0, 1, 3, 37):
         hh = torch.from_numpy(human).pin_memory()
         out = br.retarget_clips_host(hh, n_chunks=chunks)
         torch.cuda.synchronize()
         np.testing.assert_array_equal(out.numpy(), full)
+    with pytest.raises(Exception, match="pinned"):
+        br.retarget_clips_host(torch.from_numpy(human), n_chunks=0)               # zero-copy refuses pageable memory
     br.reset()
     ragged = br.run(human, T_of=T_of).cpu().numpy()
+    out = br.retarget_clips_host(torch.from_numpy(human.astype(np.float32)).pin_memory(), T_of=T_of, n_chunks=0)
+    torch.cuda.synchronize()
+    r32 = br.run(human.astype(np.float32), T_of=T_of).cpu().numpy()
+    for b in range(B):
+        np.testing.assert_array_equal(out.numpy()[b, :T_of[b]], r32[b, :T_of[b]])
     out = br.retarget_clips_host(torch.from_numpy(human), T_of=T_of, n_chunks=4)     # pageable host memory works too
     torch.cuda.synchronize()
     for b in range(B):
