@@ -319,7 +319,7 @@ def run_b200(args):
         with open(tpath) as f:
             traffic = json.load(f).get("dram_bytes_per_launch")
     roofline = {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
-                "traffic": traffic, "peak_source": peak_src, "kernel": "gmr::clip_kernel<float>",
+                "traffic": traffic, "peak_source": peak_src, "kernel": "gmr::clip_kernel<float,true>",
                 "kernel_ms_per_launch": kernel_ms, "algorithmic_bytes_per_frame": bpf,
                 "note": "neither HBM nor tensor cores bind this path; the binding resource is the FP64 FMA pipe / "
                         "dependent-chain latency - see `compute`",

@@ -241,6 +241,7 @@ def test_host_pipeline_is_bit_identical_to_one_launch():
     ragged = br.run(human, T_of=T_of).cpu().numpy()
     out = br.retarget_clips_host(torch.from_numpy(human.astype(np.float32)).pin_memory(), T_of=T_of, n_chunks=0)
     torch.cuda.synchronize()
+    br.reset()
     r32 = br.run(human.astype(np.float32), T_of=T_of).cpu().numpy()
     for b in range(B):
         np.testing.assert_array_equal(out.numpy()[b, :T_of[b]], r32[b, :T_of[b]])
