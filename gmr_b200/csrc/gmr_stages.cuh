@@ -213,21 +213,24 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
 }
 
 // ------------------------------------------------------------------ mink SO3/SE3 log
-__device__ __forceinline__ void se3_log_dev(const double* q, const double* p, double* out) {
+// Also returns sin/cos of the rotation angle th = |w| (read straight off the quaternion: with phi = th/2,
+// sin phi : cos phi = |xyz| : |qw|), which spares the sincos of the V^-1 coefficient here and the one of
+// the Jlog coefficients in stage_stiffness.
+__device__ __forceinline__ void se3_log_dev(const double* q, const double* p, double* out, double& sin_th, double& cos_th) {
   const double qw = q[0], n2 = q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+  const double n = sqrt(n2), aw = fabs(qw);
   double f;
-  if (n2 < LIE_EPS) {
-    f = 2.0 / qw - 2.0 / 3.0 * n2 / (qw * qw * qw);
-  } else {
-    const double n = sqrt(n2);
-    if (fabs(qw) < LIE_EPS) f = (qw > 0 ? 1.0 : -1.0) * 3.14159265358979323846 / n;
-    else f = 2.0 * atan2(qw < 0 ? -n : n, fabs(qw)) / n;
-  }
+  if (n2 < LIE_EPS) f = 2.0 / qw - 2.0 / 3.0 * n2 / (qw * qw * qw);
+  else if (aw < LIE_EPS) f = (qw > 0 ? 1.0 : -1.0) * 3.14159265358979323846 / n;
+  else f = 2.0 * atan2(qw < 0 ? -n : n, aw) / n;
+  const double in2 = 1.0 / (n2 + qw * qw);
+  sin_th = 2.0 * n * aw * in2;
+  cos_th = (qw * qw - n2) * in2;
   const double w0 = f * q[1], w1 = f * q[2], w2 = f * q[3];
   const double th2 = w0 * w0 + w1 * w1 + w2 * w2;
   double k;
   if (th2 < LIE_EPS) k = 1.0 / 12.0;
-  else { const double th = sqrt(th2); double sh, ch; sincos(0.5 * th, &sh, &ch); k = (1.0 - 0.5 * th * ch / sh) / th2; }
+  else k = (1.0 - 0.5 * sqrt(th2) * (aw / n)) / th2;       // cos(th/2) / sin(th/2) = |qw| / |xyz|
   // V^-1 p = p - 1/2 w x p + k w x (w x p)
   double w[3] = {w0, w1, w2}, c1[3], c2[3];
   cross3(w, p, c1);
@@ -254,7 +257,10 @@ __device__ __forceinline__ double stage_errors(const MV& mv, const Lay& lay, dou
     double qi[4] = {xq[0], -xq[1], -xq[2], -xq[3]}, qbt[4], d[3] = {tgt[0] - xp[0], tgt[1] - xp[1], tgt[2] - xp[2]}, pbt[3], e[6];
     qmul(qi, tgt + 3, qbt);
     qrot(qi, d, pbt);
-    se3_log_dev(qbt, pbt, e);
+    double sn, cs;
+    se3_log_dev(qbt, pbt, e, sn, cs);
+    sm[lay.g + 6 * lane] = sn;            // parked in g (rewritten by stage_stiffness after it has read them)
+    sm[lay.g + 6 * lane + 1] = cs;
     double* eo = sm + lay.e + 6 * lane;
 #pragma unroll
     for (int k = 0; k < 6; k++) { eo[k] = e[k]; ss += e[k] * e[k]; }
@@ -295,51 +301,47 @@ __device__ __forceinline__ double stage_stiffness(const MV& mv, const Lay& lay, 
       for (int i = 0; i < 9; i++) { P[i] = Rt[i]; Pr[i] = 0; }
     } else {
       const double th = sqrt(th2);
-      double s, c;
-      sincos(th, &s, &c);
-      double W[9], W2[9], Ji[9];
-      skew3(w, W);
-      mm3(W, W, W2);
+      const double s = sm[lay.g + 6 * lane], c = sm[lay.g + 6 * lane + 1];      // sin th, cos th from stage_errors
       const double A = (1.0 / th2) * (1.0 - (th * s / (2.0 * (1.0 - c))));
-#pragma unroll
-      for (int i = 0; i < 9; i++) Ji[i] = ((i % 4 == 0) ? 1.0 : 0.0) - 0.5 * W[i] + A * W2[i];
+      // products of skew matrices in closed form: [a]x[b]x = b a' - (a.b) I, so with cw = w.v, u = v x w:
+      //   W^2 = w w' - th2 I,  WV = v w' - cw I,  VW = w v' - cw I,  WVW = -cw W,
+      //   VWW = u w' - th2 V,  WWV = -(VWW)',  WVWW + WWVW = -2 cw W^2
+      double Wm[9], V[9], Ji[9], Q[9], u[3];
+      skew3(w, Wm);
+      skew3(ev, V);
+      cross3(ev, w, u);
+      const double cw = w[0] * ev[0] + w[1] * ev[1] + w[2] * ev[2];
       // Barfoot Q(v, w)
       const double Bc = (th - s) / (th2 * th), Cc = (1.0 - 0.5 * th2 - c) / (th2 * th2),
                    Dc = (2.0 * th - 3.0 * s + th * c) / (2.0 * th2 * th2 * th);
-      double V[9], VW[9], WV[9], WVW[9], VWW[9], t1[9], t2[9], Q[9];
-      skew3(ev, V);
-      mm3(V, W, VW);
-      mm3(W, V, WV);
-      mm3(WV, W, WVW);
-      mm3(VW, W, VWW);
-      mm3(WVW, W, t1);
-      mm3(W, WVW, t2);
+      const double kV = 0.5 + 2.0 * Cc * th2, kW = -cw * (Bc + 3.0 * Cc), kI = -2.0 * cw * (Bc - Dc * th2), kWW = -2.0 * Dc * cw;
 #pragma unroll
       for (int i = 0; i < 3; i++)
 #pragma unroll
         for (int j = 0; j < 3; j++) {
-          const int ij = 3 * i + j, ji = 3 * j + i;
-          // WWV = -(VWW)^T  ->  VWW + WWV = VWW - VWW^T
-          Q[ij] = 0.5 * V[ij] + Bc * (WV[ij] + VW[ij] + WVW[ij]) - Cc * (VWW[ij] - VWW[ji] - 3.0 * WVW[ij]) + Dc * (t1[ij] + t2[ij]);
+          const int ij = 3 * i + j;
+          const double dlt = i == j ? 1.0 : 0.0;
+          Ji[ij] = dlt * (1.0 - A * th2) - 0.5 * Wm[ij] + A * (w[i] * w[j]);
+          Q[ij] = kV * V[ij] + kW * Wm[ij] + dlt * kI + Bc * (ev[i] * w[j] + w[i] * ev[j]) - Cc * (u[i] * w[j] - w[i] * u[j]) + kWW * (w[i] * w[j]);
         }
-      double T[9], Bm[9];
+      double T[9], TP[9];
       mm3(Ji, Q, T);
-      mm3(T, Ji, Bm);               // B = -Bm
       mm3(Ji, Rt, P);
-      mm3(Bm, Rt, Pr);
+      mm3(T, P, TP);                // B R' = -Ji Q Ji R' = -T P
 #pragma unroll
-      for (int i = 0; i < 9; i++) Pr[i] = -Pr[i];
+      for (int i = 0; i < 9; i++) Pr[i] = -TP[i];
     }
     // Pr += -P [r]x
     const int ref = M.ref_body;
     const double* xp = sm + lay.xpos + 3 * body;
     const double* xo = sm + lay.xpos + 3 * ref;     // world (body 0) has xpos = 0
     const double r[3] = {xp[0] - xo[0], xp[1] - xo[1], xp[2] - xo[2]};
-    double Sr[9], PS[9];
-    skew3(r, Sr);
-    mm3(P, Sr, PS);
 #pragma unroll
-    for (int i = 0; i < 9; i++) Pr[i] -= PS[i];
+    for (int i = 0; i < 3; i++) {     // row i of P [r]x is p_i x r
+      double pr[3];
+      cross3(P + 3 * i, r, pr);
+      Pr[3 * i] -= pr[0]; Pr[3 * i + 1] -= pr[1]; Pr[3 * i + 2] -= pr[2];
+    }
     // K = [[a P'P, a P'Pr],[., a Pr'Pr + b P'P]]
     double PtP[9], PtPr[9], PrtPr[9];
     mtm3(P, P, PtP);

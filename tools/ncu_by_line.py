@@ -84,6 +84,7 @@ def main():
     hdr = rows[hdr_i]
     col = {n: i for i, n in enumerate(hdr)}
     base = None
+    inst_line = collections.Counter(); static_line = collections.Counter()
     by_line = collections.Counter(); by_func = collections.Counter(); inst_func = collections.Counter()
     noinst_func = collections.Counter(); thr_func = collections.Counter(); by_outer = collections.Counter()
     static_func = collections.Counter()
@@ -106,6 +107,7 @@ def main():
         for fl in chain:
             if fl[0] == "gmr_stages.cuh":
                 outer = func_of(fl)
+        inst_line[cur] += ins; static_line[cur] += 1
         by_line[cur] += smp; by_func[fn] += smp; inst_func[fn] += ins; noinst_func[fn] += noi; thr_func[fn] += thr
         by_outer[outer] += smp; static_func[outer] += 1
         total += smp
@@ -119,7 +121,7 @@ def main():
         print(f"{100 * s / total:6.2f}%  noinst {100 * noinst_func[fn] / max(s, 1):5.1f}%  inst {ie:14d}  thr/inst {thr_func[fn] / max(ie, 1):5.1f}  {fn}")
     print("\n-- top lines")
     for (f, ln), s in by_line.most_common(args.top):
-        print(f"{100 * s / total:6.2f}%  {f}:{ln}")
+        print(f"{100 * s / total:6.2f}%  inst {inst_line[(f, ln)]:13d}  static {static_line[(f, ln)]:4d}  {f}:{ln}")
 
 
 if __name__ == "__main__":
