@@ -169,8 +169,9 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   // side by side into the 32 lanes (lane = one stored entry of a row).  The updates
   // W(anc_a, anc_b) -= L(i,a) L(i,b) and r(anc_a) -= L(i,a) y_i of the rows of one step are merged
   // per target (rows of different branches meet in their common ancestors), one op per target:
-  //   op = {target(16) | n(2)<<16,  n x (lane_a(5) | lane_b(5)<<5) in 10-bit fields},  target < nnz: W entry,
-  //   else r[target-nnz]; the ops of a step are sorted by n (descending) so that the lanes of a pass agree on n
+  // target < nnz: W entry, else r[target-nnz]; a contribution names the two lanes of the scaled row whose
+  // product it is; the ops of a step are sorted by n (descending) so that the lanes of a pass agree on n.
+  // Everything the device would have to shift or scale is stored as a byte offset.
   std::vector<int> elim_lane, elim_opstart;
   std::vector<int> elim_ops;            // int2 per op
   int n_elim_step = 0;
@@ -192,28 +193,30 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
         while (pos < todo.size() && rows.size() < 3 && used + dof_depth[todo[pos]] + 1 <= 32) {
           rows.push_back(todo[pos]); base.push_back(used); used += dof_depth[todo[pos]] + 1; pos++;
         }
-        std::vector<int> lt(64, 0);            // per lane: w0 = ent | diag_lane<<16 | is_diag<<21 | valid<<22, w1 = col | row<<8
+        // per lane: w0 = byte offset of the entry in W | valid | is_diag<<1 | diag_lane<<16,
+        //           w1 = col | row<<8 | byte offset of r[row] (= W + nnz + row) << 16
+        std::vector<int> lt(64, 0);
         for (int l = 0; l < 32; l++) lt[2 * l] = l << 16;
-        std::map<int, std::vector<int>> tgt;   // target -> contributions (la | lb<<5)
+        std::map<int, std::vector<int>> tgt;   // target -> contributions (byte offsets into lrow: 8 la | 8 lb << 8)
         for (size_t r = 0; r < rows.size(); r++) {
           const int i = rows[r], dd = dof_depth[i], rp = dof_rowptr[i], b0 = base[r];
           for (int a2 = 0; a2 <= dd; a2++) {
-            lt[2 * (b0 + a2)] = (rp + a2) | ((b0 + dd) << 16) | ((a2 == dd ? 1 : 0) << 21) | (1 << 22);
-            lt[2 * (b0 + a2) + 1] = dof_anc[rp + a2] | (i << 8);
+            lt[2 * (b0 + a2)] = ((rp + a2) * 8) | 1 | ((a2 == dd ? 1 : 0) << 1) | ((b0 + dd) << 16);
+            lt[2 * (b0 + a2) + 1] = dof_anc[rp + a2] | (i << 8) | (((nnz + i) * 8) << 16);
           }
           for (int a2 = 0; a2 < dd; a2++) {
-            for (int b2 = 0; b2 <= a2; b2++) tgt[dof_ancrow[rp + a2] + b2].push_back((b0 + a2) | ((b0 + b2) << 5));
-            tgt[nnz + dof_anc[rp + a2]].push_back((b0 + a2) | ((b0 + dd) << 5));
+            for (int b2 = 0; b2 <= a2; b2++) tgt[dof_ancrow[rp + a2] + b2].push_back(((b0 + a2) * 8) | (((b0 + b2) * 8) << 8));
+            tgt[nnz + dof_anc[rp + a2]].push_back(((b0 + a2) * 8) | (((b0 + dd) * 8) << 8));
           }
         }
         elim_lane.insert(elim_lane.end(), lt.begin(), lt.end());
+        // op = {8 target | n | contribution 2 << 16,  contribution 0 | contribution 1 << 16}
         for (int want = 3; want >= 1; want--)
           for (auto& kv : tgt) {
             if ((int)kv.second.size() != want) continue;
-            int cw = 0;
-            for (size_t c2 = 0; c2 < kv.second.size(); c2++) cw |= kv.second[c2] << (10 * c2);
-            elim_ops.push_back(kv.first | (want << 16));
-            elim_ops.push_back(cw);
+            const std::vector<int>& c2 = kv.second;
+            elim_ops.push_back((kv.first * 8) | want | (want > 2 ? c2[2] << 16 : 0));
+            elim_ops.push_back(c2[0] | (want > 1 ? c2[1] << 16 : 0));
           }
         elim_opstart.push_back((int)elim_ops.size() / 2);
         n_elim_step++;
@@ -412,9 +415,9 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h) 
   else L.F = take(6 * nv);
   L.L = region;                                  // the factor overlays the kinematics scratch
   L.rv = region + nnz;                           // right-hand side directly behind the factor (one index space)
-  L.lrow = region + ((nnz + nv + 1) & ~1);
+  L.lrow = (region + nnz + nv + 31) & ~31;        // 256-byte aligned: the program ORs lane offsets into its address
   o = std::max(o, L.lrow + 32);
-  L.total = o;
+  L.total = (o + 31) & ~31;
   L.maxt = GMR_MAX_TASKS;
   return L;
 }

@@ -70,7 +70,7 @@ __device__ __forceinline__ int next_stage(const DevModel& M, int stage) {
 // SM = true: single-model batch, model tables staged in shared memory.
 template <typename TIn, bool SM>
 __global__ void __launch_bounds__(GMR_CTA_THREADS, GMR_MIN_CTAS) clip_kernel(const RunArgs a) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(256) double smem[];
   __shared__ unsigned short pair_tab[PAIR_TAB_SIZE];
   __shared__ DevModel smodel;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -213,7 +213,7 @@ struct StageArgs {
 
 template <typename TIn>
 __global__ void prep_kernel(const StageArgs a) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(256) double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
   if (inst >= a.B) return;
@@ -227,7 +227,7 @@ __global__ void prep_kernel(const StageArgs a) {
 }
 
 __global__ void fk_kernel(const StageArgs a) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(256) double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
   if (inst >= a.B) return;
@@ -242,7 +242,7 @@ __global__ void fk_kernel(const StageArgs a) {
 }
 
 __global__ void build_qp_kernel(const StageArgs a) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(256) double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
   if (inst >= a.B) return;
@@ -277,7 +277,7 @@ __global__ void build_qp_kernel(const StageArgs a) {
 
 // one mink.solve_ik call on the batch state: dq = argmin of the stage's QP (tree solver)
 __global__ void solve_ik_kernel(const StageArgs a) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(256) double smem[];
   __shared__ unsigned short pair_tab[PAIR_TAB_SIZE];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
@@ -306,7 +306,7 @@ __global__ void solve_ik_kernel(const StageArgs a) {
 // generic box QP: H [n_qp, n, n] full symmetric
 __global__ void qp_kernel(int n_qp, int n, const double* H, const double* c, const double* lo, const double* hi,
                           double* x_out, int* nfact_out) {
-  extern __shared__ double smem[];
+  extern __shared__ __align__(256) double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
   if (inst >= n_qp) return;

@@ -658,6 +658,12 @@ __device__ __forceinline__ void fill_pair_tab(unsigned short* pair_tab) {
   }
 }
 
+__device__ __forceinline__ double lds_f64(unsigned a) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+  return v;
+}
+
 // H(i,j) of the tree layout (0 if neither dof is an ancestor of the other)
 template <class MV>
 __device__ __forceinline__ double tree_at(const MV& mv, const double* H, int i, int j) {
@@ -684,6 +690,9 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
   const int2* elim_ops = mv(M.elim_ops);
   const int* elim_opstart = mv(M.elim_opstart);
   rv = W + nnz;                   // the program addresses factor and right-hand side as one array
+  char* Wc = (char*)W;
+  const unsigned lrow_s = (unsigned)__cvta_generic_to_shared(lrow);
+  const int nstep = M.n_elim_step, maxd = M.max_depth;
   const int i0 = lane, i1 = lane + 32;
   const bool has0 = i0 < n, has1 = i1 < n, two = n > 32;
   const double lo0 = lo[0], hi0 = hi[0], lo1 = lo[1], hi1 = hi[1], c0 = c[0], c1 = c[1];    // lane l owns dofs l and l+32
@@ -696,7 +705,6 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
   int best = n + 1, p = 3, nfact = 0;
   bool spd = true;
   double r0 = 0, r1 = 0;
-  int* isact = (int*)x;           // x is written only after the solve: its storage holds the active flags meanwhile
 #pragma unroll 1
   for (int it = 0; it < 400; it++) {
     // ---- right-hand side: active rows carry their bound, free rows -c_F - H_FA x_A
@@ -717,25 +725,25 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
     for (int e = lane; e < nnz; e += 32) W[e] = H[e];
     __syncwarp();
     // ---- L'L factorisation + the sweep L'y = r, driven by the model's static elimination program:
-    // a step scales up to 4 unrelated rows at once (lane = one stored entry; y_i = r_i / L_ii rides in
+    // a step scales up to 3 unrelated rows at once (lane = one stored entry; y_i = r_i / L_ii rides in
     // the row's diagonal lane), then applies the merged updates of those rows, one target per lane.
-    if (has0) isact[i0] = st0 != 0;
-    if (has1) isact[i1] = st1 != 0;
-    __syncwarp();
+    // The program holds byte offsets (entries relative to W, lanes relative to the 256-byte aligned lrow).
     bool notpd = false;
     int2 lt_next = elim_lane[lane];
     int q0_next = elim_opstart[0];
 #pragma unroll 1
-    for (int sidx = 0; sidx < M.n_elim_step; sidx++) {
+    for (int sidx = 0; sidx < nstep; sidx++) {
       const int2 lt = lt_next;
       const int q0 = q0_next, qend = elim_opstart[sidx + 1];
-      lt_next = elim_lane[min(sidx + 1, M.n_elim_step - 1) * 32 + lane];     // prefetch the next step's lane table
+      lt_next = elim_lane[min(sidx + 1, nstep - 1) * 32 + lane];     // prefetch the next step's lane table
       q0_next = qend;
-      const bool valid = (lt.x >> 22) & 1, isd = (lt.x >> 21) & 1;
-      const int ent = lt.x & 0xffff, dl = (lt.x >> 16) & 31, col = lt.y & 0xff, row = lt.y >> 8;
-      const double w = valid ? W[ent] : 1.0;
-      const double ri = valid ? rv[row] : 0.0;
-      const bool rowact = valid && isact[row], colact = valid && isact[col];
+      const bool valid = lt.x & 1, isd = lt.x & 2;
+      const int dl = (lt.x >> 16) & 31, col = lt.y & 0xff, row = (lt.y >> 8) & 0xff;
+      double* wp = (double*)(Wc + (lt.x & 0xfff8));
+      double* rp = (double*)(Wc + ((unsigned)lt.y >> 16));
+      const double w = valid ? *wp : 1.0;
+      const double ri = isd ? *rp : 0.0;
+      const bool rowact = valid && ((act >> row) & 1ull), colact = valid && ((act >> col) & 1ull);
       double piv = __shfl_sync(GMR_FULL, w, dl);
       if (rowact) piv = 1.0;                                     // identity row, y_i = the bound
       if (!(piv > 0.0)) { notpd = true; piv = 1.0; }
@@ -744,20 +752,24 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
       const double yi = ri * inv;
       __syncwarp();
       if (valid) {
-        W[ent] = isd ? inv : l;                                  // diagonal stores 1/L_ii
+        *wp = isd ? inv : l;                                     // diagonal stores 1/L_ii
         lrow[lane] = isd ? yi : l;
-        if (isd) rv[row] = yi;
+        if (isd) *rp = yi;
       }
       __syncwarp();
 #pragma unroll 1
       for (int q = q0 + lane; q < qend; q += 32) {
         const int2 op = elim_ops[q];
-        const int tgt = op.x & 0xffff, nc = op.x >> 16;
-        int cc = op.y;
-        double acc = lrow[cc & 31] * lrow[(cc >> 5) & 31];
-#pragma unroll 1
-        for (int k = 1; k < nc; k++) { cc >>= 10; acc += lrow[cc & 31] * lrow[(cc >> 5) & 31]; }
-        W[tgt] -= acc;
+        double* tp = (double*)(Wc + (op.x & 0xfff8));
+        const unsigned cy = (unsigned)op.y;
+        double acc = lds_f64(lrow_s | (cy & 0xf8u)) * lds_f64(lrow_s | ((cy >> 8) & 0xf8u));
+        const int nc = op.x & 3;
+        if (nc >= 2) acc += lds_f64(lrow_s | ((cy >> 16) & 0xf8u)) * lds_f64(lrow_s | (cy >> 24));
+        if (nc == 3) {
+          const unsigned cx = (unsigned)op.x >> 16;
+          acc += lds_f64(lrow_s | (cx & 0xf8u)) * lds_f64(lrow_s | (cx >> 8));
+        }
+        *tp -= acc;
       }
       __syncwarp();
     }
@@ -766,13 +778,24 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
     // ---- L x = y, wavefront over depth
     r0 = has0 ? rv[i0] : 0.0;
     r1 = has1 ? rv[i1] : 0.0;
+    {
+      const double* w0p = W + rp0;
+      const double* w1p = W + rp1;
+      const short* a0p = anc + rp0;
+      const short* a1p = anc + rp1;
 #pragma unroll 1
-    for (int a = 0; a <= M.max_depth; a++) {
-      if (d0 == a) { r0 *= W[rp0 + a]; rv[i0] = r0; }
-      if (two && d1 == a) { r1 *= W[rp1 + a]; rv[i1] = r1; }
-      __syncwarp();
-      if (d0 > a) r0 -= W[rp0 + a] * rv[anc[rp0 + a]];
-      if (two && d1 > a) r1 -= W[rp1 + a] * rv[anc[rp1 + a]];
+      for (int a = 0; a <= maxd; a++, w0p++, w1p++, a0p++, a1p++) {
+        const double wv0 = d0 >= a ? *w0p : 0.0;
+        if (d0 == a) { r0 *= wv0; rv[i0] = r0; }
+        double wv1 = 0.0;
+        if (two) {
+          if (d1 >= a) wv1 = *w1p;
+          if (d1 == a) { r1 *= wv1; rv[i1] = r1; }
+        }
+        __syncwarp();
+        if (d0 > a) r0 -= wv0 * rv[*a0p];
+        if (two && d1 > a) r1 -= wv1 * rv[*a1p];
+      }
     }
     // exact bounds on the active set (the solve reproduces them up to rounding)
     if (st0) r0 = xa0;
