@@ -11,6 +11,7 @@
 
 #include "../../include/gmr_b200.h"
 #include "gmr_clip.cuh"
+#include "gmr_bvh.cuh"
 
 using namespace gmr;
 
@@ -857,6 +858,52 @@ int fma_probe(int device, double* tflops_out) {
   return 0;
 }
 }  // namespace
+
+// ---------------------------------------------------------------- BVH motion -> frame stream
+extern "C" int gmr_bvh_to_stream(int device, void* stream, const double* lpos_dev, const double* euler_deg_dev,
+                                 const int32_t* clip_start_dev, int n_clips, int n_frames, int n_bones,
+                                 const int32_t* parents_dev, const int32_t* channel_axis, const int32_t* src_pos_dev,
+                                 const int32_t* src_rot_dev, int n_rows, int out_dtype, void* stream_out_dev,
+                                 int head_row, const int32_t* foot_rows, double* height_out_dev) {
+  if (!lpos_dev || !euler_deg_dev || !clip_start_dev || !parents_dev || !channel_axis || !src_pos_dev || !src_rot_dev ||
+      !stream_out_dev || n_clips < 0 || n_frames < 0 || n_bones < 1 || n_rows < 1)
+    return fail(-1, "gmr_bvh_to_stream: bad argument");
+  if (out_dtype != GMR_F32 && out_dtype != GMR_F64) return fail(-1, "gmr_bvh_to_stream: dtype must be GMR_F32 or GMR_F64");
+  for (int k = 0; k < 3; k++)
+    if (channel_axis[k] < 0 || channel_axis[k] > 2) return fail(-1, "gmr_bvh_to_stream: channel axis must be 0, 1 or 2");
+  if (head_row >= n_rows) return fail(-1, "gmr_bvh_to_stream: head row out of range");
+  if (n_frames == 0 || n_clips == 0) return 0;
+  DevGuard g(device);
+  cudaStream_t st = (cudaStream_t)stream;
+  BvhArgs a{};
+  a.lpos = lpos_dev; a.euler = euler_deg_dev; a.clip_start = clip_start_dev;
+  a.C = n_clips; a.N = n_frames; a.J = n_bones; a.parents = parents_dev;
+  a.ax0 = channel_axis[0]; a.ax1 = channel_axis[1]; a.ax2 = channel_axis[2];
+  a.src_pos = src_pos_dev; a.src_rot = src_rot_dev; a.h = n_rows; a.out = stream_out_dev;
+  a.head = head_row;
+  for (int k = 0; k < 4; k++) {
+    a.feet[k] = foot_rows ? foot_rows[k] : -1;
+    if (a.feet[k] >= n_rows) return fail(-1, "gmr_bvh_to_stream: foot row out of range");
+  }
+  a.height = height_out_dev;
+  void *sign = nullptr, *G = nullptr;
+  CU(cudaMallocAsync(&sign, (size_t)n_frames * n_bones, st));
+  cudaError_t e = cudaMallocAsync(&G, (size_t)n_frames * n_bones * 8 * sizeof(double), st);
+  if (e != cudaSuccess) { cudaFreeAsync(sign, st); return fail(-3, cudaGetErrorString(e)); }
+  a.sign = (signed char*)sign; a.G = (double*)G;
+  const int tb = 128;
+  bvh_sign_kernel<<<(n_clips * n_bones + tb - 1) / tb, tb, 0, st>>>(a);
+  bvh_fk_kernel<<<(n_frames + tb - 1) / tb, tb, 0, st>>>(a);
+  const long long ne = (long long)n_frames * n_rows;
+  if (out_dtype == GMR_F32) bvh_emit_kernel<float><<<(unsigned)((ne + 255) / 256), 256, 0, st>>>(a);
+  else bvh_emit_kernel<double><<<(unsigned)((ne + 255) / 256), 256, 0, st>>>(a);
+  if (height_out_dev) bvh_height_kernel<<<(n_clips + tb - 1) / tb, tb, 0, st>>>(a);
+  e = cudaGetLastError();
+  cudaFreeAsync(sign, st);
+  cudaFreeAsync(G, st);
+  if (e != cudaSuccess) return fail(-3, cudaGetErrorString(e));
+  return 0;
+}
 
 extern "C" int gmr_probe_fma_peak(int device, int fp64, double* tflops_out) {
   if (!tflops_out) return fail(-1, "null argument");

@@ -183,6 +183,25 @@ int gmr_fk_bodies_f32(gmr_model* m, void* stream, int N, const float* root_pos_d
                       const float* root_rot_xyzw_dev, const float* dof_pos_dev,
                       float* body_pos_out_dev, float* body_rot_out_dev);
 
+/* BVH motion -> human frame stream, for all frames of all clips of a folder at once: what
+ * load_lafan1_file does after the text parse (general_motion_retargeting/utils/lafan1.py:8-71 with
+ * utils/lafan_vendor/extract.py:162-163 and utils/lafan_vendor/utils.py:40-103,251-269): Euler angles
+ * (degrees, in channel order; channel_axis[k] = 0/1/2 for X/Y/Z) -> local quaternions with the
+ * reference's sign continuity over time, FK down the bone list (parents precede children), Y-up cm ->
+ * Z-up m, orientation = R_quat * q.  Clips are concatenated along the frame axis: clip c owns frames
+ * [clip_start[c], clip_start[c+1]).  Output row k takes the position of bone src_pos[k] and the
+ * orientation of bone src_rot[k] (LeftFootMod = LeftFoot position + LeftToe orientation, :35-39);
+ * stream_out [n_frames, n_rows, 7] = pos xyz, quat wxyz in out_dtype - the layout gmr_batch_run reads.
+ * height_out [n_clips] (or NULL): the loader's height guess from each clip's last frame (:42-69) with
+ * head_row = output row of "Head" (-1: absent) and foot_rows[4] = rows of LeftFootMod, RightFootMod,
+ * LeftFoot, RightFoot (-1: absent).  All pointers except channel_axis / foot_rows are device memory;
+ * asynchronous on `stream`. */
+int gmr_bvh_to_stream(int device, void* stream, const double* lpos_dev, const double* euler_deg_dev,
+                      const int32_t* clip_start_dev, int n_clips, int n_frames, int n_bones,
+                      const int32_t* parents_dev, const int32_t* channel_axis, const int32_t* src_pos_dev,
+                      const int32_t* src_rot_dev, int n_rows, int out_dtype, void* stream_out_dev,
+                      int head_row, const int32_t* foot_rows, double* height_out_dev);
+
 /* Measurement helper (no reference counterpart): measured peak of the CUDA-core FMA pipe in
  * TFLOP/s (fp64 != 0: DFMA, else FFMA) - the compute roofline denominator of bench.py.
  * Synchronous, default stream. */

@@ -4,8 +4,9 @@ per-file / per-frame Python loop replaced by ONE batched launch over every clip 
 
   python scripts/bvh_to_robot_dataset.py --src_folder <bvh or npz folder> --tgt_folder <out> --robot unitree_g1 [--override]
 
-Inputs: *.bvh (parsed by the reference's own loader, utils/lafan1.py:8-71 - text parsing is outside the
-hot path and reused as is; needs GMR_ROOT=<GMR checkout>) or *.npz frame streams
+Inputs: *.bvh (text parsed on the CPU by gmr_b200.bvh.parse_bvh, then Euler -> quaternion, sign continuity, FK,
+axis change, FootMod rows and the height guess of utils/lafan1.py:8-71 on the GPU for all files at once:
+gmr_bvh_to_stream; --reference_loader uses the reference's own Python loader instead, needs GMR_ROOT) or *.npz frame streams
 {frames [T,h,7] (pos xyz, quat wxyz), names [h], height, fps} as written by tools/bvh_to_npz.py.
 Outputs: <tgt_folder>/<relative path>.pkl with {root_pos, root_rot (xyzw), dof_pos, local_body_pos, fps,
 link_body_list} (reference :144-156); existing outputs are skipped unless --override (:70-72).
@@ -18,7 +19,7 @@ import types
 import numpy as np
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
-from gmr_b200 import dataset, params  # noqa: E402
+from gmr_b200 import bvh, dataset, params  # noqa: E402
 
 
 def reference_bvh_loader():
@@ -53,6 +54,7 @@ def main():
     ap.add_argument("--override", default=False, action="store_true")
     ap.add_argument("--target_fps", default=30, type=int)
     ap.add_argument("--device", default=0, type=int)
+    ap.add_argument("--reference_loader", default=False, action="store_true", help="parse *.bvh with the reference's Python loader")
     args = ap.parse_args()
 
     todo = dataset.pending_files(args.src_folder, args.tgt_folder, (".bvh", ".npz"), args.override)
@@ -61,8 +63,12 @@ def main():
         return
     load_bvh = None
     clips, heights, names, fps, kept = [], [], None, [], []
+    parsed = []                                          # (BvhClip, tgt): converted on the GPU in one go below
     for src, tgt in todo:
         try:
+            if src.lower().endswith(".bvh") and not args.reference_loader:
+                parsed.append((bvh.parse_bvh(src), tgt))
+                continue
             if src.lower().endswith(".npz"):
                 z = np.load(src, allow_pickle=False)
                 arr, nm, hgt, f = z["frames"].astype(np.float32), [str(x) for x in z["names"]], float(z["height"]), float(z["fps"])
@@ -80,6 +86,19 @@ def main():
             print(f"Skipping {src}: body list differs from the first file's")
             continue
         clips.append(arr); heights.append(hgt); fps.append(f); kept.append(tgt)
+    # *.bvh files: one device pass per skeleton (files of one dataset share it)
+    while parsed:
+        c0 = parsed[0][0]
+        same = [(c, t) for c, t in parsed if list(c.names) == list(c0.names) and np.array_equal(c.parents, c0.parents) and c.order == c0.order]
+        parsed = [(c, t) for c, t in parsed if not any(c is c2 for c2, _ in same)]
+        streams, rows, hs = bvh.load_bvh_clips([c for c, _ in same], device=args.device, dtype=np.float32)
+        if names is None:
+            names = rows
+        elif rows != names:
+            print(f"Skipping {len(same)} file(s): body list differs from the first file's")
+            continue
+        for (c, tgt), s, hgt in zip(same, streams, hs):
+            clips.append(s.cpu().numpy()); heights.append(float(hgt)); fps.append(float(args.target_fps)); kept.append(tgt)
     motions = dataset.retarget_clips("bvh", args.robot, clips, heights=heights, human_names=names, fps=fps,
                                      height_adjust=False, root_origin_offset=False, device=args.device)
     for tgt, m in zip(kept, motions):
