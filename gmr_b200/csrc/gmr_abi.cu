@@ -12,6 +12,7 @@
 #include "../../include/gmr_b200.h"
 #include "gmr_clip.cuh"
 #include "gmr_bvh.cuh"
+#include "gmr_smplx.cuh"
 
 using namespace gmr;
 
@@ -901,6 +902,30 @@ extern "C" int gmr_bvh_to_stream(int device, void* stream, const double* lpos_de
   e = cudaGetLastError();
   cudaFreeAsync(sign, st);
   cudaFreeAsync(G, st);
+  if (e != cudaSuccess) return fail(-3, cudaGetErrorString(e));
+  return 0;
+}
+
+// ---------------------------------------------------------------- SMPL-X model output -> frame stream
+extern "C" int gmr_smplx_to_stream(int device, void* stream, const float* full_pose_dev, const float* joints_dev,
+                                   int n_joints_in, const int32_t* src_start_dev, const int32_t* clip_of_out_dev,
+                                   const double* time_dev, const int32_t* aligned_dev, int n_frames_in, int n_frames_out,
+                                   int n_joints, const int32_t* parents_dev, int out_dtype, void* stream_out_dev) {
+  if (!full_pose_dev || !joints_dev || !src_start_dev || !clip_of_out_dev || !time_dev || !aligned_dev || !parents_dev ||
+      !stream_out_dev || n_frames_in < 0 || n_frames_out < 0 || n_joints < 1 || n_joints_in < n_joints)
+    return fail(-1, "gmr_smplx_to_stream: bad argument");
+  if (n_joints > SMPLX_MAX_JOINTS) return fail(-1, "gmr_smplx_to_stream: at most 64 joints");
+  if (out_dtype != GMR_F32 && out_dtype != GMR_F64) return fail(-1, "gmr_smplx_to_stream: dtype must be GMR_F32 or GMR_F64");
+  if (n_frames_out == 0) return 0;
+  DevGuard g(device);
+  SmplxArgs a{};
+  a.pose = full_pose_dev; a.joints = joints_dev; a.Jall = n_joints_in; a.src_start = src_start_dev;
+  a.clip_of = clip_of_out_dev; a.time = time_dev; a.aligned = aligned_dev;
+  a.N = n_frames_in; a.N_out = n_frames_out; a.J = n_joints; a.parents = parents_dev; a.out = stream_out_dev;
+  const int tb = 64;
+  if (out_dtype == GMR_F32) smplx_stream_kernel<float><<<(n_frames_out + tb - 1) / tb, tb, 0, (cudaStream_t)stream>>>(a);
+  else smplx_stream_kernel<double><<<(n_frames_out + tb - 1) / tb, tb, 0, (cudaStream_t)stream>>>(a);
+  cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(-3, cudaGetErrorString(e));
   return 0;
 }

@@ -202,6 +202,22 @@ int gmr_bvh_to_stream(int device, void* stream, const double* lpos_dev, const do
                       const int32_t* src_rot_dev, int n_rows, int out_dtype, void* stream_out_dev,
                       int head_row, const int32_t* foot_rows, double* height_out_dev);
 
+/* SMPL-X model output -> human frame stream, for all frames of all clips at once: what
+ * get_smplx_data_offline_fast does (general_motion_retargeting/utils/smpl.py:109-198) - fps alignment
+ * (SLERP of every joint's rotation vector between the two neighbouring source frames :78-107,133-160, linear
+ * interpolation of the joint positions :163-168) and the global-orientation chain R_i = R_parent(i) *
+ * R(rotvec_i) (:178-196).  full_pose [n_frames_in, n_joints, 3] float32 rotation vectors (joint 0 =
+ * global_orient) and joints [n_frames_in, n_joints_in, 3] float32 are what the body model returned (the model
+ * forward itself is outside: licensed files), clips concatenated, clip c = source frames
+ * [src_start[c], src_start[c+1]).  Output frame n belongs to clip clip_of_out[n] and samples it at source time
+ * time[n] (frames, relative to the clip; np.linspace(0, T-1, T // int(src_fps / tgt_fps)) in the reference);
+ * aligned[n] = 0 copies frame (int)time[n] as is (the reference's tgt_fps >= src_fps branch).
+ * stream_out [n_frames_out, n_joints, 7] = pos xyz, quat wxyz in out_dtype.  Device pointers; asynchronous. */
+int gmr_smplx_to_stream(int device, void* stream, const float* full_pose_dev, const float* joints_dev,
+                        int n_joints_in, const int32_t* src_start_dev, const int32_t* clip_of_out_dev,
+                        const double* time_dev, const int32_t* aligned_dev, int n_frames_in, int n_frames_out,
+                        int n_joints, const int32_t* parents_dev, int out_dtype, void* stream_out_dev);
+
 /* Measurement helper (no reference counterpart): measured peak of the CUDA-core FMA pipe in
  * TFLOP/s (fp64 != 0: DFMA, else FFMA) - the compute roofline denominator of bench.py.
  * Synchronous, default stream. */

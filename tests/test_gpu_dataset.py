@@ -104,3 +104,33 @@ def test_bvh_driver_end_to_end(tmp_path):
         assert np.isfinite(m["dof_pos"]).all() and abs(np.linalg.norm(m["root_rot"], axis=1) - 1).max() < 1e-9
     # the first 14 frames are the same motion: same result up to the height guess, which looks at the LAST frame
     assert np.isfinite(m["local_body_pos"]).all()
+
+
+def test_smplx_driver_end_to_end(tmp_path):
+    """scripts/smplx_to_robot_dataset.py on a folder of body-model outputs: fps alignment + orientation chain on the
+    GPU -> batched retarget -> pickles (HEIGHT_ADJUST and ROOT_ORIGIN_OFFSET on, as the reference driver)."""
+    import pickle
+    import subprocess
+    import sys
+    from gmr_b200 import model_pack, synth
+    m, t = model_pack.build_tables("smplx", "unitree_g1")
+    human, heights, names = synth.synth_human_clips(m, t, "smplx", B=1, T=48)          # plausible joint positions
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "smplx_prep_skip4.npz"))
+    src, tgt = tmp_path / "src", tmp_path / "tgt"
+    src.mkdir()
+    T = 41
+    joints = np.zeros((T, 127, 3), np.float32)
+    joints[:, :55] = human[0, :T, :, :3]
+    np.savez(src / "a.npz", full_pose=z["pose"].reshape(T, -1) * 0.3, joints=joints, mocap_frame_rate=np.array(120.0),
+             betas=np.zeros(16))
+    np.savez(src / "b_stagei.npz", full_pose=z["pose"], joints=joints, mocap_frame_rate=np.array(120.0), betas=np.zeros(16))
+    script = os.path.join(os.path.dirname(__file__), "..", "scripts", "smplx_to_robot_dataset.py")
+    r = subprocess.run([sys.executable, script, "--src_folder", str(src), "--tgt_folder", str(tgt), "--robot", "unitree_g1"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert sorted(os.listdir(tgt)) == ["a.pkl"]
+    with open(tgt / "a.pkl", "rb") as f:
+        mo = pickle.load(f)
+    assert mo["root_pos"].shape == (10, 3) and abs(mo["fps"] - 10 / 41 * 120.0) < 1e-12
+    np.testing.assert_allclose(mo["root_pos"][0, :2], 0.0, atol=1e-12)                # ROOT_ORIGIN_OFFSET
+    assert np.isfinite(mo["dof_pos"]).all() and mo["local_body_pos"].shape[0] == 10
