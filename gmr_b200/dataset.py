@@ -122,3 +122,54 @@ def pending_files(src_folder: str, tgt_folder: str, exts, override: bool = False
                 continue
             todo.append((src, tgt))
     return todo
+
+
+# key robot body <- human body pairs of the reference's error log (scripts/fbx_to_robot.py:1148-1153)
+KEY_BODIES = (("pelvis", "Hips"), ("left_wrist_yaw_link", "LeftHand"), ("right_wrist_yaw_link", "RightHand"))
+ERRORS_CSV_HEADER = "frame,error1,error2,pelvis_pos_err,left_hand_pos_err,right_hand_pos_err"
+
+
+def clip_diagnostics(dm: DeviceModel, human_clip, qpos, height=None, offset_to_ground: bool = False, key_bodies=KEY_BODIES):
+    """Per-frame diagnostics of one retargeted clip, all frames at once (frames become the instances of a batch):
+    what scripts/fbx_to_robot.py:1183-1212 computes after each retarget() call -
+    error1() / error2() (motion_retarget.py:188-200: unweighted task-error norms of stage 1 / 2 at the FINAL
+    configuration of the frame) and |robot body - scaled human body| for the key bodies (NaN where either is missing).
+    human_clip [T,h,7], qpos [T,nq] -> dict of float64 arrays [T]: error1, error2, and one per key body."""
+    human_clip = np.asarray(human_clip)
+    T = human_clip.shape[0]
+    model, tables = dm.desc.model, dm.desc.tables
+    br = BatchedRetargeter(dm, T, device=dm.device)
+    br.set_heights([height] * T)
+    q = np.zeros((T, br.nq_max))
+    q[:, :model.nq] = np.asarray(qpos)[:, :model.nq]
+    br.reset(q)
+    scaled = br.target_prep(human_clip, offset_to_ground=offset_to_ground)          # scaled_human_data of every frame
+    xpos, _ = br.fk()
+    out = {}
+    for stage in (0, 1):
+        n = dm.desc.c.n_task[stage]
+        if tables.use_table[stage] and n:
+            e = br.build_qp(stage, scaled)[4][:, :n]
+            out[f"error{stage + 1}"] = torch.linalg.vector_norm(e.reshape(T, -1), dim=1).cpu().numpy()
+        else:
+            out[f"error{stage + 1}"] = np.zeros(T)
+    scaled, xpos = scaled.cpu().numpy(), xpos.cpu().numpy()
+    for robot_body, human_body in key_bodies:
+        if robot_body in model.body_names and human_body in tables.scaled_names:
+            d = xpos[:, model.body_names.index(robot_body)] - scaled[:, list(tables.scaled_names).index(human_body), :3]
+            out[robot_body] = np.linalg.norm(d, axis=1)
+        else:
+            out[robot_body] = np.full(T, np.nan)
+    br.close()
+    return out
+
+
+def write_errors_csv(path: str, diag: dict, key_bodies=KEY_BODIES) -> None:
+    """The --errors_csv file of scripts/fbx_to_robot.py (:982-990 header on creation, appended rows :1211-1212)."""
+    new = not os.path.exists(path)
+    with open(path, "a") as f:
+        if new:
+            f.write(ERRORS_CSV_HEADER + "\n")
+        cols = [diag["error1"], diag["error2"]] + [diag[rb] for rb, _ in key_bodies]
+        for i in range(len(cols[0])):
+            f.write(f"{i}," + ",".join(str(float(c[i])) for c in cols) + "\n")

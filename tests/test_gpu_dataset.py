@@ -134,3 +134,49 @@ def test_smplx_driver_end_to_end(tmp_path):
     assert mo["root_pos"].shape == (10, 3) and abs(mo["fps"] - 10 / 41 * 120.0) < 1e-12
     np.testing.assert_allclose(mo["root_pos"][0, :2], 0.0, atol=1e-12)                # ROOT_ORIGIN_OFFSET
     assert np.isfinite(mo["dof_pos"]).all() and mo["local_body_pos"].shape[0] == 10
+
+
+def test_clip_diagnostics_match_the_per_frame_log(tmp_path):
+    """dataset.clip_diagnostics (all frames of a clip at once) == what scripts/fbx_to_robot.py:1183-1212 logs after
+    each retarget() call: error1(), error2(), key-body position errors; and the --errors_csv file format."""
+    from gmr_b200 import dataset, model_pack, synth
+    from gmr_b200.engine import DeviceModel
+    from gmr_b200.motion_retarget import GeneralMotionRetargeting
+    from oracle.gmr_oracle_np import OracleRetargeter
+    T = 7
+    m, t = model_pack.build_tables("bvh", "unitree_g1")
+    human, heights, names = synth.synth_human_clips(m, t, "bvh", B=1, T=T, seed=4, dtype=np.float64)
+    frames = [{n: (human[0, i, k, :3].tolist(), human[0, i, k, 3:].tolist()) for k, n in enumerate(names)} for i in range(T)]
+    gmr = GeneralMotionRetargeting("bvh", "unitree_g1", actual_human_height=float(heights[0]))
+    ref = OracleRetargeter(m, t, actual_human_height=float(heights[0]))
+    idx = [names.index(b) for b in t.scaled_names]
+    rows, qpos = [], []
+    for i in range(T):
+        qpos.append(gmr.retarget(frames[i]))
+        ref.retarget(human[0, i][idx])
+        row = [gmr.error1(), gmr.error2()]
+        # the oracle of the same two calls
+        np.testing.assert_allclose(row[0], ref.error(ref._tasks(0, ref.scaled_human_data)), atol=1e-7)
+        for rb, hb in dataset.KEY_BODIES:
+            bid = gmr.model.body(rb).id
+            row.append(float(np.linalg.norm(gmr.configuration.data.xpos[bid] - gmr.scaled_human_data[hb][0])))
+        rows.append(row)
+    rows = np.array(rows)
+    dm = DeviceModel.load("bvh", "unitree_g1", names)
+    d = dataset.clip_diagnostics(dm, human[0], np.array(qpos), height=float(heights[0]))
+    np.testing.assert_allclose(d["error1"], rows[:, 0], atol=1e-10)
+    np.testing.assert_allclose(d["error2"], rows[:, 1], atol=1e-10)
+    for k, (rb, _) in enumerate(dataset.KEY_BODIES):
+        np.testing.assert_allclose(d[rb], rows[:, 2 + k], atol=1e-10)
+    p = tmp_path / "errors.csv"
+    dataset.write_errors_csv(str(p), d)
+    dataset.write_errors_csv(str(p), d)                       # appends without a second header
+    lines = p.read_text().strip().split("\n")
+    assert lines[0] == "frame,error1,error2,pelvis_pos_err,left_hand_pos_err,right_hand_pos_err" and len(lines) == 1 + 2 * T
+    assert lines[1].split(",")[0] == "0" and abs(float(lines[1].split(",")[1]) - rows[0, 0]) < 1e-10
+    # a robot without those bodies logs NaN there
+    m2, t2 = model_pack.build_tables("smplx", "booster_t1")
+    h2, hg2, n2 = synth.synth_human_clips(m2, t2, "smplx", B=1, T=3, seed=1, dtype=np.float64)
+    dm2 = DeviceModel.load("smplx", "booster_t1", n2)
+    d2 = dataset.clip_diagnostics(dm2, h2[0], np.tile(m2.qpos0, (3, 1)), height=float(hg2[0]))
+    assert np.isnan(d2["left_wrist_yaw_link"]).all() and np.isfinite(d2["error1"]).all()
