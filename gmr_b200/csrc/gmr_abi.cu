@@ -408,10 +408,10 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h) 
   auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };   // keep 16-byte alignment
   L.q = take(nq); L.scaled = take(7 * s); L.x = take(nv); L.H = take(nnz);
   const int region = o;
-  L.xpos = take(3 * nbody); L.xquat = take(4 * nbody); L.S = take(6 * nv); L.e = take(6 * m);
+  L.xpos = take(3 * nbody); L.xquat = take(GMR_QS * nbody); L.S = take(6 * nv); L.e = take(6 * m);
   L.K = take(21 * m); L.g = take(6 * m);
   L.tl = L.K; L.ql = L.tl + ((3 * nbody + 1) & ~1);          // FK local transforms alias K/g
-  o = std::max(o, L.ql + ((4 * nbody + 1) & ~1));
+  o = std::max(o, L.ql + ((GMR_QS * nbody + 1) & ~1));
   o = std::max(o, (L.K + 7 * h + 1) & ~1);                             // one frame of the human stream is staged in K/g
   if (6 * nv <= L.S - L.xpos) L.F = L.xpos;                   // F_l aliases the body poses when it fits
   else L.F = take(6 * nv);

@@ -238,7 +238,7 @@ __global__ void fk_kernel(const StageArgs a) {
   __syncwarp();
   stage_fk(mv, a.lay, sm, lane);
   for (int i = lane; i < M.nbody * 3; i += 32) a.xpos_out[(size_t)inst * a.nbody_max * 3 + i] = sm[a.lay.xpos + i];
-  for (int i = lane; i < M.nbody * 4; i += 32) a.xquat_out[(size_t)inst * a.nbody_max * 4 + i] = sm[a.lay.xquat + i];
+  for (int i = lane; i < M.nbody * 4; i += 32) a.xquat_out[(size_t)inst * a.nbody_max * 4 + i] = sm[a.lay.xquat + GMR_QS * (i >> 2) + (i & 3)];
 }
 
 __global__ void build_qp_kernel(const StageArgs a) {

@@ -102,6 +102,10 @@ struct ModelView {
   }
 };
 
+// Body quaternions are stored with a stride of 5 doubles: lane = body accesses with a stride of 4 doubles
+// (32 bytes) hit every bank four times over, 40 bytes spread a half-warp over all 32 banks.
+#define GMR_QS 5
+
 // Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
 struct Lay {
   int q, scaled, x, H;                    // persistent across the QP solve (H: nnz packed tree rows)

@@ -143,7 +143,7 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
       }
     }
     double* T0 = T_even + 3 * b;
-    double* Q0 = Q_even + 4 * b;
+    double* Q0 = Q_even + GMR_QS * b;
     T0[0] = t[0]; T0[1] = t[1]; T0[2] = t[2];
     Q0[0] = qq[0]; Q0[1] = qq[1]; Q0[2] = qq[2]; Q0[3] = qq[3];
   }
@@ -160,9 +160,9 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
     for (int b = lane; b < nb; b += 32) {
       const int anc2 = jump[r * nb + b];                                // 2^r-th ancestor, -1: already in the world frame
       double t[3] = {Ti[3 * b], Ti[3 * b + 1], Ti[3 * b + 2]};
-      double qq[4] = {Qi[4 * b], Qi[4 * b + 1], Qi[4 * b + 2], Qi[4 * b + 3]};
+      double qq[4] = {Qi[GMR_QS * b], Qi[GMR_QS * b + 1], Qi[GMR_QS * b + 2], Qi[GMR_QS * b + 3]};
       if (anc2 >= 0) {
-        const double aq[4] = {Qi[4 * anc2], Qi[4 * anc2 + 1], Qi[4 * anc2 + 2], Qi[4 * anc2 + 3]};
+        const double aq[4] = {Qi[GMR_QS * anc2], Qi[GMR_QS * anc2 + 1], Qi[GMR_QS * anc2 + 2], Qi[GMR_QS * anc2 + 3]};
         double rt[3], nq[4];
         qrot(aq, t, rt);
         t[0] = Ti[3 * anc2] + rt[0]; t[1] = Ti[3 * anc2 + 1] + rt[1]; t[2] = Ti[3 * anc2 + 2] + rt[2];
@@ -170,13 +170,13 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
         qq[0] = nq[0]; qq[1] = nq[1]; qq[2] = nq[2]; qq[3] = nq[3];
       }
       To[3 * b] = t[0]; To[3 * b + 1] = t[1]; To[3 * b + 2] = t[2];
-      Qo[4 * b] = qq[0]; Qo[4 * b + 1] = qq[1]; Qo[4 * b + 2] = qq[2]; Qo[4 * b + 3] = qq[3];
+      Qo[GMR_QS * b] = qq[0]; Qo[GMR_QS * b + 1] = qq[1]; Qo[GMR_QS * b + 2] = qq[2]; Qo[GMR_QS * b + 3] = qq[3];
     }
     __syncwarp();
   }
   // mju_normalize4 of every body quaternion, all bodies at once (the products above keep unit norm
   // to rounding, so normalising after the sweep instead of inside it changes results by ~1e-16)
-  for (int b = 1 + lane; b < nb; b += 32) normalize4(xquat + 4 * b);
+  for (int b = 1 + lane; b < nb; b += 32) normalize4(xquat + GMR_QS * b);
   __syncwarp();
   // ---- pass C
   const int ref = M.ref_body;
@@ -192,12 +192,12 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
       if (kind == DOF_FREE_R) {
         const int i = k - mv(M.jnt_dofadr)[mv(M.body_jntadr)[b]] - 3;
         double R[9];
-        q2mat(xquat + 4 * b, R);
+        q2mat(xquat + GMR_QS * b, R);
         aw[0] = R[i]; aw[1] = R[3 + i]; aw[2] = R[6 + i];
       } else {
         const int p = mv(M.body_parent)[b];
         const double al[3] = {sk[3], sk[4], sk[5]};
-        qrot(xquat + 4 * p, al, aw);
+        qrot(xquat + GMR_QS * p, al, aw);
       }
       if (kind == DOF_SLIDE) {
         sk[0] = aw[0]; sk[1] = aw[1]; sk[2] = aw[2]; sk[3] = sk[4] = sk[5] = 0;
@@ -253,7 +253,7 @@ __device__ __forceinline__ double stage_errors(const MV& mv, const Lay& lay, dou
     const int body = mv(M.task_body)[stage * lay.maxt + lane];
     const double* tgt = sm + lay.scaled + 7 * mv(M.task_src)[stage * lay.maxt + lane];
     const double* xp = sm + lay.xpos + 3 * body;
-    const double* xq = sm + lay.xquat + 4 * body;
+    const double* xq = sm + lay.xquat + GMR_QS * body;
     double qi[4] = {xq[0], -xq[1], -xq[2], -xq[3]}, qbt[4], d[3] = {tgt[0] - xp[0], tgt[1] - xp[1], tgt[2] - xp[2]}, pbt[3], e[6];
     qmul(qi, tgt + 3, qbt);
     qrot(qi, d, pbt);
@@ -293,7 +293,7 @@ __device__ __forceinline__ double stage_stiffness(const MV& mv, const Lay& lay, 
     mu = a * (ev[0] * ev[0] + ev[1] * ev[1] + ev[2] * ev[2]) + b * (w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
     const double th2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
     double R[9], Rt[9];
-    q2mat(sm + lay.xquat + 4 * body, R);
+    q2mat(sm + lay.xquat + GMR_QS * body, R);
     Rt[0] = R[0]; Rt[1] = R[3]; Rt[2] = R[6]; Rt[3] = R[1]; Rt[4] = R[4]; Rt[5] = R[7]; Rt[6] = R[2]; Rt[7] = R[5]; Rt[8] = R[8];
     double P[9], Pr[9];
     if (th2 < LIE_EPS) {            // mink SE3.ljacinv returns the identity here
