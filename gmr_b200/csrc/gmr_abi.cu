@@ -225,6 +225,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       }
     }
   }
+  elim_ops.resize(elim_ops.size() + 2 * 64, 0);      // slack: the kernel fetches the op word one pass ahead
   // levels (level 1 first)
   std::vector<int> level_start(nlevel + 1, 0), level_body;
   for (int lv = 1; lv <= nlevel; lv++) {
@@ -292,9 +293,20 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
     if (d->scaled_human_index[i] < 0 || d->scaled_human_index[i] >= d->n_human) return fail(-5, "scaled_human_index out of range");
 
   // ---- pack and upload
+  std::vector<double> body_quat_padded((size_t)GMR_QS * nb, 0.0);
+  for (int b = 0; b < nb; b++)
+    for (int i = 0; i < 4; i++) body_quat_padded[(size_t)GMR_QS * b + i] = d->body_quat[4 * b + i];
+  // bodies whose pose the IK reads: owners of joints, task frames, every ancestor of those, and the world
+  std::vector<char> fk_need(nb, 0);
+  fk_need[0] = 1;
+  for (int b = 1; b < nb; b++) if (d->body_jntnum[b] > 0) fk_need[b] = 1;
+  for (int v : task_body) if (v > 0 && v < nb) fk_need[v] = 1;
+  for (int b = nb - 1; b > 0; b--) if (fk_need[b]) fk_need[d->body_parentid[b]] = 1;
+  std::vector<short> fk_body;
+  for (int b = 0; b < nb; b++) if (fk_need[b]) fk_body.push_back((short)b);
   Blob bl;
   size_t o_parent = bl.push(vec(d->body_parentid, nb)), o_bpos = bl.push(vec(d->body_pos, 3 * nb)),
-         o_bquat = bl.push(vec(d->body_quat, 4 * nb)), o_jadr = bl.push(vec(d->body_jntadr, nb)),
+         o_bquat = bl.push(body_quat_padded), o_jadr = bl.push(vec(d->body_jntadr, nb)),
          o_jnum = bl.push(vec(d->body_jntnum, nb)), o_lstart = bl.push(level_start), o_lbody = bl.push(level_body),
          o_jtype = bl.push(vec(d->jnt_type, nj)), o_jq = bl.push(vec(d->jnt_qposadr, nj)),
          o_jd = bl.push(vec(d->jnt_dofadr, nj)), o_jaxis = bl.push(vec(d->jnt_axis, 3 * nj)),
@@ -306,7 +318,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
          o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot),
          o_dd = bl.push(dof_depth), o_rp = bl.push(dof_rowptr), o_an = bl.push(dof_anc), o_ar = bl.push(dof_ancrow),
          o_er = bl.push(ent_row), o_tpm = bl.push(topmask), o_chm = bl.push(childmask), o_tls = bl.push(tasklev_start),
-         o_tlt = bl.push(tasklev_task), o_fj = bl.push(fk_jump), o_el = bl.push(elim_lane), o_eo = bl.push(elim_ops), o_es = bl.push(elim_opstart);
+         o_tlt = bl.push(tasklev_task), o_fj = bl.push(fk_jump), o_fb = bl.push(fk_body), o_el = bl.push(elim_lane), o_eo = bl.push(elim_ops), o_es = bl.push(elim_opstart);
   const size_t staged_bytes = (bl.bytes.size() + 15) & ~size_t(15);
 
   // FK tail tables (KinematicsModel semantics: bodies under the first top-level body, float32, xyzw)
@@ -379,6 +391,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.elim_lane = (const int2*)(B0 + o_el); h.elim_ops = (const int2*)(B0 + o_eo);
   h.elim_opstart = (const int*)(B0 + o_es); h.n_elim_step = n_elim_step;
   h.fk_rounds = fk_rounds; h.fk_jump = (const short*)(B0 + o_fj);
+  h.n_fk = (int)fk_body.size(); h.fk_body = (const short*)(B0 + o_fb);
   h.tasklev_task = (const int*)(B0 + o_tlt); h.n_tasklev[0] = n_tasklev[0]; h.n_tasklev[1] = n_tasklev[1];
   m->max_task = std::max(h.n_task[0], h.n_task[1]);
   char* T0 = m->tail_blob;
@@ -402,23 +415,37 @@ extern "C" int gmr_model_destroy(gmr_model* m) {
 }
 
 // ---------------------------------------------------------------- batch
+// the instantiation of the fused kernel for (stream dtype, model staged in shared memory)
+static const void* clip_kernel_ptr(int dtype, bool staged) {
+  if (dtype == GMR_F32) return staged ? (const void*)clip_kernel<float, true> : (const void*)clip_kernel<float, false>;
+  return staged ? (const void*)clip_kernel<double, true> : (const void*)clip_kernel<double, false>;
+}
+
 static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h) {
+  // Two scratch regions behind the per-frame state (q, targets, x), each reused along the tick:
+  //   region 1: body poses + spatial axes (FK .. assembly; F_l aliases the poses, dead after the stiffness pass),
+  //             then the factor L, the right-hand side and one row of L during the solve;
+  //   region 2: local FK transforms / the staged human frame -> task errors e, stiffness K, g (errors .. assembly
+  //             step 2) -> H, written by assembly step 3 once K/g have been folded into F, read-only during the solve.
   Lay L{};
   int o = 0;
   auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };   // keep 16-byte alignment
-  L.q = take(nq); L.scaled = take(7 * s); L.x = take(nv); L.H = take(nnz);
-  const int region = o;
-  L.xpos = take(3 * nbody); L.xquat = take(GMR_QS * nbody); L.S = take(6 * nv); L.e = take(6 * m);
-  L.K = take(21 * m); L.g = take(6 * m);
+  L.q = take(nq); L.scaled = take(7 * s); L.x = take(nv);
+  const int region1 = o;
+  L.xpos = take(3 * nbody); L.xquat = take(GMR_QS * nbody); L.S = take(GMR_SS * nv);
+  if (GMR_SS * nv <= L.S - L.xpos) L.F = L.xpos;              // F_l aliases the body poses when it fits
+  else L.F = take(GMR_SS * nv);
+  L.L = region1;                                 // the factor overlays the kinematics scratch
+  L.rv = region1 + nnz;                          // right-hand side directly behind the factor (one index space)
+  L.lrow = (region1 + nnz + nv + 31) & ~31;      // 256-byte aligned: the program ORs lane offsets into its address
+  o = std::max(o, L.lrow + 32);
+  const int region2 = o;
+  L.e = take(6 * m); L.K = take(21 * m); L.g = take(6 * m);
   L.tl = L.K; L.ql = L.tl + ((3 * nbody + 1) & ~1);          // FK local transforms alias K/g
   o = std::max(o, L.ql + ((GMR_QS * nbody + 1) & ~1));
-  o = std::max(o, (L.K + 7 * h + 1) & ~1);                             // one frame of the human stream is staged in K/g
-  if (6 * nv <= L.S - L.xpos) L.F = L.xpos;                   // F_l aliases the body poses when it fits
-  else L.F = take(6 * nv);
-  L.L = region;                                  // the factor overlays the kinematics scratch
-  L.rv = region + nnz;                           // right-hand side directly behind the factor (one index space)
-  L.lrow = (region + nnz + nv + 31) & ~31;        // 256-byte aligned: the program ORs lane offsets into its address
-  o = std::max(o, L.lrow + 32);
+  o = std::max(o, (L.K + 7 * h + 1) & ~1);                   // one frame of the human stream is staged in K/g
+  L.H = region2;                                             // H aliases e/K/g
+  o = std::max(o, (L.H + nnz + 1) & ~1);
   L.total = (o + 31) & ~31;
   L.maxt = GMR_MAX_TASKS;
   return L;
@@ -468,27 +495,27 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device);
   if (e == cudaSuccess) {
     // the fused kernel is compiled for 128 registers (16 warps per SM): pick the CTA width that puts
-    // the most warps on an SM (the staged model is per CTA, so wide CTAs amortise it); ties go to
-    // the narrower CTA
+    // the most warps on an SM; ties go to the wider CTA (the staged model is per CTA)
     const size_t blob = n_models == 1 ? models[0]->staged_bytes : 0;
     const size_t fixed = 2048 + 1024;   // static shared memory of the kernel + the per-CTA reservation
     const size_t sm_total = 228 * 1024;
     b->smem_model = n_models == 1 && per_warp + blob + fixed <= (size_t)dev_smem && !getenv("GMR_DEBUG_GLOBAL_MODEL");
     const size_t extra = fixed + (b->smem_model ? blob : 0);
+    const int max_w = GMR_CTA_THREADS / 32;
     int best_w = 1, best_total = 0;
-    for (int w = 1; w <= 16; w++) {
+    for (int w = 1; w <= max_w; w++) {
       if ((size_t)w * per_warp + extra > (size_t)dev_smem + 1024) break;
-      int ctas = (int)std::min<size_t>(sm_total / ((size_t)w * per_warp + extra), (size_t)(16 / w));
-      if (ctas * w > best_total) { best_total = ctas * w; best_w = w; }
+      int ctas = (int)std::min<size_t>(sm_total / ((size_t)w * per_warp + extra), (size_t)(max_w / w));
+      if (ctas * w >= best_total) { best_total = ctas * w; best_w = w; }
     }
-    if (const char* ev = getenv("GMR_DEBUG_WARPS")) best_w = std::max(1, std::min(16, atoi(ev)));
+    if (const char* ev = getenv("GMR_DEBUG_WARPS")) best_w = std::max(1, std::min(max_w, atoi(ev)));
     b->warps_per_cta = std::min(best_w, B);
     b->smem_bytes = per_warp * b->warps_per_cta;
     b->clip_smem_bytes = b->smem_bytes + (b->smem_model ? blob : 0);
     if (b->clip_smem_bytes + 2048 > (size_t)dev_smem) e = cudaErrorInvalidConfiguration;
   }
-  const void* kf = b->smem_model ? (const void*)clip_kernel<float, true> : (const void*)clip_kernel<float, false>;
-  const void* kd = b->smem_model ? (const void*)clip_kernel<double, true> : (const void*)clip_kernel<double, false>;
+  const void* kf = clip_kernel_ptr(GMR_F32, b->smem_model);
+  const void* kd = clip_kernel_ptr(GMR_F64, b->smem_model);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->clip_smem_bytes);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(kd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->clip_smem_bytes);
   int per_sm = 0;
@@ -619,13 +646,8 @@ static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const in
   CU(cudaMemsetAsync(b->d_done, 0, sizeof(int) * (size_t)b->B, b->stream));
   CU(cudaMemsetAsync(b->d_counter, 0, sizeof(int), b->stream));
   const dim3 grid(b->grid), block(32 * b->warps_per_cta);
-  if (b->smem_model) {
-    if (dtype == GMR_F32) clip_kernel<float, true><<<grid, block, b->clip_smem_bytes, b->stream>>>(a);
-    else clip_kernel<double, true><<<grid, block, b->clip_smem_bytes, b->stream>>>(a);
-  } else {
-    if (dtype == GMR_F32) clip_kernel<float, false><<<grid, block, b->clip_smem_bytes, b->stream>>>(a);
-    else clip_kernel<double, false><<<grid, block, b->clip_smem_bytes, b->stream>>>(a);
-  }
+  void* kargs[] = {(void*)&a};
+  CU(cudaLaunchKernel(clip_kernel_ptr(dtype, b->smem_model), grid, block, kargs, b->clip_smem_bytes, b->stream));
   CU(cudaGetLastError());
   return 0;
 }
@@ -743,9 +765,10 @@ static StageArgs stage_args(gmr_batch* b) {
   return a;
 }
 #define STAGE_LAUNCH(kernel, b, a) do { \
-    const int w_ = b->warps_per_cta; \
-    CU(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes)); \
-    kernel<<<(b->B + w_ - 1) / w_, 32 * w_, b->smem_bytes, b->stream>>>(a); \
+    const int w_ = std::min(b->warps_per_cta, 8);      /* stage kernels carry no launch bound: stay narrow */ \
+    const size_t sm_ = sizeof(double) * (size_t)b->lay.total * w_; \
+    CU(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); \
+    kernel<<<(b->B + w_ - 1) / w_, 32 * w_, sm_, b->stream>>>(a); \
     CU(cudaGetLastError()); } while (0)
 
 extern "C" int gmr_target_prep(gmr_batch* b, const void* human_dev, int human_dtype, int offset_to_ground, double* scaled_out_dev) {

@@ -10,10 +10,9 @@
 
 namespace gmr {
 
-#ifndef GMR_MIN_CTAS
-#define GMR_MIN_CTAS 1
+// One CTA of up to 16 warps per SM, 128 registers per thread.  (Registers are allocated to a CTA in groups of
+// four warps, so the next step up is 20 warps at 96 registers: measured 17 % slower on the bench workload.)
 #define GMR_CTA_THREADS 512
-#endif
 
 struct RunArgs {
   const DevModel* models;        // [n_models]
@@ -69,7 +68,7 @@ __device__ __forceinline__ int next_stage(const DevModel& M, int stage) {
 // iteration its own instance is in, and each stage function has exactly one call site.
 // SM = true: single-model batch, model tables staged in shared memory.
 template <typename TIn, bool SM>
-__global__ void __launch_bounds__(GMR_CTA_THREADS, GMR_MIN_CTAS) clip_kernel(const RunArgs a) {
+__global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs a) {
   extern __shared__ __align__(256) double smem[];
   __shared__ unsigned short pair_tab[PAIR_TAB_SIZE];
   __shared__ DevModel smodel;
@@ -130,7 +129,7 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, GMR_MIN_CTAS) clip_kernel(con
     }
     const DevModel& M = mv.M();
     // ---- Kernel 2: FK (q changed: integrate of the previous tick, or a new clip)
-    if (s.need_fk) { stage_fk(mv, lay, sm, lane); s.need_fk = false; }
+    if (s.need_fk) { stage_fk<false>(mv, lay, sm, lane); s.need_fk = false; }
     // ---- Kernel 4: control
     bool solve = false;
     for (;;) {
@@ -236,7 +235,7 @@ __global__ void fk_kernel(const StageArgs a) {
   const DevModel& M = mv.M();
   for (int i = lane; i < M.nq; i += 32) sm[a.lay.q + i] = a.q[(size_t)inst * a.nq_max + i];
   __syncwarp();
-  stage_fk(mv, a.lay, sm, lane);
+  stage_fk<true>(mv, a.lay, sm, lane);
   for (int i = lane; i < M.nbody * 3; i += 32) a.xpos_out[(size_t)inst * a.nbody_max * 3 + i] = sm[a.lay.xpos + i];
   for (int i = lane; i < M.nbody * 4; i += 32) a.xquat_out[(size_t)inst * a.nbody_max * 4 + i] = sm[a.lay.xquat + GMR_QS * (i >> 2) + (i & 3)];
 }
@@ -253,13 +252,14 @@ __global__ void build_qp_kernel(const StageArgs a) {
   for (int i = lane; i < M.nq; i += 32) sm[lay.q + i] = a.q[(size_t)inst * a.nq_max + i];
   for (int i = lane; i < M.n_scaled * 7; i += 32) sm[lay.scaled + i] = a.scaled[(size_t)inst * a.s_max * 7 + i];
   __syncwarp();
-  stage_fk(mv, lay, sm, lane);
+  stage_fk<false>(mv, lay, sm, lane);
   stage_errors(mv, lay, sm, a.stage, lane);
   const double mu = stage_stiffness(mv, lay, sm, a.stage, lane);
+  const int n = M.nv, m = M.n_task[a.stage];
+  if (a.e_out) for (int i = lane; i < 6 * m; i += 32) a.e_out[(size_t)inst * a.m_max * 6 + i] = sm[lay.e + i];   // H overwrites e
+  __syncwarp();
   double qc[2], qlo[2], qhi[2];
   stage_assemble(mv, lay, sm, a.stage, mu, lane, qc, qlo, qhi);
-  const int n = M.nv, m = M.n_task[a.stage];
-  if (a.e_out) for (int i = lane; i < 6 * m; i += 32) a.e_out[(size_t)inst * a.m_max * 6 + i] = sm[lay.e + i];
   double* Ho = a.H_out + (size_t)inst * a.nv_max * a.nv_max;
   for (int idx = lane; idx < n * n; idx += 32) {
     const int i = idx / n, j = idx % n;
@@ -291,7 +291,7 @@ __global__ void solve_ik_kernel(const StageArgs a) {
   for (int i = lane; i < M.nq; i += 32) sm[lay.q + i] = a.q[(size_t)inst * a.nq_max + i];
   for (int i = lane; i < M.n_scaled * 7; i += 32) sm[lay.scaled + i] = a.scaled[(size_t)inst * a.s_max * 7 + i];
   __syncwarp();
-  stage_fk(mv, lay, sm, lane);
+  stage_fk<false>(mv, lay, sm, lane);
   stage_errors(mv, lay, sm, a.stage, lane);
   const double mu = stage_stiffness(mv, lay, sm, a.stage, lane);
   double qc[2], qlo[2], qhi[2];

@@ -29,9 +29,11 @@ struct DevModel {
   // bodies
   const int* body_parent;    // [nbody]
   const double* body_pos;    // [nbody*3]
-  const double* body_quat;   // [nbody*4]
+  const double* body_quat;   // [nbody*GMR_QS] wxyz, padded like the pose quaternions (lane = body reads)
   const int* body_jntadr;    // [nbody]
   const int* body_jntnum;    // [nbody]
+  int n_fk;                  // bodies the IK needs: those with joints, task frames, their ancestors, the world
+  const short* fk_body;      // [n_fk] increasing body ids, entry 0 = world
   int fk_rounds;             // ceil(log2(deepest body))
   const short* fk_jump;      // [fk_rounds*nbody] 2^r-th ancestor of each body, -1 once that is the world
   const int* level_start;    // [nlevel+1] into level_body (level 1 = children of world)
@@ -105,10 +107,14 @@ struct ModelView {
 // Body quaternions are stored with a stride of 5 doubles: lane = body accesses with a stride of 4 doubles
 // (32 bytes) hit every bank four times over, 40 bytes spread a half-warp over all 32 banks.
 #define GMR_QS 5
+// Spatial axes S_k and the assembly's F_l are 6-vectors stored with a stride of 7 doubles: an even stride
+// puts 16 consecutive dofs on 8 bank pairs (2-way conflicts for lane = dof and for the H fill), 7 on 16.
+#define GMR_SS 7
 
 // Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
 struct Lay {
-  int q, scaled, x, H;                    // persistent across the QP solve (H: nnz packed tree rows)
+  int q, scaled, x;                       // per-frame state: configuration, targets, the last solve's dq
+  int H;                                  // nnz packed tree rows; aliases e/K/g (written once they are folded into F)
   int xpos, xquat, S, e, K, g;            // kinematics / assembly scratch ...
   int tl, ql;                             // FK local transforms (alias K/g: dead before the stiffness pass)
   int F;                                  // F_l = Kc_l S_l of the assembly (aliases xpos/xquat: dead after the stiffness pass)

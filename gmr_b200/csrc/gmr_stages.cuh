@@ -82,7 +82,7 @@ __device__ __forceinline__ void stage_prep(const MV& mv, const Lay& lay, double*
 // mj_kinematics in three passes:
 //   A (lane = body, all bodies at once): the body's LOCAL transform, joints included -
 //       tl = body_pos + R(body_quat) sum(slide axis * value),  ql = body_quat (x) prod(hinge rotations),
-//       and each joint axis expressed in the PARENT frame (al, parked in S[6k+3..5]);
+//       and each joint axis expressed in the PARENT frame (al, parked in S[k][3..5]);
 //   B (pointer jumping, lane = body): compose every body's transform with that of its 2^r-th ancestor,
 //       r = 0, 1, ...: ceil(log2(tree depth)) rounds over all bodies instead of one pass per level;
 //   C (lane = dof): spatial axis S_k = (v_O, w): twist of the dof expressed at the reference point O =
@@ -90,7 +90,10 @@ __device__ __forceinline__ void stage_prep(const MV& mv, const Lay& lay, double*
 //       column of ANY descendant frame at x is [v_O + w x (x - O); w].
 // Joint anchors are the body origin (jnt_pos = 0, checked at model creation) and slides precede
 // hinges inside a body, which is what makes the local transform independent of the parent.
-template <class MV>
+// ALL = false: only the bodies the IK needs are swept (M.fk_body: bodies with joints, task frames, their
+// ancestors and the world - 31 of 39 for unitree_g1, one pass of the warp instead of two); the poses of the other
+// bodies are then stale.  ALL = true (gmr_fk, diagnostics): every body.
+template <bool ALL, class MV>
 __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* sm, int lane) {
   const DevModel& M = mv.M();
   const double* q = sm + lay.q;
@@ -106,8 +109,11 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
   double* const T_odd = (R & 1) ? xpos : tl;
   double* const Q_even = (R & 1) ? ql : xquat;
   double* const Q_odd = (R & 1) ? xquat : ql;
+  const int nfk = ALL ? nb : M.n_fk;
+  const short* fkb = mv(M.fk_body);
   // ---- pass A: local transform of every body (relative to its parent)
-  for (int b = lane; b < nb; b += 32) {
+  for (int i = lane; i < nfk; i += 32) {
+    const int b = ALL ? i : fkb[i];
     double t[3] = {0, 0, 0}, qq[4] = {1, 0, 0, 0};
     if (b > 0) {
       const int jadr = mv(M.body_jntadr)[b], jnum = mv(M.body_jntnum)[b];
@@ -118,7 +124,7 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
         normalize4(qq);            // qpos may hold any quaternion; everything below needs a rotation
       } else {
         const double* bpp = mv(M.body_pos) + 3 * b;
-        const double* bqp = mv(M.body_quat) + 4 * b;
+        const double* bqp = mv(M.body_quat) + GMR_QS * b;
         t[0] = bpp[0]; t[1] = bpp[1]; t[2] = bpp[2];
         qq[0] = bqp[0]; qq[1] = bqp[1]; qq[2] = bqp[2]; qq[3] = bqp[3];
         for (int j = jadr; j < jadr + jnum; j++) {
@@ -127,7 +133,7 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
           const double ax[3] = {axp[0], axp[1], axp[2]};
           double al[3];
           qrot(qq, ax, al);                                             // axis in the parent frame
-          S[6 * da + 3] = al[0]; S[6 * da + 4] = al[1]; S[6 * da + 5] = al[2];
+          S[GMR_SS * da + 3] = al[0]; S[GMR_SS * da + 4] = al[1]; S[GMR_SS * da + 5] = al[2];
           const double val = q[qa] - mv(M.qpos0)[qa];
           if (mv(M.jnt_type)[j] == 2) {                                 // slide
             t[0] += al[0] * val; t[1] += al[1] * val; t[2] += al[2] * val;
@@ -157,7 +163,8 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
     const double* Qi = (r & 1) ? Q_odd : Q_even;
     double* To = (r & 1) ? T_even : T_odd;
     double* Qo = (r & 1) ? Q_even : Q_odd;
-    for (int b = lane; b < nb; b += 32) {
+    for (int i = lane; i < nfk; i += 32) {
+      const int b = ALL ? i : fkb[i];
       const int anc2 = jump[r * nb + b];                                // 2^r-th ancestor, -1: already in the world frame
       double t[3] = {Ti[3 * b], Ti[3 * b + 1], Ti[3 * b + 2]};
       double qq[4] = {Qi[GMR_QS * b], Qi[GMR_QS * b + 1], Qi[GMR_QS * b + 2], Qi[GMR_QS * b + 3]};
@@ -176,14 +183,14 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
   }
   // mju_normalize4 of every body quaternion, all bodies at once (the products above keep unit norm
   // to rounding, so normalising after the sweep instead of inside it changes results by ~1e-16)
-  for (int b = 1 + lane; b < nb; b += 32) normalize4(xquat + GMR_QS * b);
+  for (int i = 1 + lane; i < nfk; i += 32) normalize4(xquat + GMR_QS * (ALL ? i : fkb[i]));      // entry 0 is the world
   __syncwarp();
   // ---- pass C
   const int ref = M.ref_body;
   const double O[3] = {xpos[3 * ref], xpos[3 * ref + 1], xpos[3 * ref + 2]};    // world (body 0) has xpos = 0
   for (int k = lane; k < M.nv; k += 32) {
     const int kind = mv(M.dof_kind)[k], b = mv(M.dof_body)[k];
-    double* sk = S + 6 * k;
+    double* sk = S + GMR_SS * k;
     if (kind == DOF_FREE_T) {
       const int i = k - mv(M.jnt_dofadr)[mv(M.body_jntadr)[b]];
       sk[0] = (i == 0); sk[1] = (i == 1); sk[2] = (i == 2); sk[3] = sk[4] = sk[5] = 0;
@@ -191,9 +198,8 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
       double aw[3];
       if (kind == DOF_FREE_R) {
         const int i = k - mv(M.jnt_dofadr)[mv(M.body_jntadr)[b]] - 3;
-        double R[9];
-        q2mat(xquat + GMR_QS * b, R);
-        aw[0] = R[i]; aw[1] = R[3 + i]; aw[2] = R[6 + i];
+        const double ei[3] = {i == 0 ? 1.0 : 0.0, i == 1 ? 1.0 : 0.0, i == 2 ? 1.0 : 0.0};
+        qrot(xquat + GMR_QS * b, ei, aw);                               // column i of R(Q_root)
       } else {
         const int p = mv(M.body_parent)[b];
         const double al[3] = {sk[3], sk[4], sk[5]};
@@ -435,7 +441,7 @@ __device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, dou
 #pragma unroll
       for (int i = 0; i < 6; i++) gc[i] += g[i];
     }
-    const double* Sl = sm + lay.S + 6 * l;
+    const double* Sl = sm + lay.S + GMR_SS * l;
     double s[6];
 #pragma unroll
     for (int i = 0; i < 6; i++) s[i] = Sl[i];
@@ -444,7 +450,7 @@ __device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, dou
       double acc = 0;
 #pragma unroll
       for (int j = 0; j < 6; j++) acc += Kc[i >= j ? i * (i + 1) / 2 + j : j * (j + 1) / 2 + i] * s[j];
-      F[6 * l + i] = acc;
+      F[GMR_SS * l + i] = acc;
     }
     double cl = 0;
 #pragma unroll
@@ -466,8 +472,8 @@ __device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, dou
   const short* anc = mv(M.dof_anc);
   for (int e = lane; e < M.nnz; e += 32) {
     const int l = ent_row[e], k = anc[e];
-    const double* Sk = sm + lay.S + 6 * k;
-    const double* Fl = F + 6 * l;
+    const double* Sk = sm + lay.S + GMR_SS * k;
+    const double* Fl = F + GMR_SS * l;
     double h = 0;
 #pragma unroll
     for (int i = 0; i < 6; i++) h += Sk[i] * Fl[i];
@@ -757,9 +763,13 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
         if (isd) *rp = yi;
       }
       __syncwarp();
+      // the op word of the next pass is fetched while this pass waits on its operands (one shared-memory round
+      // trip off the dependent chain of every pass; the table is padded by one pass of slack)
+      int2 op_next = elim_ops[q0 + lane];
 #pragma unroll 1
       for (int q = q0 + lane; q < qend; q += 32) {
-        const int2 op = elim_ops[q];
+        const int2 op = op_next;
+        op_next = elim_ops[q + 32];
         double* tp = (double*)(Wc + (op.x & 0xfff8));
         const unsigned cy = (unsigned)op.y;
         double acc = lds_f64(lrow_s | (cy & 0xf8u)) * lds_f64(lrow_s | ((cy >> 8) & 0xf8u));
@@ -856,7 +866,7 @@ __device__ __forceinline__ void stage_integrate(const MV& mv, const Lay& lay, do
         double n = sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
         double quat[4] = {q[qa], q[qa + 1], q[qa + 2], q[qa + 3]};
         normalize4(quat);
-        if (n < 1e-15) { w[0] = 1; w[1] = w[2] = 0; n = 0; } else { w[0] /= n; w[1] /= n; w[2] /= n; }
+        if (n < 1e-15) { w[0] = 1; w[1] = w[2] = 0; n = 0; } else { const double in = 1.0 / n; w[0] *= in; w[1] *= in; w[2] *= in; }
         const double ang = dt * n;
         if (ang != 0.0) {
           double sh, ch;

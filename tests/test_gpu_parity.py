@@ -319,3 +319,48 @@ def test_fk_tail_matches_reference_golden(golden_dir):
         ident[:, 3] = 1
         lbp, _ = dm.fk_bodies_f32(torch.zeros((n, 3), device=dev), ident, torch.from_numpy(g["dof_pos"]).to(dev), want_rot=False)
         np.testing.assert_allclose(lbp.cpu().numpy(), g["local_body_pos"], atol=2e-6)
+
+
+def test_full_size_bench_workload():
+    """BASELINE.json configs[1] at full size (4096 clips x 300 frames, unitree_g1 <- bvh): a random sample of
+    clips against the oracle, and the size-independent properties of the whole result - two launches agree bit
+    for bit whatever order the work queue served the frame ranges in, limited joints stay inside their range
+    (ConfigurationLimit with gain 0.95 never leaves it), the floating-base quaternion is unit, every frame
+    closed both stages."""
+    from gmr_b200 import synth
+    from oracle import oracle as oc
+    B, T = 4096, 300
+    m, t, dm, br, human, heights = _setup("bvh", "unitree_g1", B, T, seed=0xB201)
+    qpos, diag = br.run(human, diag=True)
+    qpos = qpos.cpu().numpy()
+    iters = diag["iters"].cpu().numpy()
+    pick = np.sort(np.random.default_rng(7).choice(B, size=16, replace=False))
+    ref = oc.run_clips(dm.desc, human[pick], scale=synth.clip_scales(t, heights)[pick], nthreads=8)
+    worst = _check_clip(qpos[pick][..., :m.nq], ref["qpos"], m, "4096x300 sample")
+    assert worst < 1e-7
+    np.testing.assert_array_equal(iters[pick], ref["iters"])
+    assert np.isfinite(qpos).all()
+    assert (iters >= 1).all() and (iters <= 11).all()
+    assert (diag["nfact"].cpu().numpy() > 0).all()          # H was positive definite in every solve
+    for j in range(m.njnt):
+        qa = m.jnt_qposadr[j]
+        if m.jnt_type[j] == 0:
+            np.testing.assert_allclose(np.linalg.norm(qpos[..., qa + 3:qa + 7], axis=-1), 1.0, atol=1e-12)
+        elif m.jnt_limited[j]:
+            assert qpos[..., qa].min() >= m.jnt_range[j, 0] - 1e-12 and qpos[..., qa].max() <= m.jnt_range[j, 1] + 1e-12
+    br.reset()
+    again = br.run(human).cpu().numpy()
+    np.testing.assert_array_equal(again, qpos)
+
+
+@pytest.mark.parametrize("T", [1, 31, 32, 33, 65])
+def test_frame_range_boundaries(T):
+    """Clip lengths around the work queue's 32-frame unit: the warm start crosses units through the batch state."""
+    from gmr_b200 import synth
+    from oracle import oracle as oc
+    B = 12
+    m, t, dm, br, human, heights = _setup("bvh", "unitree_g1", B, T, seed=21)
+    qpos = br.run(human).cpu().numpy()
+    ref = oc.run_clips(dm.desc, human, scale=synth.clip_scales(t, heights), nthreads=8)
+    assert _check_clip(qpos[..., :m.nq], ref["qpos"], m, f"T={T}") < 1e-7
+    np.testing.assert_array_equal(br.state().cpu().numpy()[:, :m.nq], qpos[:, -1, :m.nq])

@@ -88,6 +88,10 @@ def main():
     by_line = collections.Counter(); by_func = collections.Counter(); inst_func = collections.Counter()
     noinst_func = collections.Counter(); thr_func = collections.Counter(); by_outer = collections.Counter()
     static_func = collections.Counter()
+    STALLS = ["stall_wait", "stall_no_inst", "stall_short_sb", "stall_branch_resolving", "stall_not_selected", "stall_selected",
+              "stall_long_sb", "stall_math", "stall_dispatch", "stall_mio"]
+    stall_outer = collections.defaultdict(collections.Counter); inst_outer = collections.Counter()
+    exc_line = collections.Counter(); wav_line = collections.Counter()
     total = 0
     for r in rows[hdr_i + 1:]:
         if len(r) < len(hdr):
@@ -109,7 +113,13 @@ def main():
                 outer = func_of(fl)
         inst_line[cur] += ins; static_line[cur] += 1
         by_line[cur] += smp; by_func[fn] += smp; inst_func[fn] += ins; noinst_func[fn] += noi; thr_func[fn] += thr
-        by_outer[outer] += smp; static_func[outer] += 1
+        by_outer[outer] += smp; static_func[outer] += 1; inst_outer[outer] += ins
+        for st in STALLS:
+            if st in col:
+                stall_outer[outer][st] += int(r[col[st]] or 0)
+        if "L1 Wavefronts Shared Excessive" in col:
+            exc_line[cur] += int(r[col["L1 Wavefronts Shared Excessive"]] or 0)
+            wav_line[cur] += int(r[col["L1 Wavefronts Shared"]] or 0)
         total += smp
     print(f"total samples {total}")
     print("\n-- by outermost stage function (samples %, static SASS instructions)")
@@ -119,6 +129,13 @@ def main():
     for fn, s in by_func.most_common(25):
         ie = inst_func[fn]
         print(f"{100 * s / total:6.2f}%  noinst {100 * noinst_func[fn] / max(s, 1):5.1f}%  inst {ie:14d}  thr/inst {thr_func[fn] / max(ie, 1):5.1f}  {fn}")
+    print("\n-- by outermost stage function: warp-instr executed, share of the kernel's samples per stall reason (%)")
+    print(" " * 40 + "".join(f"{st[6:][:9]:>10s}" for st in STALLS))
+    for fn, s in by_outer.most_common(9):
+        print(f"{fn:22s} {inst_outer[fn]:14d}   " + "".join(f"{100 * stall_outer[fn][st] / total:10.2f}" for st in STALLS))
+    print("\n-- shared-memory wavefronts beyond the ideal (bank conflicts), top lines: excess, total")
+    for (f, ln), x in exc_line.most_common(12):
+        print(f"{x:14d} {wav_line[(f, ln)]:14d}  {f}:{ln}")
     print("\n-- top lines")
     for (f, ln), s in by_line.most_common(args.top):
         print(f"{100 * s / total:6.2f}%  inst {inst_line[(f, ln)]:13d}  static {static_line[(f, ln)]:4d}  {f}:{ln}")
