@@ -44,7 +44,7 @@ struct gmr_batch {
   int* d_counter = nullptr;
   int* d_done = nullptr;        // [B] per-clip range flags of the current launch
   int* d_order = nullptr;
-  int nq_max = 0, s_max = 0, h_max = 0, nbody_max = 0, nv_max = 0, m_max = 0, nnz_max = 0;
+  int nq_max = 0, s_max = 0, h_max = 0, nbody_max = 0, nv_max = 0, m_max = 0, nnz_max = 0, blocks_max = 1;
   Lay lay{};
   int warps_per_cta = 4, grid = 0;
   size_t smem_bytes = 0;          // per-warp blocks only (stage kernels)
@@ -165,67 +165,6 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       fk_jump[(size_t)r * nb + b] = (short)(a2 > 0 ? a2 : -1);
     }
   }
-  // ---- static elimination program of the L'L factorisation (see qp_solve_tree):
-  // dofs of equal height (longest path to a leaf) are pairwise unrelated and all their descendants
-  // have lower height, so they can be eliminated in the same step; a step packs up to 4 such rows
-  // side by side into the 32 lanes (lane = one stored entry of a row).  The updates
-  // W(anc_a, anc_b) -= L(i,a) L(i,b) and r(anc_a) -= L(i,a) y_i of the rows of one step are merged
-  // per target (rows of different branches meet in their common ancestors), one op per target:
-  // target < nnz: W entry, else r[target-nnz]; a contribution names the two lanes of the scaled row whose
-  // product it is; the ops of a step are sorted by n (descending) so that the lanes of a pass agree on n.
-  // Everything the device would have to shift or scale is stored as a byte offset.
-  std::vector<int> elim_lane, elim_opstart;
-  std::vector<int> elim_ops;            // int2 per op
-  int n_elim_step = 0;
-  {
-    std::vector<int> hgt(nv, 0);
-    int hmax = 0;
-    for (int i = nv - 1; i >= 0; i--) {
-      if (dof_parent[i] >= 0) hgt[dof_parent[i]] = std::max(hgt[dof_parent[i]], hgt[i] + 1);
-      hmax = std::max(hmax, hgt[i]);
-    }
-    elim_opstart.push_back(0);
-    for (int hh = 0; hh <= hmax; hh++) {
-      std::vector<int> todo;
-      for (int i = nv - 1; i >= 0; i--) if (hgt[i] == hh) todo.push_back(i);
-      size_t pos = 0;
-      while (pos < todo.size()) {
-        std::vector<int> rows, base;
-        int used = 0;
-        while (pos < todo.size() && rows.size() < 3 && used + dof_depth[todo[pos]] + 1 <= 32) {
-          rows.push_back(todo[pos]); base.push_back(used); used += dof_depth[todo[pos]] + 1; pos++;
-        }
-        // per lane: w0 = byte offset of the entry in W | valid | is_diag<<1 | diag_lane<<16,
-        //           w1 = col | row<<8 | byte offset of r[row] (= W + nnz + row) << 16
-        std::vector<int> lt(64, 0);
-        for (int l = 0; l < 32; l++) lt[2 * l] = l << 16;
-        std::map<int, std::vector<int>> tgt;   // target -> contributions (byte offsets into lrow: 8 la | 8 lb << 8)
-        for (size_t r = 0; r < rows.size(); r++) {
-          const int i = rows[r], dd = dof_depth[i], rp = dof_rowptr[i], b0 = base[r];
-          for (int a2 = 0; a2 <= dd; a2++) {
-            lt[2 * (b0 + a2)] = ((rp + a2) * 8) | 1 | ((a2 == dd ? 1 : 0) << 1) | ((b0 + dd) << 16);
-            lt[2 * (b0 + a2) + 1] = dof_anc[rp + a2] | (i << 8) | (((nnz + i) * 8) << 16);
-          }
-          for (int a2 = 0; a2 < dd; a2++) {
-            for (int b2 = 0; b2 <= a2; b2++) tgt[dof_ancrow[rp + a2] + b2].push_back(((b0 + a2) * 8) | (((b0 + b2) * 8) << 8));
-            tgt[nnz + dof_anc[rp + a2]].push_back(((b0 + a2) * 8) | (((b0 + dd) * 8) << 8));
-          }
-        }
-        elim_lane.insert(elim_lane.end(), lt.begin(), lt.end());
-        // op = {8 target | n | contribution 2 << 16,  contribution 0 | contribution 1 << 16}
-        for (int want = 3; want >= 1; want--)
-          for (auto& kv : tgt) {
-            if ((int)kv.second.size() != want) continue;
-            const std::vector<int>& c2 = kv.second;
-            elim_ops.push_back((kv.first * 8) | want | (want > 2 ? c2[2] << 16 : 0));
-            elim_ops.push_back(c2[0] | (want > 1 ? c2[1] << 16 : 0));
-          }
-        elim_opstart.push_back((int)elim_ops.size() / 2);
-        n_elim_step++;
-      }
-    }
-  }
-  elim_ops.resize(elim_ops.size() + 2 * 64, 0);      // slack: the kernel fetches the op word one pass ahead
   // levels (level 1 first)
   std::vector<int> level_start(nlevel + 1, 0), level_body;
   for (int lv = 1; lv <= nlevel; lv++) {
@@ -289,6 +228,100 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
         if (((mk >> t) & 1u) && (tparent[t] < 0 || !((mk >> tparent[t]) & 1u))) topmask[k * nv + l] |= 1u << t;
     }
   }
+  // ---- static schedule of the articulated-body solver (qp_solve_aba), per stage
+  std::vector<int> aba_uplev, aba_dnlev, aba_p1, aba_p2, aba_dn;      // level tables: stage 0's levels, then stage 1's
+  int aba_up0[2] = {0, 0}, aba_dn0[2] = {0, 0};
+  std::vector<int> aba_merge(2 * MT * 2, 0), task_dof(2 * MT, -1);
+  int aba_nup[2] = {0, 0}, aba_ndn[2] = {0, 0}, aba_nmerge[2] = {0, 0}, aba_zero[2] = {0, 0}, aba_blocks = 1;
+  unsigned aba_kktmask[2] = {0u, 0u};
+  for (int k = 0; k < 2; k++) {
+    if (!d->use_table[k]) continue;
+    const int m_k = d->n_task[k];
+    std::vector<int> own(nv, -1);                       // first task hanging on the dof
+    for (int t = 0; t < m_k; t++) {
+      const int a = body_lastdof[task_body[k * MT + t]];
+      task_dof[k * MT + t] = a;
+      if (a < 0) continue;                              // a task on a body no dof moves
+      if (own[a] < 0) { own[a] = t; aba_kktmask[k] |= 1u << t; }
+      else { aba_merge[2 * (k * MT + aba_nmerge[k])] = own[a]; aba_merge[2 * (k * MT + aba_nmerge[k]) + 1] = t; aba_nmerge[k]++; }
+    }
+    // dofs with a task in their subtree, their heights among themselves, depths
+    std::vector<char> in(nv, 0);
+    for (int i = 0; i < nv; i++) in[i] = taskmask[k * nv + i] != 0;
+    std::vector<int> hgt(nv, 0), nchild(nv, 0);
+    int hmax = -1;
+    for (int i = nv - 1; i >= 0; i--) {
+      if (!in[i]) continue;
+      hmax = std::max(hmax, hgt[i]);
+      if (dof_parent[i] >= 0) { hgt[dof_parent[i]] = std::max(hgt[dof_parent[i]], hgt[i] + 1); nchild[dof_parent[i]]++; }
+    }
+    // blocks: tasks [0, m_k), then one accumulator per chain (a dof reuses the accumulator of its first finished child)
+    std::vector<int> xblk(nv, -1), acc(nv, -1);
+    int nacc = 0;
+    for (int i = 0; i < nv; i++) if (in[i] && nchild[i] == 0) xblk[i] = own[i];        // a leaf always carries a task
+    aba_up0[k] = (int)aba_uplev.size() / 4;
+    aba_uplev.resize(aba_uplev.size() + 4 * (hmax + 1), 0);
+    for (int hh = 0; hh <= hmax; hh++) {
+      int* L = &aba_uplev[4 * (aba_up0[k] + hh)];
+      std::vector<int> todo;
+      for (int i = nv - 1; i >= 0; i--) if (in[i] && hgt[i] == hh) todo.push_back(i);
+      L[0] = (int)aba_p1.size() / 8;
+      for (size_t pos = 0; pos < todo.size(); pos += 4)
+        for (int g = 0; g < 4; g++) {
+          const bool have = pos + g < todo.size();
+          aba_p1.push_back(have ? todo[pos + g] : -1);
+          aba_p1.push_back(have ? xblk[todo[pos + g]] : 0);
+        }
+      L[1] = (int)aba_p1.size() / 8;
+      L[2] = (int)aba_p2.size() / 4;
+      for (int c : todo) {
+        const int pr = dof_parent[c];
+        if (pr < 0) continue;
+        int base;
+        if (acc[pr] < 0) {                               // first child to finish: X_parent = own tasks + X^a_c
+          // the child's accumulator is reused in place; a leaf reads its task block, so it opens a new one
+          acc[pr] = (xblk[c] >= m_k) ? xblk[c] : m_k + nacc++;
+          base = own[pr];                                // -1 -> the block of zeros, patched below
+        } else base = acc[pr];
+        xblk[pr] = acc[pr];
+        aba_p2.push_back(c); aba_p2.push_back(xblk[c]); aba_p2.push_back(acc[pr]); aba_p2.push_back(base);
+      }
+      L[3] = (int)aba_p2.size() / 4;
+    }
+    aba_nup[k] = hmax + 1;
+    aba_zero[k] = m_k + nacc;
+    aba_blocks = std::max(aba_blocks, m_k + nacc + 1);
+    // downward levels by depth among the scheduled dofs
+    std::vector<int> dep(nv, 0);
+    int dmax = -1;
+    for (int i = 0; i < nv; i++) {
+      if (!in[i]) continue;
+      dep[i] = dof_parent[i] < 0 ? 0 : dep[dof_parent[i]] + 1;
+      dmax = std::max(dmax, dep[i]);
+    }
+    aba_dn0[k] = (int)aba_dnlev.size() / 2;
+    aba_dnlev.resize(aba_dnlev.size() + 2 * (dmax + 1), 0);
+    for (int dd = 0; dd <= dmax; dd++) {
+      int* L = &aba_dnlev[2 * (aba_dn0[k] + dd)];
+      std::vector<int> todo;
+      for (int i = 0; i < nv; i++) if (in[i] && dep[i] == dd) todo.push_back(i);
+      L[0] = (int)aba_dn.size() / 8;
+      for (size_t pos = 0; pos < todo.size(); pos += 4)
+        for (int g = 0; g < 4; g++) {
+          const bool have = pos + g < todo.size();
+          aba_dn.push_back(have ? todo[pos + g] : -1);
+          aba_dn.push_back(have ? dof_parent[todo[pos + g]] : -1);
+        }
+      L[1] = (int)aba_dn.size() / 8;
+    }
+    aba_ndn[k] = dmax + 1;
+  }
+  // the stage of a pass is implied by its level table; patch "no own task" (-1) to the stage's block of zeros
+  for (int k = 0; k < 2; k++)
+    for (int lv = 0; lv < aba_nup[k]; lv++) {
+      const int* L = &aba_uplev[4 * (aba_up0[k] + lv)];
+      for (int ps = L[2]; ps < L[3]; ps++) if (aba_p2[4 * ps + 3] < 0) aba_p2[4 * ps + 3] = aba_zero[k];
+    }
   for (int i = 0; i < d->n_scaled; i++)
     if (d->scaled_human_index[i] < 0 || d->scaled_human_index[i] >= d->n_human) return fail(-5, "scaled_human_index out of range");
 
@@ -305,21 +338,27 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   std::vector<short> fk_body;
   for (int b = 0; b < nb; b++) if (fk_need[b]) fk_body.push_back((short)b);
   Blob bl;
+  // tables of the fused kernel first: a CTA stages exactly this leading part of the blob in shared memory
   size_t o_parent = bl.push(vec(d->body_parentid, nb)), o_bpos = bl.push(vec(d->body_pos, 3 * nb)),
          o_bquat = bl.push(body_quat_padded), o_jadr = bl.push(vec(d->body_jntadr, nb)),
-         o_jnum = bl.push(vec(d->body_jntnum, nb)), o_lstart = bl.push(level_start), o_lbody = bl.push(level_body),
+         o_jnum = bl.push(vec(d->body_jntnum, nb)),
          o_jtype = bl.push(vec(d->jnt_type, nj)), o_jq = bl.push(vec(d->jnt_qposadr, nj)),
          o_jd = bl.push(vec(d->jnt_dofadr, nj)), o_jaxis = bl.push(vec(d->jnt_axis, 3 * nj)),
          o_q0 = bl.push(vec(d->qpos0, d->nq)), o_dk = bl.push(dof_kind), o_dq = bl.push(dof_qadr),
-         o_dp = bl.push(dof_parent), o_db = bl.push(dof_body), o_dl = bl.push(dof_limited), o_dlo = bl.push(dof_lo), o_dhi = bl.push(dof_hi),
+         o_db = bl.push(dof_body), o_dl = bl.push(dof_limited), o_dlo = bl.push(dof_lo), o_dhi = bl.push(dof_hi),
          o_tm = bl.push(taskmask), o_si = bl.push(vec(d->scaled_human_index, d->n_scaled)),
          o_sc = bl.push(vec(d->scale, d->n_scaled)), o_po = bl.push(vec(d->pos_off, 3 * d->n_scaled)),
          o_ro = bl.push(vec(d->rot_off, 4 * d->n_scaled)), o_ft = bl.push(vec(d->is_foot, d->n_scaled)),
          o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot),
+         o_fj = bl.push(fk_jump), o_fb = bl.push(fk_body), o_aul = bl.push(aba_uplev), o_adl = bl.push(aba_dnlev),
+         o_ap1 = bl.push(aba_p1), o_ap2 = bl.push(aba_p2), o_adn = bl.push(aba_dn), o_amg = bl.push(aba_merge),
+         o_atd = bl.push(task_dof);
+  const size_t staged_bytes = (bl.bytes.size() + 15) & ~size_t(15);
+  // tables only the stage kernels read (gmr_build_qp: the assembly of H), from global memory
+  size_t o_lstart = bl.push(level_start), o_lbody = bl.push(level_body), o_dp = bl.push(dof_parent),
          o_dd = bl.push(dof_depth), o_rp = bl.push(dof_rowptr), o_an = bl.push(dof_anc), o_ar = bl.push(dof_ancrow),
          o_er = bl.push(ent_row), o_tpm = bl.push(topmask), o_chm = bl.push(childmask), o_tls = bl.push(tasklev_start),
-         o_tlt = bl.push(tasklev_task), o_fj = bl.push(fk_jump), o_fb = bl.push(fk_body), o_el = bl.push(elim_lane), o_eo = bl.push(elim_ops), o_es = bl.push(elim_opstart);
-  const size_t staged_bytes = (bl.bytes.size() + 15) & ~size_t(15);
+         o_tlt = bl.push(tasklev_task);
 
   // FK tail tables (KinematicsModel semantics: bodies under the first top-level body, float32, xyzw)
   const int nbt = nb - 1;
@@ -388,8 +427,14 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.dof_anc = (const short*)(B0 + o_an); h.dof_ancrow = (const short*)(B0 + o_ar);
   h.ent_row = (const short*)(B0 + o_er); h.dof_topmask = (const unsigned*)(B0 + o_tpm);
   h.task_childmask = (const unsigned*)(B0 + o_chm); h.tasklev_start = (const int*)(B0 + o_tls);
-  h.elim_lane = (const int2*)(B0 + o_el); h.elim_ops = (const int2*)(B0 + o_eo);
-  h.elim_opstart = (const int*)(B0 + o_es); h.n_elim_step = n_elim_step;
+  for (int k = 0; k < 2; k++) {
+    h.aba_nup[k] = aba_nup[k]; h.aba_ndn[k] = aba_ndn[k]; h.aba_nmerge[k] = aba_nmerge[k]; h.aba_zero[k] = aba_zero[k];
+    h.aba_kktmask[k] = aba_kktmask[k]; h.aba_up0[k] = aba_up0[k]; h.aba_dn0[k] = aba_dn0[k];
+  }
+  h.aba_blocks = aba_blocks;
+  h.aba_uplev = (const int4*)(B0 + o_aul); h.aba_dnlev = (const int2*)(B0 + o_adl); h.aba_p1 = (const int2*)(B0 + o_ap1);
+  h.aba_p2 = (const int4*)(B0 + o_ap2); h.aba_dn = (const int2*)(B0 + o_adn); h.aba_merge = (const int2*)(B0 + o_amg);
+  h.task_dof = (const int*)(B0 + o_atd);
   h.fk_rounds = fk_rounds; h.fk_jump = (const short*)(B0 + o_fj);
   h.n_fk = (int)fk_body.size(); h.fk_body = (const short*)(B0 + o_fb);
   h.tasklev_task = (const int*)(B0 + o_tlt); h.n_tasklev[0] = n_tasklev[0]; h.n_tasklev[1] = n_tasklev[1];
@@ -421,30 +466,31 @@ static const void* clip_kernel_ptr(int dtype, bool staged) {
   return staged ? (const void*)clip_kernel<double, true> : (const void*)clip_kernel<double, false>;
 }
 
-static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h) {
-  // Two scratch regions behind the per-frame state (q, targets, x), each reused along the tick:
-  //   region 1: body poses + spatial axes (FK .. assembly; F_l aliases the poses, dead after the stiffness pass),
-  //             then the factor L, the right-hand side and one row of L during the solve;
-  //   region 2: local FK transforms / the staged human frame -> task errors e, stiffness K, g (errors .. assembly
-  //             step 2) -> H, written by assembly step 3 once K/g have been folded into F, read-only during the solve.
+static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h, int blocks) {
+  // Scratch behind the per-frame state (q, targets, x), reused along the tick:
+  //   poses + spatial axes: FK .. stiffness; during the solve the link velocities v overlay the poses
+  //                         (gmr_build_qp: F_l of the assembly does);
+  //   Ud: per dof [U, alpha, beta] of the solver;
+  //   e:  task errors (+ sin/cos of the angle), then the task forces of the KKT check;
+  //   K:  `blocks` blocks of GMR_KS doubles - task stiffness [K_t | g_t], the solver's accumulators, a block of
+  //       zeros; before the stiffness pass the same span holds the local FK transforms / the staged human frame
+  //       (gmr_build_qp: H overlays e/K once the assembly has folded them into F).
   Lay L{};
   int o = 0;
   auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };   // keep 16-byte alignment
   L.q = take(nq); L.scaled = take(7 * s); L.x = take(nv);
-  const int region1 = o;
-  L.xpos = take(3 * nbody); L.xquat = take(GMR_QS * nbody); L.S = take(GMR_SS * nv);
-  if (GMR_SS * nv <= L.S - L.xpos) L.F = L.xpos;              // F_l aliases the body poses when it fits
-  else L.F = take(GMR_SS * nv);
-  L.L = region1;                                 // the factor overlays the kinematics scratch
-  L.rv = region1 + nnz;                          // right-hand side directly behind the factor (one index space)
-  L.lrow = (region1 + nnz + nv + 31) & ~31;      // 256-byte aligned: the program ORs lane offsets into its address
-  o = std::max(o, L.lrow + 32);
+  L.xpos = take(3 * nbody); L.xquat = take(GMR_QS * nbody);
+  o = std::max(o, L.xpos + ((std::max(GMR_SS, 6) * nv + 1) & ~1));   // F_l (stride GMR_SS) and v (stride 6) alias the body poses
+  L.F = L.xpos; L.v = L.xpos;
+  L.S = take(GMR_SS * nv);
+  L.Ud = take(8 * nv);
   const int region2 = o;
-  L.e = take(6 * m); L.K = take(21 * m); L.g = take(6 * m);
-  L.tl = L.K; L.ql = L.tl + ((3 * nbody + 1) & ~1);          // FK local transforms alias K/g
+  L.e = take(GMR_ES * m);
+  L.K = take(GMR_KS * std::max(blocks, m));
+  L.tl = L.K; L.ql = L.tl + ((3 * nbody + 1) & ~1);          // FK local transforms alias the blocks
   o = std::max(o, L.ql + ((GMR_QS * nbody + 1) & ~1));
-  o = std::max(o, (L.K + 7 * h + 1) & ~1);                   // one frame of the human stream is staged in K/g
-  L.H = region2;                                             // H aliases e/K/g
+  o = std::max(o, (L.K + 7 * h + 1) & ~1);                   // one frame of the human stream is staged there too
+  L.H = region2;
   o = std::max(o, (L.H + nnz + 1) & ~1);
   L.total = (o + 31) & ~31;
   L.maxt = GMR_MAX_TASKS;
@@ -468,12 +514,12 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
     b->nq_max = std::max(b->nq_max, m->host.nq); b->s_max = std::max(b->s_max, m->host.n_scaled);
     b->h_max = std::max(b->h_max, m->host.n_human); b->nbody_max = std::max(b->nbody_max, m->host.nbody);
     b->nv_max = std::max(b->nv_max, m->host.nv); b->m_max = std::max(b->m_max, m->max_task);
-    b->nnz_max = std::max(b->nnz_max, m->host.nnz);
+    b->nnz_max = std::max(b->nnz_max, m->host.nnz); b->blocks_max = std::max(b->blocks_max, m->host.aba_blocks);
   }
   if (model_of_instance)
     for (int i = 0; i < B; i++)
       if (model_of_instance[i] < 0 || model_of_instance[i] >= n_models) { delete b; return fail(-1, "model_of_instance out of range"); }
-  b->lay = make_layout(b->nq_max, b->s_max, b->nv_max, b->nbody_max, std::max(b->m_max, 1), b->nnz_max, b->h_max);
+  b->lay = make_layout(b->nq_max, b->s_max, b->nv_max, b->nbody_max, std::max(b->m_max, 1), b->nnz_max, b->h_max, b->blocks_max);
   int prev = 0;
   cudaGetDevice(&prev);
   cudaError_t e = cudaSetDevice(b->device);

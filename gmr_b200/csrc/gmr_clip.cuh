@@ -47,7 +47,7 @@ struct Slot {
   int inst;                      // instance being retargeted, -1 = none
   int t, T;                      // current frame, clip length
   int stage, it;                 // stage being solved, loop counter of motion_retarget.py:152/171
-  int nfact;                     // factorisations in this frame (negative once H was not SPD)
+  int nfact;                     // sweeps of the box QP in this frame (1 per solve_ik + 1 per change of the active set)
   bool new_frame, fresh, need_fk;
   double curr;                   // curr_error of the reference loop
   unsigned long long act_lo, act_hi;   // active set of the previous solve of this frame/stage
@@ -70,12 +70,10 @@ __device__ __forceinline__ int next_stage(const DevModel& M, int stage) {
 template <typename TIn, bool SM>
 __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs a) {
   extern __shared__ __align__(256) double smem[];
-  __shared__ unsigned short pair_tab[PAIR_TAB_SIZE];
   __shared__ DevModel smodel;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const Lay lay = a.lay;
   double* sm = smem + (size_t)warp * lay.total;
-  fill_pair_tab(pair_tab);
   ModelView<SM> mv;
   mv.m = a.models;
   mv.sblob = nullptr;
@@ -180,13 +178,11 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
       break;
     }
     if (!solve) continue;
-    // ---- Kernel 2+3: task stiffness, QP assembly (mink build_ik), box QP; Kernel 4: integrate
+    // ---- Kernel 2+3: task stiffness, box QP of mink build_ik (never assembled: articulated-body sweeps over
+    //      the task stiffnesses); Kernel 4: integrate
     const double mu = stage_stiffness(mv, lay, sm, s.stage, lane);
-    double qc[2], qlo[2], qhi[2];
-    stage_assemble(mv, lay, sm, s.stage, mu, lane, qc, qlo, qhi);
-    const int nf = qp_solve_tree(mv, sm + lay.H, qc, qlo, qhi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
-                                 sm + lay.x, pair_tab, lane, s.act_lo, s.act_hi);
-    s.nfact = (nf < 0 || s.nfact < 0) ? -abs(s.nfact) - abs(nf) : s.nfact + nf;
+    const int nf = qp_solve_aba(mv, lay, sm, s.stage, mu, lane, s.act_lo, s.act_hi);
+    s.nfact += nf;
     stage_integrate(mv, lay, sm, lane);
     s.need_fk = true;
   }
@@ -256,7 +252,7 @@ __global__ void build_qp_kernel(const StageArgs a) {
   stage_errors(mv, lay, sm, a.stage, lane);
   const double mu = stage_stiffness(mv, lay, sm, a.stage, lane);
   const int n = M.nv, m = M.n_task[a.stage];
-  if (a.e_out) for (int i = lane; i < 6 * m; i += 32) a.e_out[(size_t)inst * a.m_max * 6 + i] = sm[lay.e + i];   // H overwrites e
+  if (a.e_out) for (int i = lane; i < 6 * m; i += 32) a.e_out[(size_t)inst * a.m_max * 6 + i] = sm[lay.e + GMR_ES * (i / 6) + i % 6];   // H overwrites e
   __syncwarp();
   double qc[2], qlo[2], qhi[2];
   stage_assemble(mv, lay, sm, a.stage, mu, lane, qc, qlo, qhi);
@@ -275,14 +271,11 @@ __global__ void build_qp_kernel(const StageArgs a) {
   }
 }
 
-// one mink.solve_ik call on the batch state: dq = argmin of the stage's QP (tree solver)
+// one mink.solve_ik call on the batch state: dq = argmin of the stage's QP (articulated-body solver)
 __global__ void solve_ik_kernel(const StageArgs a) {
   extern __shared__ __align__(256) double smem[];
-  __shared__ unsigned short pair_tab[PAIR_TAB_SIZE];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int inst = blockIdx.x * (blockDim.x >> 5) + warp;
-  fill_pair_tab(pair_tab);
-  __syncthreads();
   if (inst >= a.B) return;
   const Lay& lay = a.lay;
   double* sm = smem + (size_t)warp * lay.total;
@@ -294,11 +287,8 @@ __global__ void solve_ik_kernel(const StageArgs a) {
   stage_fk<false>(mv, lay, sm, lane);
   stage_errors(mv, lay, sm, a.stage, lane);
   const double mu = stage_stiffness(mv, lay, sm, a.stage, lane);
-  double qc[2], qlo[2], qhi[2];
-  stage_assemble(mv, lay, sm, a.stage, mu, lane, qc, qlo, qhi);
   unsigned long long act_lo = 0, act_hi = 0;
-  const int nf = qp_solve_tree(mv, sm + lay.H, qc, qlo, qhi, sm + lay.L, sm + lay.lrow, sm + lay.rv,
-                               sm + lay.x, pair_tab, lane, act_lo, act_hi);
+  const int nf = qp_solve_aba(mv, lay, sm, a.stage, mu, lane, act_lo, act_hi);
   for (int i = lane; i < M.nv; i += 32) a.dq_out[(size_t)inst * a.nv_max + i] = sm[lay.x + i];
   if (lane == 0 && a.nfact_out) a.nfact_out[inst] = nf;
 }

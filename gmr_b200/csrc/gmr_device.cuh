@@ -10,6 +10,9 @@
 #include <cuda_runtime.h>
 
 #define GMR_FULL 0xffffffffu
+#ifndef GMR_MAX_TASKS
+#define GMR_MAX_TASKS 32
+#endif
 
 namespace gmr {
 
@@ -70,11 +73,18 @@ struct DevModel {
   const short* dof_anc;          // [nnz]
   const short* dof_ancrow;       // [nnz] rowptr of that ancestor
   const short* ent_row;          // [nnz] row (dof) of each stored entry
-  // static elimination program of the L'L factorisation (built by gmr_model_create)
-  int n_elim_step;
-  const int2* elim_lane;         // [n_elim_step*32] per lane: x = entry | diag_lane<<16 | is_diag<<21 | valid<<22, y = col | row<<8
-  const int2* elim_ops;          // merged updates: x = target(16) | n<<16, y = n x (lane_a(5) | lane_b(5)<<5), 10-bit fields
-  const int* elim_opstart;       // [n_elim_step+1]
+  // static schedule of the articulated-body box-QP solver (qp_solve_aba), per stage; blocks are indices into the
+  // per-warp array of GMR_KS-double blocks: [0, n_task) the task blocks, then the accumulators, then a block of zeros
+  int aba_nup[2], aba_ndn[2], aba_up0[2], aba_dn0[2], aba_nmerge[2], aba_zero[2];
+  unsigned aba_kktmask[2];       // tasks whose block is not merged into another task's (same dof)
+  int aba_blocks;                // blocks a warp needs (max over stages)
+  const int4* aba_uplev;         // [aba_up0[stage] + level] per level (by height): phase-1 passes [x,y), phase-2 passes [z,w)
+  const int2* aba_p1;            // per (pass, 8-lane group): dof (-1: idle), block of X_dof
+  const int4* aba_p2;            // per pass: dof c, block of X_c, destination block (X_parent), block it adds to
+  const int2* aba_dnlev;         // [aba_dn0[stage] + level] per level (by depth): passes [x,y)
+  const int2* aba_dn;            // per (pass, 8-lane group): dof (-1: idle), parent dof (-1: none)
+  const int2* aba_merge;         // [2*GMR_MAX_TASKS] (dst task, src task) hanging on the same dof
+  const int* task_dof;           // [2*GMR_MAX_TASKS] dof the task's body hangs on (-1: none, the task moves nothing)
   // target preparation
   const int* scaled_index;   // [s] body index inside a human frame
   const double* scale;       // [s]
@@ -110,15 +120,20 @@ struct ModelView {
 // Spatial axes S_k and the assembly's F_l are 6-vectors stored with a stride of 7 doubles: an even stride
 // puts 16 consecutive dofs on 8 bank pairs (2-way conflicts for lane = dof and for the H fill), 7 on 16.
 #define GMR_SS 7
+// Task error e_t is stored with a stride of 8: 6 components, then sin and cos of its rotation angle.
+#define GMR_ES 8
+// Task stiffness block: K_t (21, packed lower 6x6) followed by g_t (6).
+#define GMR_KS 27
 
 // Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
 struct Lay {
   int q, scaled, x;                       // per-frame state: configuration, targets, the last solve's dq
-  int H;                                  // nnz packed tree rows; aliases e/K/g (written once they are folded into F)
-  int xpos, xquat, S, e, K, g;            // kinematics / assembly scratch ...
-  int tl, ql;                             // FK local transforms (alias K/g: dead before the stiffness pass)
+  int H;                                  // gmr_build_qp only: nnz packed tree rows; aliases e/K (written once they are folded into F)
+  int xpos, xquat, S;                     // kinematics: body poses, spatial axes (stride GMR_SS)
+  int e, K;                               // task errors (stride GMR_ES), task blocks [K_t | g_t] (stride GMR_KS) + solver accumulators
+  int tl, ql;                             // FK local transforms (alias K: dead before the stiffness pass)
   int F;                                  // F_l = Kc_l S_l of the assembly (aliases xpos/xquat: dead after the stiffness pass)
-  int L, rv, lrow;                        // ... overlaid by the factor (nnz), the rhs (nv, = L + nnz) and one row (32)
+  int Ud, v;                              // qp_solve_aba: per dof [U (6), alpha, beta]; link velocities (6 per dof, alias xpos/xquat)
   int total;                              // doubles per warp
   int maxt;                               // stride of the stage-major task tables
 };

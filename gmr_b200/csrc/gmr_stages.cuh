@@ -5,7 +5,7 @@
 //   stage_errors    Kernel 2  FrameTask.compute_error         motion_retarget.py:188-200
 //   stage_stiffness Kernel 2  FrameTask.compute_jacobian, folded into a 6x6 stiffness
 //   stage_assemble  Kernel 3  mink build_ik: H, c, box
-//   qp_solve_tree   Kernel 3  exact box QP on the kinematic tree (stands in for daqp)
+//   qp_solve_aba    Kernel 3  exact box QP on the kinematic tree, articulated-body sweeps (stands in for daqp)
 //   stage_integrate Kernel 4  mj_integratePos
 // Kernel 4's convergence control lives in gmr_clip.cuh.
 //
@@ -248,7 +248,7 @@ __device__ __forceinline__ void se3_log_dev(const double* q, const double* p, do
 }
 
 // ------------------------------------------------------------------ Kernel 2: task errors
-// lane t < m: e_t = log(T_b^-1 T_t) -> sm[e + 6t]; returns ||concat e|| (unweighted, :188-200),
+// lane t < m: e_t = log(T_b^-1 T_t) -> sm[e + GMR_ES t]; returns ||concat e|| (unweighted, :188-200),
 // bitwise identical on all lanes.
 template <class MV>
 __device__ __forceinline__ double stage_errors(const MV& mv, const Lay& lay, double* sm, int stage, int lane) {
@@ -265,11 +265,10 @@ __device__ __forceinline__ double stage_errors(const MV& mv, const Lay& lay, dou
     qrot(qi, d, pbt);
     double sn, cs;
     se3_log_dev(qbt, pbt, e, sn, cs);
-    sm[lay.g + 6 * lane] = sn;            // parked in g (rewritten by stage_stiffness after it has read them)
-    sm[lay.g + 6 * lane + 1] = cs;
-    double* eo = sm + lay.e + 6 * lane;
+    double* eo = sm + lay.e + GMR_ES * lane;
 #pragma unroll
     for (int k = 0; k < 6; k++) { eo[k] = e[k]; ss += e[k] * e[k]; }
+    eo[6] = sn; eo[7] = cs;               // for stage_stiffness
   }
   ss = warp_sum(ss);
   __syncwarp();
@@ -283,7 +282,7 @@ __device__ __forceinline__ double stage_errors(const MV& mv, const Lay& lay, dou
 // T(r) = [[I, -[r]x],[0, I]], so W J_t[:,k] = N_t S_k with the 6x6
 //       N_t = -[[wp P, wp Pr],[0, wr P]],  P = Ji R^T,  Pr = -P [r]x + B R^T,
 // where Jl^-1(e) = [[Ji, B],[0, Ji]].  Lane t stores K_t = N_t^T N_t (21 packed) and
-// g_t = N_t^T W e_t (6); the assembly then needs only S_k^T (sum K_t) S_l - no 6 x nv Jacobian.
+// g_t = N_t^T W e_t (6) as one block of GMR_KS = 27 doubles; the assembly then needs only S_k^T (sum K_t) S_l - no 6 x nv Jacobian.
 // Returns sum_t mu_t = sum_t ||W e_t||^2 (all lanes).
 template <class MV>
 __device__ __forceinline__ double stage_stiffness(const MV& mv, const Lay& lay, double* sm, int stage, int lane) {
@@ -294,7 +293,7 @@ __device__ __forceinline__ double stage_stiffness(const MV& mv, const Lay& lay, 
     const int body = mv(M.task_body)[stage * lay.maxt + lane];
     const double wp = mv(M.task_wpos)[stage * lay.maxt + lane], wr = mv(M.task_wrot)[stage * lay.maxt + lane];
     const double a = wp * wp, b = wr * wr;
-    const double* e = sm + lay.e + 6 * lane;
+    const double* e = sm + lay.e + GMR_ES * lane;
     const double ev[3] = {e[0], e[1], e[2]}, w[3] = {e[3], e[4], e[5]};
     mu = a * (ev[0] * ev[0] + ev[1] * ev[1] + ev[2] * ev[2]) + b * (w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
     const double th2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
@@ -307,7 +306,7 @@ __device__ __forceinline__ double stage_stiffness(const MV& mv, const Lay& lay, 
       for (int i = 0; i < 9; i++) { P[i] = Rt[i]; Pr[i] = 0; }
     } else {
       const double th = sqrt(th2);
-      const double s = sm[lay.g + 6 * lane], c = sm[lay.g + 6 * lane + 1];      // sin th, cos th from stage_errors
+      const double s = e[6], c = e[7];                                         // sin th, cos th from stage_errors
       const double A = (1.0 / th2) * (1.0 - (th * s / (2.0 * (1.0 - c))));
       // products of skew matrices in closed form: [a]x[b]x = b a' - (a.b) I, so with cw = w.v, u = v x w:
       //   W^2 = w w' - th2 I,  WV = v w' - cw I,  VW = w v' - cw I,  WVW = -cw W,
@@ -353,7 +352,7 @@ __device__ __forceinline__ double stage_stiffness(const MV& mv, const Lay& lay, 
     mtm3(P, P, PtP);
     mtm3(P, Pr, PtPr);
     mtm3(Pr, Pr, PrtPr);
-    double* K = sm + lay.K + 21 * lane;
+    double* K = sm + lay.K + GMR_KS * lane;      // block of the task: 21 packed K, then g
     // packed lower 6x6: (i,j) -> i(i+1)/2 + j
     K[0] = a * PtP[0];
     K[1] = a * PtP[3]; K[2] = a * PtP[4];
@@ -367,7 +366,7 @@ __device__ __forceinline__ double stage_stiffness(const MV& mv, const Lay& lay, 
       for (int j = 0; j <= i; j++) K[base + 3 + j] = a * PrtPr[3 * i + j] + b * PtP[3 * i + j];
     }
     // g = -[a P' ev ; a Pr' ev + b P' w]
-    double* g = sm + lay.g + 6 * lane;
+    double* g = K + 21;
 #pragma unroll
     for (int i = 0; i < 3; i++) {
       g[i] = -a * (P[i] * ev[0] + P[3 + i] * ev[1] + P[6 + i] * ev[2]);
@@ -395,8 +394,7 @@ __device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, dou
   const DevModel& M = mv.M();
   const int n = M.nv;
   double* H = sm + lay.H;
-  double* Kt = sm + lay.K;
-  double* gt = sm + lay.g;
+  double* Kt = sm + lay.K;                  // blocks [K_t (21) | g_t (6)]
   double* F = sm + lay.F;
   const double diag = M.damping + M.lm_damping * mu_sum;
   const double* q = sm + lay.q;
@@ -409,11 +407,9 @@ __device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, dou
     const int beg = tl_start[lv], cnt = (tl_start[lv + 1] - beg) * 27;
     for (int it = lane; it < cnt; it += 32) {
       const int t = tl_task[beg + it / 27], e = it % 27;
-      double* dst = e < 21 ? Kt + 21 * t + e : gt + 6 * t + (e - 21);
-      const int stride = e < 21 ? 21 : 6;
-      const double* src0 = e < 21 ? Kt + e : gt + (e - 21);
+      double* dst = Kt + GMR_KS * t + e;
       double acc = *dst;
-      for (unsigned cm = child_mask[t]; cm; cm &= cm - 1) acc += src0[stride * (__ffs(cm) - 1)];
+      for (unsigned cm = child_mask[t]; cm; cm &= cm - 1) acc += Kt[GMR_KS * (__ffs(cm) - 1) + e];
       *dst = acc;
     }
     __syncwarp();
@@ -434,8 +430,8 @@ __device__ __forceinline__ void stage_assemble(const MV& mv, const Lay& lay, dou
     while (mask) {
       const int t = __ffs(mask) - 1;
       mask &= mask - 1;
-      const double* K = Kt + 21 * t;
-      const double* g = gt + 6 * t;
+      const double* K = Kt + GMR_KS * t;
+      const double* g = K + 21;
 #pragma unroll
       for (int i = 0; i < 21; i++) Kc[i] += K[i];
 #pragma unroll
@@ -642,194 +638,190 @@ __device__ __noinline__ int qp_solve(int n, const double* __restrict__ H, const 
 }
 
 // ------------------------------------------------------------------ Kernel 3: exact box QP on the kinematic tree
-// Same problem and same pivoting rules as qp_solve above, but H is held in the tree layout of
-// DevModel (row i = its depth[i]+1 chain entries) and factorised as H = L'L from the leaves to the
-// root (Featherstone's LTL): eliminating dof i touches only pairs of its ancestors, so L has exactly
-// the sparsity of H - no fill-in, ~1/6 of the dense flops for a humanoid, and no zero is ever stored.
-//   factor : for i = n-1..0:  L(i,i) = sqrt(W(i,i)); L(i,a) = W(i,a)/L(i,i); W(a,b) -= L(i,a) L(i,b)
-//            over ancestor pairs b <= a, one pair per lane (pair_tab enumerates (a,b));
-//   L'y = r: for i = n-1..0:  y_i = r_i/L(i,i); r_a -= L(i,a) y_i  (lanes = ancestors);
-//   L x = y: wavefront over depth: lane = dof, at step a the dofs of depth a finish and everyone
-//            deeper subtracts L(i,a) x_a - max_depth steps instead of n.
-// Rows/columns of dofs held at a bound are replaced by identity (their L row is e_i).
-// W (the factor, diagonal = 1/L_ii) and lrow (one row of L) overlay the kinematics scratch.
-#define PAIR_TAB_SIZE 496      // 31*32/2: chains of up to 32 dofs
-
-__device__ __forceinline__ void fill_pair_tab(unsigned short* pair_tab) {
-  for (int p = threadIdx.x; p < PAIR_TAB_SIZE; p += blockDim.x) {
-    int a = (int)((sqrtf(8.0f * p + 1.0f) - 1.0f) * 0.5f);
-    while (a * (a + 1) / 2 > p) a--;
-    while ((a + 1) * (a + 2) / 2 <= p) a++;
-    pair_tab[p] = (unsigned short)(a | ((p - a * (a + 1) / 2) << 8));
-  }
-}
-
-__device__ __forceinline__ double lds_f64(unsigned a) {
-  double v;
-  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
-  return v;
-}
-
-// H(i,j) of the tree layout (0 if neither dof is an ancestor of the other)
+// Same problem and same pivoting rules as qp_solve above, but neither H nor c is ever formed.  With v_i the
+// "spatial velocity" of dof i's link (v_i = v_parent + S_i x_i), the objective of mink's build_ik is
+//   1/2 sum_t v' K_t v + sum_t g_t' v  (v at the link task t hangs on)  +  1/2 d |x|^2,   d = damping + lm * sum mu,
+// i.e. the forward dynamics of a tree whose link "inertias" are the task stiffnesses K_t, whose bias forces are g_t
+// and whose joints carry an armature d - so the stationary point is what the articulated-body algorithm computes,
+// in O(n) 6x6 operations instead of the O(sum depth^2) of a factorisation of H:
+//   up   (leaves to root):  X_i = [I_i | p_i] = own tasks + sum_children X^a_c,
+//                            U_c = I_c S_c,  D_c = S_c'U_c + d,  alpha_c = 1/D_c,  beta_c = S_c'p_c / D_c,
+//                            X^a_c = [I_c - U_c U_c' alpha_c | p_c - U_c beta_c];
+//   down (root to leaves):  x_c = -(U_c'v_parent) alpha_c - beta_c,  v_c = v_parent + S_c x_c.
+// A dof held at a bound b_c is a locked joint: alpha_c = 0, beta_c = -b_c (then X^a_c = [I_c | p_c + U_c b_c] and
+// the same downward formula returns x_c = b_c).  Its multiplier is (Hx + c)_c = S_c' sum_{t below c} f_t + d x_c with
+// f_t = K_t v + g_t.  All spatial quantities are expressed about the one reference point O of stage_fk, so nothing is
+// transformed between links.  The schedule is static (DevModel.aba_*, built at model creation per stage): dofs without a
+// task below them are left out (x = 0 or their bound), dofs of equal height share a level; X blocks live in the task
+// blocks themselves (leaves), in one accumulator per leaf-to-branch chain, updated in place.
+// Lanes: phase 1 (U, alpha, beta) runs 4 dofs per pass, 8 lanes each (6 rows + alpha + beta); phase 2 (X^a into the
+// parent) one dof per pass, lane = one of the 27 numbers of the block; the downward pass 4 dofs per pass.
+// `act_lo`/`act_hi` seed the search and return the final active set; returns #passes of the pivoting loop.
 template <class MV>
-__device__ __forceinline__ double tree_at(const MV& mv, const double* H, int i, int j) {
+__device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double* __restrict__ sm, int stage, double mu_sum,
+                                            int lane, unsigned long long& act_lo, unsigned long long& act_hi) {
   const DevModel& M = mv.M();
-  const int di = mv(M.dof_depth)[i], dj = mv(M.dof_depth)[j];
-  if (dj <= di) { const int e = mv(M.dof_rowptr)[i] + dj; return mv(M.dof_anc)[e] == j ? H[e] : 0.0; }
-  const int e = mv(M.dof_rowptr)[j] + di;
-  return mv(M.dof_anc)[e] == i ? H[e] : 0.0;
-}
-
-template <class MV>
-__device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restrict__ H, const double (&c)[2],
-                                          const double (&lo)[2], const double (&hi)[2],
-                                          double* __restrict__ W, double* __restrict__ lrow, double* __restrict__ rv,
-                                          double* __restrict__ x, const unsigned short* __restrict__ pair_tab, int lane,
-                                          unsigned long long& act_lo, unsigned long long& act_hi) {
-  const DevModel& M = mv.M();
-  const int n = M.nv, nnz = M.nnz;
-  const short* anc = mv(M.dof_anc);
-  const short* ancrow = mv(M.dof_ancrow);
-  const int* depth = mv(M.dof_depth);
-  const int* rowptr = mv(M.dof_rowptr);
-  const int2* elim_lane = mv(M.elim_lane);
-  const int2* elim_ops = mv(M.elim_ops);
-  const int* elim_opstart = mv(M.elim_opstart);
-  rv = W + nnz;                   // the program addresses factor and right-hand side as one array
-  char* Wc = (char*)W;
-  const unsigned lrow_s = (unsigned)__cvta_generic_to_shared(lrow);
-  const int nstep = M.n_elim_step, maxd = M.max_depth;
+  const int n = M.nv, m = M.n_task[stage];
+  const double diag = M.damping + M.lm_damping * mu_sum;
+  double* XA = sm + lay.K;
+  const double* S = sm + lay.S;
+  double* Ud = sm + lay.Ud;
+  double* v = sm + lay.v;
+  double* x = sm + lay.x;
+  double* fv = sm + lay.e;                  // task forces of the KKT check (e is dead during the solve)
+  const double* q = sm + lay.q;
+  const int4* uplev = mv(M.aba_uplev) + M.aba_up0[stage];
+  const int2* dnlev = mv(M.aba_dnlev) + M.aba_dn0[stage];
+  const int2* p1 = mv(M.aba_p1);
+  const int4* p2 = mv(M.aba_p2);
+  const int2* dn = mv(M.aba_dn);
+  const int nup = M.aba_nup[stage], ndn = M.aba_ndn[stage];
+  const int g8 = lane >> 3, i8 = lane & 7;
+  // lane e of phase 2 handles entry e of a block: K(a,b) for e < 21, g(a) for e >= 21 (its factor is beta, slot 7 of Ud)
+  int pa = 0, pb = 7;
+  if (lane < 21) { while ((pa + 1) * (pa + 2) / 2 <= lane) pa++; pb = lane - pa * (pa + 1) / 2; }
+  else if (lane < 27) pa = lane - 21;
   const int i0 = lane, i1 = lane + 32;
-  const bool has0 = i0 < n, has1 = i1 < n, two = n > 32;
-  const double lo0 = lo[0], hi0 = hi[0], lo1 = lo[1], hi1 = hi[1], c0 = c[0], c1 = c[1];    // lane l owns dofs l and l+32
-  const int d0 = has0 ? depth[i0] : -1, d1 = has1 ? depth[i1] : -1;
-  const int rp0 = has0 ? rowptr[i0] : 0, rp1 = has1 ? rowptr[i1] : 0;
+  const bool has0 = i0 < n, has1 = i1 < n;
+  // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs
+  double lo0 = -INFINITY, hi0 = INFINITY, lo1 = -INFINITY, hi1 = INFINITY;
+  if (has0 && mv(M.dof_limited)[i0]) {
+    const double qv = q[mv(M.dof_qadr)[i0]];
+    hi0 = M.limit_gain * (mv(M.dof_hi)[i0] - qv); lo0 = -M.limit_gain * (qv - mv(M.dof_lo)[i0]);
+  }
+  if (has1 && mv(M.dof_limited)[i1]) {
+    const double qv = q[mv(M.dof_qadr)[i1]];
+    hi1 = M.limit_gain * (mv(M.dof_hi)[i1] - qv); lo1 = -M.limit_gain * (qv - mv(M.dof_lo)[i1]);
+  }
+  // tasks that hang on the same dof are summed into the first of them; the block of zeros stands in for "no task"
+  {
+    const int2* mg = mv(M.aba_merge) + stage * GMR_MAX_TASKS;
+    for (int k = 0; k < M.aba_nmerge[stage]; k++) {
+      const int2 pr = mg[k];
+      if (lane < GMR_KS) XA[GMR_KS * pr.x + lane] += XA[GMR_KS * pr.y + lane];
+    }
+    if (lane < GMR_KS) XA[GMR_KS * M.aba_zero[stage] + lane] = 0.0;
+  }
   int st0 = 0, st1 = 0;      // 0 free, -1 at lower, +1 at upper; a seed is only honoured where the bound is finite
   if (has0) st0 = ((act_lo >> i0) & 1ull) && lo0 > -INFINITY ? -1 : (((act_hi >> i0) & 1ull) && hi0 < INFINITY ? 1 : 0);
   if (has1) st1 = ((act_lo >> i1) & 1ull) && lo1 > -INFINITY ? -1 : (((act_hi >> i1) & 1ull) && hi1 < INFINITY ? 1 : 0);
   unsigned long long act = (unsigned long long)__ballot_sync(GMR_FULL, st0 != 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 != 0) << 32);
   int best = n + 1, p = 3, nfact = 0;
-  bool spd = true;
   double r0 = 0, r1 = 0;
 #pragma unroll 1
   for (int it = 0; it < 400; it++) {
-    // ---- right-hand side: active rows carry their bound, free rows -c_F - H_FA x_A
+    // dofs at a bound carry it; free dofs without a task below them stay at 0 (the sweeps skip them)
     const double xa0 = st0 < 0 ? lo0 : (st0 > 0 ? hi0 : 0.0), xa1 = st1 < 0 ? lo1 : (st1 > 0 ? hi1 : 0.0);
-    r0 = st0 ? xa0 : -c0;
-    r1 = st1 ? xa1 : -c1;
-    if (act) {
-#pragma unroll 1
-      for (unsigned long long mk = act; mk; mk &= mk - 1) {
-        const int j = __ffsll((long long)mk) - 1;
-        const double xj = __shfl_sync(GMR_FULL, j < 32 ? xa0 : xa1, j & 31);
-        if (has0 && !st0) r0 -= tree_at(mv, H, i0, j) * xj;
-        if (has1 && !st1) r1 -= tree_at(mv, H, i1, j) * xj;
-      }
-    }
-    if (has0) rv[i0] = r0;
-    if (has1) rv[i1] = r1;
-    for (int e = lane; e < nnz; e += 32) W[e] = H[e];
+    if (has0) x[i0] = xa0;
+    if (has1) x[i1] = xa1;
     __syncwarp();
-    // ---- L'L factorisation + the sweep L'y = r, driven by the model's static elimination program:
-    // a step scales up to 3 unrelated rows at once (lane = one stored entry; y_i = r_i / L_ii rides in
-    // the row's diagonal lane), then applies the merged updates of those rows, one target per lane.
-    // The program holds byte offsets (entries relative to W, lanes relative to the 256-byte aligned lrow).
-    bool notpd = false;
-    int2 lt_next = elim_lane[lane];
-    int q0_next = elim_opstart[0];
+    // ---- upward sweep
 #pragma unroll 1
-    for (int sidx = 0; sidx < nstep; sidx++) {
-      const int2 lt = lt_next;
-      const int q0 = q0_next, qend = elim_opstart[sidx + 1];
-      lt_next = elim_lane[min(sidx + 1, nstep - 1) * 32 + lane];     // prefetch the next step's lane table
-      q0_next = qend;
-      const bool valid = lt.x & 1, isd = lt.x & 2;
-      const int dl = (lt.x >> 16) & 31, col = lt.y & 0xff, row = (lt.y >> 8) & 0xff;
-      double* wp = (double*)(Wc + (lt.x & 0xfff8));
-      double* rp = (double*)(Wc + ((unsigned)lt.y >> 16));
-      const double w = valid ? *wp : 1.0;
-      const double ri = isd ? *rp : 0.0;
-      const bool rowact = valid && ((act >> row) & 1ull), colact = valid && ((act >> col) & 1ull);
-      double piv = __shfl_sync(GMR_FULL, w, dl);
-      if (rowact) piv = 1.0;                                     // identity row, y_i = the bound
-      if (!(piv > 0.0)) { notpd = true; piv = 1.0; }
-      const double inv = rsqrt(piv);
-      const double l = (rowact || colact) ? 0.0 : w * inv;
-      const double yi = ri * inv;
-      __syncwarp();
-      if (valid) {
-        *wp = isd ? inv : l;                                     // diagonal stores 1/L_ii
-        lrow[lane] = isd ? yi : l;
-        if (isd) *rp = yi;
+    for (int lv = 0; lv < nup; lv++) {
+      const int4 L = uplev[lv];
+#pragma unroll 1
+      for (int ps = L.x; ps < L.y; ps++) {                       // phase 1: U_c, alpha_c, beta_c
+        const int2 en = p1[ps * 4 + g8];
+        const bool valid = en.x >= 0;
+        const int c = valid ? en.x : 0;
+        const double* Xc = XA + GMR_KS * en.y;
+        const double* Sc = S + GMR_SS * c;
+        double U = 0.0, t = 0.0, w = 0.0;
+        if (i8 < 6) {
+          const int ii = i8 * (i8 + 1) / 2;
+#pragma unroll
+          for (int j = 0; j < 6; j++) U += Xc[i8 >= j ? ii + j : j * (j + 1) / 2 + i8] * Sc[j];
+          const double si = Sc[i8];
+          t = si * U;
+          w = si * Xc[21 + i8];
+        }
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) { t += __shfl_xor_sync(GMR_FULL, t, o); w += __shfl_xor_sync(GMR_FULL, w, o); }
+        const bool isact = (act >> c) & 1ull;
+        const double inv = 1.0 / (t + diag);
+        const double ab = i8 == 6 ? (isact ? 0.0 : inv) : (isact ? -x[c] : w * inv);
+        if (valid) Ud[8 * c + i8] = i8 < 6 ? U : ab;
       }
       __syncwarp();
-      // the op word of the next pass is fetched while this pass waits on its operands (one shared-memory round
-      // trip off the dependent chain of every pass; the table is padded by one pass of slack)
-      int2 op_next = elim_ops[q0 + lane];
 #pragma unroll 1
-      for (int q = q0 + lane; q < qend; q += 32) {
-        const int2 op = op_next;
-        op_next = elim_ops[q + 32];
-        double* tp = (double*)(Wc + (op.x & 0xfff8));
-        const unsigned cy = (unsigned)op.y;
-        double acc = lds_f64(lrow_s | (cy & 0xf8u)) * lds_f64(lrow_s | ((cy >> 8) & 0xf8u));
-        const int nc = op.x & 3;
-        if (nc >= 2) acc += lds_f64(lrow_s | ((cy >> 16) & 0xf8u)) * lds_f64(lrow_s | (cy >> 24));
-        if (nc == 3) {
-          const unsigned cx = (unsigned)op.x >> 16;
-          acc += lds_f64(lrow_s | (cx & 0xf8u)) * lds_f64(lrow_s | (cx >> 8));
+      for (int ps = L.z; ps < L.w; ps++) {                       // phase 2: X_parent (+)= X^a_c
+        const int4 op = p2[ps];
+        if (lane < GMR_KS) {
+          const double* ud = Ud + 8 * op.x;
+          const double ub = ud[pb];
+          const double fac = lane < 21 ? ub * ud[6] : ub;
+          XA[GMR_KS * op.z + lane] = XA[GMR_KS * op.w + lane] + (XA[GMR_KS * op.y + lane] - ud[pa] * fac);
         }
-        *tp -= acc;
       }
       __syncwarp();
     }
-    if (__any_sync(GMR_FULL, notpd)) spd = false;
     nfact++;
-    // ---- L x = y, wavefront over depth
-    r0 = has0 ? rv[i0] : 0.0;
-    r1 = has1 ? rv[i1] : 0.0;
-    {
-      const double* w0p = W + rp0;
-      const double* w1p = W + rp1;
-      const short* a0p = anc + rp0;
-      const short* a1p = anc + rp1;
+    // ---- downward sweep
 #pragma unroll 1
-      for (int a = 0; a <= maxd; a++, w0p++, w1p++, a0p++, a1p++) {
-        const double wv0 = d0 >= a ? *w0p : 0.0;
-        if (d0 == a) { r0 *= wv0; rv[i0] = r0; }
-        double wv1 = 0.0;
-        if (two) {
-          if (d1 >= a) wv1 = *w1p;
-          if (d1 == a) { r1 *= wv1; rv[i1] = r1; }
+    for (int lv = 0; lv < ndn; lv++) {
+      const int2 L = dnlev[lv];
+#pragma unroll 1
+      for (int ps = L.x; ps < L.y; ps++) {
+        const int2 en = dn[ps * 4 + g8];
+        const bool valid = en.x >= 0;
+        const int c = valid ? en.x : 0;
+        const double vp = (valid && en.y >= 0 && i8 < 6) ? v[6 * en.y + i8] : 0.0;
+        const double* ud = Ud + 8 * c;
+        double dot = i8 < 6 ? ud[i8] * vp : 0.0;
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) dot += __shfl_xor_sync(GMR_FULL, dot, o);
+        const double xc = -dot * ud[6] - ud[7];
+        if (valid) {
+          if (i8 < 6) v[6 * c + i8] = vp + S[GMR_SS * c + i8] * xc;
+          else if (i8 == 6) x[c] = xc;
         }
-        __syncwarp();
-        if (d0 > a) r0 -= wv0 * rv[*a0p];
-        if (two && d1 > a) r1 -= wv1 * rv[*a1p];
       }
+      __syncwarp();
     }
-    // exact bounds on the active set (the solve reproduces them up to rounding)
+    r0 = has0 ? x[i0] : 0.0;
+    r1 = has1 ? x[i1] : 0.0;
+    // exact bounds on the active set (the sweep reproduces them up to rounding)
     if (st0) r0 = xa0;
     if (st1) r1 = xa1;
-    if (has0) x[i0] = r0;
-    if (has1) x[i1] = r1;
-    __syncwarp();
     // ---- KKT check
     bool bad0 = false, bad1 = false;
     if (has0 && !st0) bad0 = (r0 < lo0 - QP_PTOL) || (r0 > hi0 + QP_PTOL);
     if (has1 && !st1) bad1 = (r1 < lo1 - QP_PTOL) || (r1 > hi1 + QP_PTOL);
     if (act) {
-      if (has0 && st0) {
-        double g = c0;
-#pragma unroll 1
-        for (int j = 0; j < n; j++) g += tree_at(mv, H, i0, j) * x[j];
-        bad0 = st0 < 0 ? (g < -QP_DTOL) : (g > QP_DTOL);
+      const int* tdof = mv(M.task_dof) + stage * GMR_MAX_TASKS;
+      for (int k = lane; k < 6 * m; k += 32) {                   // f_t = K_t v + g_t
+        const int t = k / 6, row = k - 6 * t, a = tdof[t];
+        const double* Kt = XA + GMR_KS * t;
+        double acc = Kt[21 + row];
+        if (a >= 0) {
+          const int ii = row * (row + 1) / 2;
+#pragma unroll
+          for (int j = 0; j < 6; j++) acc += Kt[row >= j ? ii + j : j * (j + 1) / 2 + row] * v[6 * a + j];
+        }
+        fv[GMR_ES * t + row] = acc;
       }
-      if (has1 && st1) {
-        double g = c1;
-#pragma unroll 1
-        for (int j = 0; j < n; j++) g += tree_at(mv, H, i1, j) * x[j];
-        bad1 = st1 < 0 ? (g < -QP_DTOL) : (g > QP_DTOL);
+      __syncwarp();
+      const unsigned* tmask = mv(M.dof_taskmask) + stage * n;
+      const unsigned keep = M.aba_kktmask[stage];
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        const int i = r ? i1 : i0;
+        const int st = r ? st1 : st0;
+        if ((r ? has1 : has0) && st) {
+          double F[6] = {0, 0, 0, 0, 0, 0};
+          for (unsigned mk = tmask[i] & keep; mk; mk &= mk - 1) {
+            const double* f = fv + GMR_ES * (__ffs(mk) - 1);
+#pragma unroll
+            for (int k = 0; k < 6; k++) F[k] += f[k];
+          }
+          double g = diag * (r ? r1 : r0);
+#pragma unroll
+          for (int k = 0; k < 6; k++) g += S[GMR_SS * i + k] * F[k];
+          const bool bad = st < 0 ? (g < -QP_DTOL) : (g > QP_DTOL);
+          if (r) bad1 = bad; else bad0 = bad;
+        }
       }
+      __syncwarp();
     }
     const unsigned b0 = __ballot_sync(GMR_FULL, bad0), b1 = __ballot_sync(GMR_FULL, bad1);
     const int nbad = __popc(b0) + __popc(b1);
@@ -843,10 +835,22 @@ __device__ __forceinline__ int qp_solve_tree(const MV& mv, const double* __restr
     if (bad1 && (all || i1 == last)) st1 = st1 ? 0 : (r1 < lo1 ? -1 : 1);
     act = (unsigned long long)__ballot_sync(GMR_FULL, st0 != 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 != 0) << 32);
   }
+  if (has0) x[i0] = r0;
+  if (has1) x[i1] = r1;
   act_lo = (unsigned long long)__ballot_sync(GMR_FULL, st0 < 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 < 0) << 32);
   act_hi = (unsigned long long)__ballot_sync(GMR_FULL, st0 > 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 > 0) << 32);
   __syncwarp();
-  return spd ? nfact : -nfact;
+  return nfact;
+}
+
+// H(i,j) of the tree layout (0 if neither dof is an ancestor of the other)
+template <class MV>
+__device__ __forceinline__ double tree_at(const MV& mv, const double* H, int i, int j) {
+  const DevModel& M = mv.M();
+  const int di = mv(M.dof_depth)[i], dj = mv(M.dof_depth)[j];
+  if (dj <= di) { const int e = mv(M.dof_rowptr)[i] + dj; return mv(M.dof_anc)[e] == j ? H[e] : 0.0; }
+  const int e = mv(M.dof_rowptr)[j] + di;
+  return mv(M.dof_anc)[e] == i ? H[e] : 0.0;
 }
 
 // ------------------------------------------------------------------ Kernel 4: integrate
