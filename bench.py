@@ -254,7 +254,7 @@ def run_b200(args):
     iters = diag["iters"].double()
     iters_per_frame = float(iters.sum(-1).mean().item())
     hit_max = float((diag["iters"] >= dm.desc.c.max_iter + 1).any(-1).double().mean().item())
-    bad_fact = int((diag["nfact"] < 0).sum().item())
+    sweeps_per_solve = float((diag["nfact"].double().sum() / iters.sum()).item())
     del diag
     for _ in range(max(W - 1, 0)):
         br.reset()
@@ -344,7 +344,7 @@ def run_b200(args):
             "gpu_launches": 2 * K, "gpu_launches_note": "per step: fill_rows_kernel (reset to qpos0) + clip_kernel",
             "clocks": clk, "roofline": roofline,
             "convergence": {"iters_per_frame": iters_per_frame, "frames_hitting_max_iter": hit_max,
-                            "non_spd_factorisations": bad_fact}, "checksum": checksum}
+                            "qp_sweeps_per_solve": sweeps_per_solve}, "checksum": checksum}
     if not args.no_cpu_baseline and world == 1:
         desc = dm.desc
         hn = human_host.numpy()

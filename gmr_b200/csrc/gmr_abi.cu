@@ -265,14 +265,17 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       int* L = &aba_uplev[4 * (aba_up0[k] + hh)];
       std::vector<int> todo;
       for (int i = nv - 1; i >= 0; i--) if (in[i] && hgt[i] == hh) todo.push_back(i);
-      L[0] = (int)aba_p1.size() / 8;
+      L[0] = (int)aba_p1.size() / 16;
       for (size_t pos = 0; pos < todo.size(); pos += 4)
         for (int g = 0; g < 4; g++) {
           const bool have = pos + g < todo.size();
-          aba_p1.push_back(have ? todo[pos + g] : -1);
-          aba_p1.push_back(have ? xblk[todo[pos + g]] : 0);
+          const int c = have ? todo[pos + g] : 0;
+          aba_p1.push_back(have ? c : -1);
+          aba_p1.push_back(have ? xblk[c] * GMR_KS * 8 : 0);
+          aba_p1.push_back(c * GMR_SS * 8);
+          aba_p1.push_back(c * 64);
         }
-      L[1] = (int)aba_p1.size() / 8;
+      L[1] = (int)aba_p1.size() / 16;
       L[2] = (int)aba_p2.size() / 4;
       for (int c : todo) {
         const int pr = dof_parent[c];
@@ -284,7 +287,8 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
           base = own[pr];                                // -1 -> the block of zeros, patched below
         } else base = acc[pr];
         xblk[pr] = acc[pr];
-        aba_p2.push_back(c); aba_p2.push_back(xblk[c]); aba_p2.push_back(acc[pr]); aba_p2.push_back(base);
+        aba_p2.push_back(c * 64); aba_p2.push_back(xblk[c] * GMR_KS * 8); aba_p2.push_back(acc[pr] * GMR_KS * 8);
+        aba_p2.push_back(base < 0 ? -1 : base * GMR_KS * 8);
       }
       L[3] = (int)aba_p2.size() / 4;
     }
@@ -305,14 +309,17 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       int* L = &aba_dnlev[2 * (aba_dn0[k] + dd)];
       std::vector<int> todo;
       for (int i = 0; i < nv; i++) if (in[i] && dep[i] == dd) todo.push_back(i);
-      L[0] = (int)aba_dn.size() / 8;
+      L[0] = (int)aba_dn.size() / 16;
       for (size_t pos = 0; pos < todo.size(); pos += 4)
         for (int g = 0; g < 4; g++) {
           const bool have = pos + g < todo.size();
-          aba_dn.push_back(have ? todo[pos + g] : -1);
-          aba_dn.push_back(have ? dof_parent[todo[pos + g]] : -1);
+          const int c = have ? todo[pos + g] : 0, pr = have ? dof_parent[c] : -1;
+          aba_dn.push_back(have ? c : -1);
+          aba_dn.push_back(pr >= 0 ? pr * 48 : -1);
+          aba_dn.push_back(c * 48);
+          aba_dn.push_back(c * GMR_SS * 8);
         }
-      L[1] = (int)aba_dn.size() / 8;
+      L[1] = (int)aba_dn.size() / 16;
     }
     aba_ndn[k] = dmax + 1;
   }
@@ -320,7 +327,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   for (int k = 0; k < 2; k++)
     for (int lv = 0; lv < aba_nup[k]; lv++) {
       const int* L = &aba_uplev[4 * (aba_up0[k] + lv)];
-      for (int ps = L[2]; ps < L[3]; ps++) if (aba_p2[4 * ps + 3] < 0) aba_p2[4 * ps + 3] = aba_zero[k];
+      for (int ps = L[2]; ps < L[3]; ps++) if (aba_p2[4 * ps + 3] < 0) aba_p2[4 * ps + 3] = aba_zero[k] * GMR_KS * 8;
     }
   for (int i = 0; i < d->n_scaled; i++)
     if (d->scaled_human_index[i] < 0 || d->scaled_human_index[i] >= d->n_human) return fail(-5, "scaled_human_index out of range");
@@ -432,8 +439,8 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
     h.aba_kktmask[k] = aba_kktmask[k]; h.aba_up0[k] = aba_up0[k]; h.aba_dn0[k] = aba_dn0[k];
   }
   h.aba_blocks = aba_blocks;
-  h.aba_uplev = (const int4*)(B0 + o_aul); h.aba_dnlev = (const int2*)(B0 + o_adl); h.aba_p1 = (const int2*)(B0 + o_ap1);
-  h.aba_p2 = (const int4*)(B0 + o_ap2); h.aba_dn = (const int2*)(B0 + o_adn); h.aba_merge = (const int2*)(B0 + o_amg);
+  h.aba_uplev = (const int4*)(B0 + o_aul); h.aba_dnlev = (const int2*)(B0 + o_adl); h.aba_p1 = (const int4*)(B0 + o_ap1);
+  h.aba_p2 = (const int4*)(B0 + o_ap2); h.aba_dn = (const int4*)(B0 + o_adn); h.aba_merge = (const int2*)(B0 + o_amg);
   h.task_dof = (const int*)(B0 + o_atd);
   h.fk_rounds = fk_rounds; h.fk_jump = (const short*)(B0 + o_fj);
   h.n_fk = (int)fk_body.size(); h.fk_body = (const short*)(B0 + o_fb);

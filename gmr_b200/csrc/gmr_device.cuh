@@ -79,10 +79,10 @@ struct DevModel {
   unsigned aba_kktmask[2];       // tasks whose block is not merged into another task's (same dof)
   int aba_blocks;                // blocks a warp needs (max over stages)
   const int4* aba_uplev;         // [aba_up0[stage] + level] per level (by height): phase-1 passes [x,y), phase-2 passes [z,w)
-  const int2* aba_p1;            // per (pass, 8-lane group): dof (-1: idle), block of X_dof
-  const int4* aba_p2;            // per pass: dof c, block of X_c, destination block (X_parent), block it adds to
+  const int4* aba_p1;            // per (pass, 8-lane group): dof (-1: idle), byte offsets of X_dof (in the blocks), S_dof, Ud_dof
+  const int4* aba_p2;            // per pass, byte offsets: Ud_c, block of X_c, destination block (X_parent), block it adds to
   const int2* aba_dnlev;         // [aba_dn0[stage] + level] per level (by depth): passes [x,y)
-  const int2* aba_dn;            // per (pass, 8-lane group): dof (-1: idle), parent dof (-1: none)
+  const int4* aba_dn;            // per (pass, 8-lane group): dof (-1: idle), byte offsets of v_parent (-1: none), v_dof, S_dof
   const int2* aba_merge;         // [2*GMR_MAX_TASKS] (dst task, src task) hanging on the same dof
   const int* task_dof;           // [2*GMR_MAX_TASKS] dof the task's body hangs on (-1: none, the task moves nothing)
   // target preparation

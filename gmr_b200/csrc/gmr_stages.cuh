@@ -672,15 +672,32 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   const double* q = sm + lay.q;
   const int4* uplev = mv(M.aba_uplev) + M.aba_up0[stage];
   const int2* dnlev = mv(M.aba_dnlev) + M.aba_dn0[stage];
-  const int2* p1 = mv(M.aba_p1);
+  const int4* p1 = mv(M.aba_p1);
   const int4* p2 = mv(M.aba_p2);
-  const int2* dn = mv(M.aba_dn);
+  const int4* dn = mv(M.aba_dn);
   const int nup = M.aba_nup[stage], ndn = M.aba_ndn[stage];
   const int g8 = lane >> 3, i8 = lane & 7;
   // lane e of phase 2 handles entry e of a block: K(a,b) for e < 21, g(a) for e >= 21 (its factor is beta, slot 7 of Ud)
   int pa = 0, pb = 7;
   if (lane < 21) { while ((pa + 1) * (pa + 2) / 2 <= lane) pa++; pb = lane - pa * (pa + 1) / 2; }
-  else if (lane < 27) pa = lane - 21;
+  else if (lane < GMR_KS) pa = lane - 21;
+  // row i8 of a packed symmetric block: byte offsets of K(i8, 0..5), one byte each
+  unsigned row_lo = 0, row_hi = 0;
+  {
+    const int r = i8 < 6 ? i8 : 0;
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+      const unsigned off = 8u * (unsigned)(r >= j ? r * (r + 1) / 2 + j : j * (j + 1) / 2 + r);
+      if (j < 4) row_lo |= off << (8 * j); else row_hi |= off << (8 * (j - 4));
+    }
+  }
+  // everything below addresses shared memory as base + byte offset (the schedule tables hold byte offsets)
+  char* const XAc = (char*)XA;
+  char* const XAl = XAc + 8 * lane;
+  const char* const Sb = (const char*)S;
+  char* const Udb = (char*)Ud;
+  char* const vb = (char*)v;
+  const int i8b = 8 * i8, pa8 = 8 * pa, pb8 = 8 * pb;
   const int i0 = lane, i1 = lane + 32;
   const bool has0 = i0 < n, has1 = i1 < n;
   // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs
@@ -712,45 +729,56 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   for (int it = 0; it < 400; it++) {
     // dofs at a bound carry it; free dofs without a task below them stay at 0 (the sweeps skip them)
     const double xa0 = st0 < 0 ? lo0 : (st0 > 0 ? hi0 : 0.0), xa1 = st1 < 0 ? lo1 : (st1 > 0 ? hi1 : 0.0);
-    if (has0) x[i0] = xa0;
-    if (has1) x[i1] = xa1;
+    if (has0) { x[i0] = xa0; if (st0) { Ud[8 * i0 + 6] = 0.0; Ud[8 * i0 + 7] = -xa0; } }      // locked joint: alpha = 0, beta = -bound
+    if (has1) { x[i1] = xa1; if (st1) { Ud[8 * i1 + 6] = 0.0; Ud[8 * i1 + 7] = -xa1; } }
     __syncwarp();
     // ---- upward sweep
+    const unsigned actw0 = (unsigned)act, actw1 = (unsigned)(act >> 32);
 #pragma unroll 1
     for (int lv = 0; lv < nup; lv++) {
       const int4 L = uplev[lv];
 #pragma unroll 1
       for (int ps = L.x; ps < L.y; ps++) {                       // phase 1: U_c, alpha_c, beta_c
-        const int2 en = p1[ps * 4 + g8];
+        const int4 en = p1[ps * 4 + g8];                         // dof (-1: idle), byte offsets of X_c, S_c, Ud_c
         const bool valid = en.x >= 0;
-        const int c = valid ? en.x : 0;
-        const double* Xc = XA + GMR_KS * en.y;
-        const double* Sc = S + GMR_SS * c;
+        const char* Xc = XAc + en.y;
+        const char* Sc = Sb + en.z;
         double U = 0.0, t = 0.0, w = 0.0;
         if (i8 < 6) {
-          const int ii = i8 * (i8 + 1) / 2;
-#pragma unroll
-          for (int j = 0; j < 6; j++) U += Xc[i8 >= j ? ii + j : j * (j + 1) / 2 + i8] * Sc[j];
-          const double si = Sc[i8];
+          double U1;
+          U = *(const double*)(Xc + __byte_perm(row_lo, 0, 0x4440)) * *(const double*)(Sc + 0);
+          U1 = *(const double*)(Xc + __byte_perm(row_lo, 0, 0x4441)) * *(const double*)(Sc + 8);
+          U += *(const double*)(Xc + __byte_perm(row_lo, 0, 0x4442)) * *(const double*)(Sc + 16);
+          U1 += *(const double*)(Xc + __byte_perm(row_lo, 0, 0x4443)) * *(const double*)(Sc + 24);
+          U += *(const double*)(Xc + __byte_perm(row_hi, 0, 0x4440)) * *(const double*)(Sc + 32);
+          U1 += *(const double*)(Xc + __byte_perm(row_hi, 0, 0x4441)) * *(const double*)(Sc + 40);
+          U += U1;
+          const double si = *(const double*)(Sc + i8b);
           t = si * U;
-          w = si * Xc[21 + i8];
+          w = si * *(const double*)(Xc + 168 + i8b);
         }
 #pragma unroll
         for (int o = 1; o < 8; o <<= 1) { t += __shfl_xor_sync(GMR_FULL, t, o); w += __shfl_xor_sync(GMR_FULL, w, o); }
-        const bool isact = (act >> c) & 1ull;
-        const double inv = 1.0 / (t + diag);
-        const double ab = i8 == 6 ? (isact ? 0.0 : inv) : (isact ? -x[c] : w * inv);
-        if (valid) Ud[8 * c + i8] = i8 < 6 ? U : ab;
+        const bool isact = valid && (((en.x < 32 ? actw0 : actw1) >> (en.x & 31)) & 1u);
+        // 1 / D, D = S'U + d >= damping > 0 and far inside the float range: single-precision seed + two Newton steps
+        const double D = t + diag;
+        float seed;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(seed) : "f"((float)D));
+        double inv = (double)seed;
+        inv = fma(inv, fma(-D, inv, 1.0), inv);
+        inv = fma(inv, fma(-D, inv, 1.0), inv);
+        // lanes 0..5 store U, lane 6 alpha = 1/D, lane 7 beta = S'p / D (a locked dof keeps the pair its owner lane wrote)
+        if (valid && (i8 < 6 || !isact)) *(double*)(Udb + en.w + i8b) = i8 < 6 ? U : (i8 == 6 ? inv : w * inv);
       }
       __syncwarp();
 #pragma unroll 1
       for (int ps = L.z; ps < L.w; ps++) {                       // phase 2: X_parent (+)= X^a_c
-        const int4 op = p2[ps];
+        const int4 op = p2[ps];                                  // byte offsets: Ud_c, X_c, destination, what it adds to
         if (lane < GMR_KS) {
-          const double* ud = Ud + 8 * op.x;
-          const double ub = ud[pb];
-          const double fac = lane < 21 ? ub * ud[6] : ub;
-          XA[GMR_KS * op.z + lane] = XA[GMR_KS * op.w + lane] + (XA[GMR_KS * op.y + lane] - ud[pa] * fac);
+          const char* ud = Udb + op.x;
+          const double ub = *(const double*)(ud + pb8);
+          const double fac = lane < 21 ? ub * *(const double*)(ud + 48) : ub;
+          *(double*)(XAl + op.z) = *(const double*)(XAl + op.w) + (*(const double*)(XAl + op.y) - *(const double*)(ud + pa8) * fac);
         }
       }
       __syncwarp();
@@ -762,17 +790,17 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
       const int2 L = dnlev[lv];
 #pragma unroll 1
       for (int ps = L.x; ps < L.y; ps++) {
-        const int2 en = dn[ps * 4 + g8];
+        const int4 en = dn[ps * 4 + g8];                         // dof (-1: idle), byte offsets of v_parent (-1: none), v_c, S_c
         const bool valid = en.x >= 0;
         const int c = valid ? en.x : 0;
-        const double vp = (valid && en.y >= 0 && i8 < 6) ? v[6 * en.y + i8] : 0.0;
-        const double* ud = Ud + 8 * c;
-        double dot = i8 < 6 ? ud[i8] * vp : 0.0;
+        const double vp = (en.y >= 0 && i8 < 6) ? *(const double*)(vb + en.y + i8b) : 0.0;
+        const char* ud = Udb + 64 * c;
+        double dot = i8 < 6 ? *(const double*)(ud + i8b) * vp : 0.0;
 #pragma unroll
         for (int o = 1; o < 8; o <<= 1) dot += __shfl_xor_sync(GMR_FULL, dot, o);
-        const double xc = -dot * ud[6] - ud[7];
+        const double xc = -dot * *(const double*)(ud + 48) - *(const double*)(ud + 56);
         if (valid) {
-          if (i8 < 6) v[6 * c + i8] = vp + S[GMR_SS * c + i8] * xc;
+          if (i8 < 6) *(double*)(vb + en.z + i8b) = vp + *(const double*)(Sb + en.w + i8b) * xc;
           else if (i8 == 6) x[c] = xc;
         }
       }

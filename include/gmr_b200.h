@@ -96,7 +96,7 @@ typedef struct gmr_model_desc {
 typedef struct gmr_diag {
   double*  err_dev;      /* [B,T,2] final error1/error2 of the frame, or NULL */
   int32_t* iters_dev;    /* [B,T,2] QP solves per stage (1..max_iter+1), or NULL */
-  int32_t* nfact_dev;    /* [B,T]   Cholesky factorisations in the frame, or NULL */
+  int32_t* nfact_dev;    /* [B,T]   sweeps of the box-QP solver in the frame (one per solve_ik + one per change of the active set), or NULL */
 } gmr_diag;
 
 typedef struct gmr_model gmr_model;
@@ -166,8 +166,9 @@ int gmr_fk(gmr_batch* b, const double* q_dev, double* xpos_out_dev, double* xqua
  * H [B,nv_max,nv_max] (full symmetric), c, lo, hi [B,nv_max]; targets = scaled_dev [B,s,7] */
 int gmr_build_qp(gmr_batch* b, int stage, const double* scaled_dev, double* e_out_dev,
                  double* H_out_dev, double* c_out_dev, double* lo_out_dev, double* hi_out_dev);
-/* Kernel 2+3: one mink.solve_ik on the batch state (motion_retarget.py:147-149): assembly + the
- * tree-structured box QP of the fused path; dq_out_dev [B,nv_max] (= v*dt), nfact [B] or NULL */
+/* Kernel 2+3: one mink.solve_ik on the batch state (motion_retarget.py:147-149): task stiffness + the
+ * tree-structured box QP of the fused path (articulated-body sweeps, H never formed);
+ * dq_out_dev [B,nv_max] (= v*dt), nfact [B] (solver sweeps) or NULL */
 int gmr_solve_ik(gmr_batch* b, int stage, const double* scaled_dev, double* dq_out_dev,
                  int32_t* nfact_out_dev);
 /* Kernel 3 (dense variant): box QP for arbitrary SPD H: x [n_qp,n] ; nfact [n_qp] or NULL */

@@ -341,7 +341,7 @@ def test_full_size_bench_workload():
     np.testing.assert_array_equal(iters[pick], ref["iters"])
     assert np.isfinite(qpos).all()
     assert (iters >= 1).all() and (iters <= 11).all()
-    assert (diag["nfact"].cpu().numpy() > 0).all()          # H was positive definite in every solve
+    assert (diag["nfact"].cpu().numpy() >= iters.sum(-1)).all()          # at least one solver sweep per solve_ik
     for j in range(m.njnt):
         qa = m.jnt_qposadr[j]
         if m.jnt_type[j] == 0:
