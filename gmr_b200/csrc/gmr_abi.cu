@@ -229,10 +229,10 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
     }
   }
   // ---- static schedule of the articulated-body solver (qp_solve_aba), per stage
-  std::vector<int> aba_uplev, aba_dnlev, aba_p1, aba_p2, aba_dn;      // level tables: stage 0's levels, then stage 1's
+  std::vector<int> aba_uplev, aba_dnlev, aba_p1, aba_ch, aba_dn;      // level tables: stage 0's levels, then stage 1's
   int aba_up0[2] = {0, 0}, aba_dn0[2] = {0, 0};
   std::vector<int> aba_merge(2 * MT * 2, 0), task_dof(2 * MT, -1);
-  int aba_nup[2] = {0, 0}, aba_ndn[2] = {0, 0}, aba_nmerge[2] = {0, 0}, aba_zero[2] = {0, 0}, aba_blocks = 1;
+  int aba_nup[2] = {0, 0}, aba_ndn[2] = {0, 0}, aba_nmerge[2] = {0, 0}, aba_doubles = GMR_KS;
   unsigned aba_kktmask[2] = {0u, 0u};
   for (int k = 0; k < 2; k++) {
     if (!d->use_table[k]) continue;
@@ -255,46 +255,40 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       hmax = std::max(hmax, hgt[i]);
       if (dof_parent[i] >= 0) { hgt[dof_parent[i]] = std::max(hgt[dof_parent[i]], hgt[i] + 1); nchild[dof_parent[i]]++; }
     }
-    // blocks: tasks [0, m_k), then one accumulator per chain (a dof reuses the accumulator of its first finished child)
-    std::vector<int> xblk(nv, -1), acc(nv, -1);
+    // accumulators behind the task blocks: one per chain (a dof writes its X over its first child's, row by row)
+    const int accbase = (m_k * GMR_KS * 8 + 15) & ~15;
+    std::vector<int> acc(nv, -1);
+    std::vector<std::vector<int>> kids(nv);
+    for (int i = 0; i < nv; i++) if (in[i] && dof_parent[i] >= 0) kids[dof_parent[i]].push_back(i);
     int nacc = 0;
-    for (int i = 0; i < nv; i++) if (in[i] && nchild[i] == 0) xblk[i] = own[i];        // a leaf always carries a task
-    aba_up0[k] = (int)aba_uplev.size() / 4;
-    aba_uplev.resize(aba_uplev.size() + 4 * (hmax + 1), 0);
+    aba_up0[k] = (int)aba_uplev.size() / 2;
+    aba_uplev.resize(aba_uplev.size() + 2 * (hmax + 1), 0);
     for (int hh = 0; hh <= hmax; hh++) {
-      int* L = &aba_uplev[4 * (aba_up0[k] + hh)];
+      int* L = &aba_uplev[2 * (aba_up0[k] + hh)];
       std::vector<int> todo;
       for (int i = nv - 1; i >= 0; i--) if (in[i] && hgt[i] == hh) todo.push_back(i);
-      L[0] = (int)aba_p1.size() / 16;
+      L[0] = (int)aba_p1.size() / 32;
       for (size_t pos = 0; pos < todo.size(); pos += 4)
         for (int g = 0; g < 4; g++) {
           const bool have = pos + g < todo.size();
           const int c = have ? todo[pos + g] : 0;
+          int cb = (int)aba_ch.size() / 2, ce = cb;
+          if (have) {
+            acc[c] = kids[c].empty() ? nacc++ : acc[kids[c][0]];
+            for (int kid : kids[c]) { aba_ch.push_back(accbase + acc[kid] * GMR_XS * 8); aba_ch.push_back(kid * 64); }
+            ce = (int)aba_ch.size() / 2;
+          }
           aba_p1.push_back(have ? c : -1);
-          aba_p1.push_back(have ? xblk[c] * GMR_KS * 8 : 0);
+          aba_p1.push_back(have ? accbase + acc[c] * GMR_XS * 8 : 0);
           aba_p1.push_back(c * GMR_SS * 8);
           aba_p1.push_back(c * 64);
+          aba_p1.push_back(have && own[c] >= 0 ? own[c] * GMR_KS * 8 : -1);
+          aba_p1.push_back(cb); aba_p1.push_back(ce); aba_p1.push_back(0);
         }
-      L[1] = (int)aba_p1.size() / 16;
-      L[2] = (int)aba_p2.size() / 4;
-      for (int c : todo) {
-        const int pr = dof_parent[c];
-        if (pr < 0) continue;
-        int base;
-        if (acc[pr] < 0) {                               // first child to finish: X_parent = own tasks + X^a_c
-          // the child's accumulator is reused in place; a leaf reads its task block, so it opens a new one
-          acc[pr] = (xblk[c] >= m_k) ? xblk[c] : m_k + nacc++;
-          base = own[pr];                                // -1 -> the block of zeros, patched below
-        } else base = acc[pr];
-        xblk[pr] = acc[pr];
-        aba_p2.push_back(c * 64); aba_p2.push_back(xblk[c] * GMR_KS * 8); aba_p2.push_back(acc[pr] * GMR_KS * 8);
-        aba_p2.push_back(base < 0 ? -1 : base * GMR_KS * 8);
-      }
-      L[3] = (int)aba_p2.size() / 4;
+      L[1] = (int)aba_p1.size() / 32;
     }
     aba_nup[k] = hmax + 1;
-    aba_zero[k] = m_k + nacc;
-    aba_blocks = std::max(aba_blocks, m_k + nacc + 1);
+    aba_doubles = std::max(aba_doubles, accbase / 8 + nacc * GMR_XS);
     // downward levels by depth among the scheduled dofs
     std::vector<int> dep(nv, 0);
     int dmax = -1;
@@ -323,12 +317,6 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
     }
     aba_ndn[k] = dmax + 1;
   }
-  // the stage of a pass is implied by its level table; patch "no own task" (-1) to the stage's block of zeros
-  for (int k = 0; k < 2; k++)
-    for (int lv = 0; lv < aba_nup[k]; lv++) {
-      const int* L = &aba_uplev[4 * (aba_up0[k] + lv)];
-      for (int ps = L[2]; ps < L[3]; ps++) if (aba_p2[4 * ps + 3] < 0) aba_p2[4 * ps + 3] = aba_zero[k] * GMR_KS * 8;
-    }
   for (int i = 0; i < d->n_scaled; i++)
     if (d->scaled_human_index[i] < 0 || d->scaled_human_index[i] >= d->n_human) return fail(-5, "scaled_human_index out of range");
 
@@ -358,7 +346,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
          o_ro = bl.push(vec(d->rot_off, 4 * d->n_scaled)), o_ft = bl.push(vec(d->is_foot, d->n_scaled)),
          o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot),
          o_fj = bl.push(fk_jump), o_fb = bl.push(fk_body), o_aul = bl.push(aba_uplev), o_adl = bl.push(aba_dnlev),
-         o_ap1 = bl.push(aba_p1), o_ap2 = bl.push(aba_p2), o_adn = bl.push(aba_dn), o_amg = bl.push(aba_merge),
+         o_ap1 = bl.push(aba_p1), o_ach = bl.push(aba_ch), o_adn = bl.push(aba_dn), o_amg = bl.push(aba_merge),
          o_atd = bl.push(task_dof);
   const size_t staged_bytes = (bl.bytes.size() + 15) & ~size_t(15);
   // tables only the stage kernels read (gmr_build_qp: the assembly of H), from global memory
@@ -435,12 +423,12 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.ent_row = (const short*)(B0 + o_er); h.dof_topmask = (const unsigned*)(B0 + o_tpm);
   h.task_childmask = (const unsigned*)(B0 + o_chm); h.tasklev_start = (const int*)(B0 + o_tls);
   for (int k = 0; k < 2; k++) {
-    h.aba_nup[k] = aba_nup[k]; h.aba_ndn[k] = aba_ndn[k]; h.aba_nmerge[k] = aba_nmerge[k]; h.aba_zero[k] = aba_zero[k];
+    h.aba_nup[k] = aba_nup[k]; h.aba_ndn[k] = aba_ndn[k]; h.aba_nmerge[k] = aba_nmerge[k];
     h.aba_kktmask[k] = aba_kktmask[k]; h.aba_up0[k] = aba_up0[k]; h.aba_dn0[k] = aba_dn0[k];
   }
-  h.aba_blocks = aba_blocks;
-  h.aba_uplev = (const int4*)(B0 + o_aul); h.aba_dnlev = (const int2*)(B0 + o_adl); h.aba_p1 = (const int4*)(B0 + o_ap1);
-  h.aba_p2 = (const int4*)(B0 + o_ap2); h.aba_dn = (const int4*)(B0 + o_adn); h.aba_merge = (const int2*)(B0 + o_amg);
+  h.aba_doubles = aba_doubles;
+  h.aba_uplev = (const int2*)(B0 + o_aul); h.aba_dnlev = (const int2*)(B0 + o_adl); h.aba_p1 = (const int4*)(B0 + o_ap1);
+  h.aba_ch = (const int2*)(B0 + o_ach); h.aba_dn = (const int4*)(B0 + o_adn); h.aba_merge = (const int2*)(B0 + o_amg);
   h.task_dof = (const int*)(B0 + o_atd);
   h.fk_rounds = fk_rounds; h.fk_jump = (const short*)(B0 + o_fj);
   h.n_fk = (int)fk_body.size(); h.fk_body = (const short*)(B0 + o_fb);
@@ -479,8 +467,8 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h, 
   //                         (gmr_build_qp: F_l of the assembly does);
   //   Ud: per dof [U, alpha, beta] of the solver;
   //   e:  task errors (+ sin/cos of the angle), then the task forces of the KKT check;
-  //   K:  `blocks` blocks of GMR_KS doubles - task stiffness [K_t | g_t], the solver's accumulators, a block of
-  //       zeros; before the stiffness pass the same span holds the local FK transforms / the staged human frame
+  //   K:  `blocks` doubles - task stiffness blocks [K_t | g_t], then the solver's accumulators;
+  //       before the stiffness pass the same span holds the local FK transforms / the staged human frame
   //       (gmr_build_qp: H overlays e/K once the assembly has folded them into F).
   Lay L{};
   int o = 0;
@@ -493,7 +481,7 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h, 
   L.Ud = take(8 * nv);
   const int region2 = o;
   L.e = take(GMR_ES * m);
-  L.K = take(GMR_KS * std::max(blocks, m));
+  L.K = take(std::max(blocks, GMR_KS * m));
   L.tl = L.K; L.ql = L.tl + ((3 * nbody + 1) & ~1);          // FK local transforms alias the blocks
   o = std::max(o, L.ql + ((GMR_QS * nbody + 1) & ~1));
   o = std::max(o, (L.K + 7 * h + 1) & ~1);                   // one frame of the human stream is staged there too
@@ -521,7 +509,7 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
     b->nq_max = std::max(b->nq_max, m->host.nq); b->s_max = std::max(b->s_max, m->host.n_scaled);
     b->h_max = std::max(b->h_max, m->host.n_human); b->nbody_max = std::max(b->nbody_max, m->host.nbody);
     b->nv_max = std::max(b->nv_max, m->host.nv); b->m_max = std::max(b->m_max, m->max_task);
-    b->nnz_max = std::max(b->nnz_max, m->host.nnz); b->blocks_max = std::max(b->blocks_max, m->host.aba_blocks);
+    b->nnz_max = std::max(b->nnz_max, m->host.nnz); b->blocks_max = std::max(b->blocks_max, m->host.aba_doubles);
   }
   if (model_of_instance)
     for (int i = 0; i < B; i++)

@@ -73,14 +73,15 @@ struct DevModel {
   const short* dof_anc;          // [nnz]
   const short* dof_ancrow;       // [nnz] rowptr of that ancestor
   const short* ent_row;          // [nnz] row (dof) of each stored entry
-  // static schedule of the articulated-body box-QP solver (qp_solve_aba), per stage; blocks are indices into the
-  // per-warp array of GMR_KS-double blocks: [0, n_task) the task blocks, then the accumulators, then a block of zeros
-  int aba_nup[2], aba_ndn[2], aba_up0[2], aba_dn0[2], aba_nmerge[2], aba_zero[2];
+  // static schedule of the articulated-body box-QP solver (qp_solve_aba), per stage.  Byte offsets are relative to
+  // the per-warp block array (Lay::K): n_task packed task blocks [K_t | g_t] of GMR_KS doubles, then the dofs'
+  // accumulators X = [I (6x6 rows) | p] of GMR_XS doubles
+  int aba_nup[2], aba_ndn[2], aba_up0[2], aba_dn0[2], aba_nmerge[2];
   unsigned aba_kktmask[2];       // tasks whose block is not merged into another task's (same dof)
-  int aba_blocks;                // blocks a warp needs (max over stages)
-  const int4* aba_uplev;         // [aba_up0[stage] + level] per level (by height): phase-1 passes [x,y), phase-2 passes [z,w)
-  const int4* aba_p1;            // per (pass, 8-lane group): dof (-1: idle), byte offsets of X_dof (in the blocks), S_dof, Ud_dof
-  const int4* aba_p2;            // per pass, byte offsets: Ud_c, block of X_c, destination block (X_parent), block it adds to
+  int aba_doubles;               // doubles of the block array a warp needs (max over stages)
+  const int2* aba_uplev;         // [aba_up0[stage] + level] per level (by height): passes [x,y)
+  const int4* aba_p1;            // per (pass, 8-lane group) two words: {dof (-1: idle), X_dof, S_dof, Ud_dof} {task block (-1), children [y,z) of aba_ch, -}
+  const int2* aba_ch;            // per child: its accumulator, its Ud
   const int2* aba_dnlev;         // [aba_dn0[stage] + level] per level (by depth): passes [x,y)
   const int4* aba_dn;            // per (pass, 8-lane group): dof (-1: idle), byte offsets of v_parent (-1: none), v_dof, S_dof
   const int2* aba_merge;         // [2*GMR_MAX_TASKS] (dst task, src task) hanging on the same dof
@@ -124,6 +125,8 @@ struct ModelView {
 #define GMR_ES 8
 // Task stiffness block: K_t (21, packed lower 6x6) followed by g_t (6).
 #define GMR_KS 27
+// Accumulator of the articulated-body solver: I as 6 full rows, then p.
+#define GMR_XS 42
 
 // Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
 struct Lay {

@@ -652,10 +652,11 @@ __device__ __noinline__ int qp_solve(int n, const double* __restrict__ H, const 
 // the same downward formula returns x_c = b_c).  Its multiplier is (Hx + c)_c = S_c' sum_{t below c} f_t + d x_c with
 // f_t = K_t v + g_t.  All spatial quantities are expressed about the one reference point O of stage_fk, so nothing is
 // transformed between links.  The schedule is static (DevModel.aba_*, built at model creation per stage): dofs without a
-// task below them are left out (x = 0 or their bound), dofs of equal height share a level; X blocks live in the task
-// blocks themselves (leaves), in one accumulator per leaf-to-branch chain, updated in place.
-// Lanes: phase 1 (U, alpha, beta) runs 4 dofs per pass, 8 lanes each (6 rows + alpha + beta); phase 2 (X^a into the
-// parent) one dof per pass, lane = one of the 27 numbers of the block; the downward pass 4 dofs per pass.
+// task below them are left out (x = 0 or their bound), dofs of equal height share a level.
+// Lanes: a pass of the upward sweep handles 4 dofs, 8 lanes each: lane i < 6 gathers row i of X_c (its own task block,
+// packed, plus the children's accumulators minus their rank-1 terms), stores it in the dof's accumulator (full rows,
+// in place over the first child's), forms U_i and the partial sums of D and S'p; lanes 6 and 7 store alpha and beta.
+// The downward pass handles 4 dofs per pass the same way.  One __syncwarp per level in each direction.
 // `act_lo`/`act_hi` seed the search and return the final active set; returns #passes of the pivoting loop.
 template <class MV>
 __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double* __restrict__ sm, int stage, double mu_sum,
@@ -670,17 +671,13 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   double* x = sm + lay.x;
   double* fv = sm + lay.e;                  // task forces of the KKT check (e is dead during the solve)
   const double* q = sm + lay.q;
-  const int4* uplev = mv(M.aba_uplev) + M.aba_up0[stage];
+  const int2* uplev = mv(M.aba_uplev) + M.aba_up0[stage];
   const int2* dnlev = mv(M.aba_dnlev) + M.aba_dn0[stage];
   const int4* p1 = mv(M.aba_p1);
-  const int4* p2 = mv(M.aba_p2);
+  const int2* chl = mv(M.aba_ch);
   const int4* dn = mv(M.aba_dn);
   const int nup = M.aba_nup[stage], ndn = M.aba_ndn[stage];
   const int g8 = lane >> 3, i8 = lane & 7;
-  // lane e of phase 2 handles entry e of a block: K(a,b) for e < 21, g(a) for e >= 21 (its factor is beta, slot 7 of Ud)
-  int pa = 0, pb = 7;
-  if (lane < 21) { while ((pa + 1) * (pa + 2) / 2 <= lane) pa++; pb = lane - pa * (pa + 1) / 2; }
-  else if (lane < GMR_KS) pa = lane - 21;
   // row i8 of a packed symmetric block: byte offsets of K(i8, 0..5), one byte each
   unsigned row_lo = 0, row_hi = 0;
   {
@@ -693,11 +690,10 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   }
   // everything below addresses shared memory as base + byte offset (the schedule tables hold byte offsets)
   char* const XAc = (char*)XA;
-  char* const XAl = XAc + 8 * lane;
   const char* const Sb = (const char*)S;
   char* const Udb = (char*)Ud;
   char* const vb = (char*)v;
-  const int i8b = 8 * i8, pa8 = 8 * pa, pb8 = 8 * pb;
+  const int i8b = 8 * i8;
   const int i0 = lane, i1 = lane + 32;
   const bool has0 = i0 < n, has1 = i1 < n;
   // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs
@@ -710,14 +706,13 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
     const double qv = q[mv(M.dof_qadr)[i1]];
     hi1 = M.limit_gain * (mv(M.dof_hi)[i1] - qv); lo1 = -M.limit_gain * (qv - mv(M.dof_lo)[i1]);
   }
-  // tasks that hang on the same dof are summed into the first of them; the block of zeros stands in for "no task"
+  // tasks that hang on the same dof are summed into the first of them
   {
     const int2* mg = mv(M.aba_merge) + stage * GMR_MAX_TASKS;
     for (int k = 0; k < M.aba_nmerge[stage]; k++) {
       const int2 pr = mg[k];
       if (lane < GMR_KS) XA[GMR_KS * pr.x + lane] += XA[GMR_KS * pr.y + lane];
     }
-    if (lane < GMR_KS) XA[GMR_KS * M.aba_zero[stage] + lane] = 0.0;
   }
   int st0 = 0, st1 = 0;      // 0 free, -1 at lower, +1 at upper; a seed is only honoured where the bound is finite
   if (has0) st0 = ((act_lo >> i0) & 1ull) && lo0 > -INFINITY ? -1 : (((act_hi >> i0) & 1ull) && hi0 < INFINITY ? 1 : 0);
@@ -736,26 +731,45 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
     const unsigned actw0 = (unsigned)act, actw1 = (unsigned)(act >> 32);
 #pragma unroll 1
     for (int lv = 0; lv < nup; lv++) {
-      const int4 L = uplev[lv];
+      const int2 L = uplev[lv];
 #pragma unroll 1
-      for (int ps = L.x; ps < L.y; ps++) {                       // phase 1: U_c, alpha_c, beta_c
-        const int4 en = p1[ps * 4 + g8];                         // dof (-1: idle), byte offsets of X_c, S_c, Ud_c
+      for (int ps = L.x; ps < L.y; ps++) {
+        // dof (-1: idle), byte offsets of its accumulator X_c, of S_c, of Ud_c | its task block (-1: none), children [y, z)
+        const int4 en = p1[(ps * 4 + g8) * 2], eb = p1[(ps * 4 + g8) * 2 + 1];
         const bool valid = en.x >= 0;
-        const char* Xc = XAc + en.y;
         const char* Sc = Sb + en.z;
         double U = 0.0, t = 0.0, w = 0.0;
         if (i8 < 6) {
-          double U1;
-          U = *(const double*)(Xc + __byte_perm(row_lo, 0, 0x4440)) * *(const double*)(Sc + 0);
-          U1 = *(const double*)(Xc + __byte_perm(row_lo, 0, 0x4441)) * *(const double*)(Sc + 8);
-          U += *(const double*)(Xc + __byte_perm(row_lo, 0, 0x4442)) * *(const double*)(Sc + 16);
-          U1 += *(const double*)(Xc + __byte_perm(row_lo, 0, 0x4443)) * *(const double*)(Sc + 24);
-          U += *(const double*)(Xc + __byte_perm(row_hi, 0, 0x4440)) * *(const double*)(Sc + 32);
-          U1 += *(const double*)(Xc + __byte_perm(row_hi, 0, 0x4441)) * *(const double*)(Sc + 40);
-          U += U1;
+          // row i8 of X_c = [I_c | p_c] = own tasks + sum over children of [I - U U' alpha | p - U beta]
+          double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0, a5 = 0, pi = 0;
+          if (eb.x >= 0) {
+            const char* own = XAc + eb.x;
+            a0 = *(const double*)(own + __byte_perm(row_lo, 0, 0x4440)); a1 = *(const double*)(own + __byte_perm(row_lo, 0, 0x4441));
+            a2 = *(const double*)(own + __byte_perm(row_lo, 0, 0x4442)); a3 = *(const double*)(own + __byte_perm(row_lo, 0, 0x4443));
+            a4 = *(const double*)(own + __byte_perm(row_hi, 0, 0x4440)); a5 = *(const double*)(own + __byte_perm(row_hi, 0, 0x4441));
+            pi = *(const double*)(own + 168 + i8b);
+          }
+#pragma unroll 1
+          for (int ch = eb.y; ch < eb.z; ch++) {
+            const int2 cd = chl[ch];                             // byte offsets of the child's accumulator and of its Ud
+            const double* Xr = (const double*)(XAc + cd.x + 6 * i8b);
+            const double* ud = (const double*)(Udb + cd.y);
+            const double ui = *(const double*)(Udb + cd.y + i8b), al = ud[6];
+            a0 += Xr[0] - (ui * ud[0]) * al; a1 += Xr[1] - (ui * ud[1]) * al; a2 += Xr[2] - (ui * ud[2]) * al;
+            a3 += Xr[3] - (ui * ud[3]) * al; a4 += Xr[4] - (ui * ud[4]) * al; a5 += Xr[5] - (ui * ud[5]) * al;
+            pi += *(const double*)(XAc + cd.x + 288 + i8b) - ui * ud[7];
+          }
+          if (valid) {
+            double* Xd = (double*)(XAc + en.y + 6 * i8b);
+            Xd[0] = a0; Xd[1] = a1; Xd[2] = a2; Xd[3] = a3; Xd[4] = a4; Xd[5] = a5;
+            *(double*)(XAc + en.y + 288 + i8b) = pi;
+          }
+          const double* Sd = (const double*)Sc;
+          U = a0 * Sd[0] + a2 * Sd[2] + a4 * Sd[4];
+          U += a1 * Sd[1] + a3 * Sd[3] + a5 * Sd[5];
           const double si = *(const double*)(Sc + i8b);
           t = si * U;
-          w = si * *(const double*)(Xc + 168 + i8b);
+          w = si * pi;
         }
 #pragma unroll
         for (int o = 1; o < 8; o <<= 1) { t += __shfl_xor_sync(GMR_FULL, t, o); w += __shfl_xor_sync(GMR_FULL, w, o); }
@@ -769,17 +783,6 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
         inv = fma(inv, fma(-D, inv, 1.0), inv);
         // lanes 0..5 store U, lane 6 alpha = 1/D, lane 7 beta = S'p / D (a locked dof keeps the pair its owner lane wrote)
         if (valid && (i8 < 6 || !isact)) *(double*)(Udb + en.w + i8b) = i8 < 6 ? U : (i8 == 6 ? inv : w * inv);
-      }
-      __syncwarp();
-#pragma unroll 1
-      for (int ps = L.z; ps < L.w; ps++) {                       // phase 2: X_parent (+)= X^a_c
-        const int4 op = p2[ps];                                  // byte offsets: Ud_c, X_c, destination, what it adds to
-        if (lane < GMR_KS) {
-          const char* ud = Udb + op.x;
-          const double ub = *(const double*)(ud + pb8);
-          const double fac = lane < 21 ? ub * *(const double*)(ud + 48) : ub;
-          *(double*)(XAl + op.z) = *(const double*)(XAl + op.w) + (*(const double*)(XAl + op.y) - *(const double*)(ud + pa8) * fac);
-        }
       }
       __syncwarp();
     }
