@@ -232,7 +232,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   std::vector<int> aba_uplev, aba_dnlev, aba_p1, aba_ch, aba_dn;      // level tables: stage 0's levels, then stage 1's
   int aba_up0[2] = {0, 0}, aba_dn0[2] = {0, 0};
   std::vector<int> aba_merge(2 * MT * 2, 0), task_dof(2 * MT, -1);
-  int aba_nup[2] = {0, 0}, aba_ndn[2] = {0, 0}, aba_nmerge[2] = {0, 0}, aba_doubles = GMR_KS;
+  int aba_nup[2] = {0, 0}, aba_ndn[2] = {0, 0}, aba_nmerge[2] = {0, 0}, aba_root[2] = {-1, -1}, aba_rootdof[2] = {0, 0}, aba_doubles = GMR_KS;
   unsigned aba_kktmask[2] = {0u, 0u};
   for (int k = 0; k < 2; k++) {
     if (!d->use_table[k]) continue;
@@ -255,6 +255,13 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       hmax = std::max(hmax, hgt[i]);
       if (dof_parent[i] >= 0) { hgt[dof_parent[i]] = std::max(hgt[dof_parent[i]], hgt[i] + 1); nchild[dof_parent[i]]++; }
     }
+    // floating base (six unlimited dofs at the top of the tree): solved as one block by the kernel, so dofs
+    // fb .. fb+4 leave the upward schedule (fb+5, the base link, still gathers its X) and all six the downward one
+    int fb = -1;
+    for (int i = 0; i + 5 < nv && fb < 0; i++)
+      if (dof_kind[i] == DOF_FREE_T && dof_parent[i] < 0 && in[i + 5]) fb = i;
+    auto skip_up = [&](int i) { return fb >= 0 && i >= fb && i < fb + 5; };
+    auto skip_dn = [&](int i) { return fb >= 0 && i >= fb && i <= fb + 5; };
     // accumulators behind the task blocks: one per chain (a dof writes its X over its first child's, row by row)
     const int accbase = (m_k * GMR_KS * 8 + 15) & ~15;
     std::vector<int> acc(nv, -1);
@@ -262,11 +269,13 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
     for (int i = 0; i < nv; i++) if (in[i] && dof_parent[i] >= 0) kids[dof_parent[i]].push_back(i);
     int nacc = 0;
     aba_up0[k] = (int)aba_uplev.size() / 2;
-    aba_uplev.resize(aba_uplev.size() + 2 * (hmax + 1), 0);
     for (int hh = 0; hh <= hmax; hh++) {
-      int* L = &aba_uplev[2 * (aba_up0[k] + hh)];
       std::vector<int> todo;
-      for (int i = nv - 1; i >= 0; i--) if (in[i] && hgt[i] == hh) todo.push_back(i);
+      for (int i = nv - 1; i >= 0; i--) if (in[i] && hgt[i] == hh && !skip_up(i)) todo.push_back(i);
+      if (todo.empty()) continue;
+      aba_uplev.resize(aba_uplev.size() + 2, 0);
+      int* L = &aba_uplev[aba_uplev.size() - 2];
+      aba_nup[k]++;
       L[0] = (int)aba_p1.size() / 32;
       for (size_t pos = 0; pos < todo.size(); pos += 4)
         for (int g = 0; g < 4; g++) {
@@ -287,7 +296,8 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
         }
       L[1] = (int)aba_p1.size() / 32;
     }
-    aba_nup[k] = hmax + 1;
+    aba_root[k] = fb >= 0 ? accbase + acc[fb + 5] * GMR_XS * 8 : -1;
+    aba_rootdof[k] = std::max(fb, 0);
     aba_doubles = std::max(aba_doubles, accbase / 8 + nacc * GMR_XS);
     // downward levels by depth among the scheduled dofs
     std::vector<int> dep(nv, 0);
@@ -298,11 +308,13 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       dmax = std::max(dmax, dep[i]);
     }
     aba_dn0[k] = (int)aba_dnlev.size() / 2;
-    aba_dnlev.resize(aba_dnlev.size() + 2 * (dmax + 1), 0);
     for (int dd = 0; dd <= dmax; dd++) {
-      int* L = &aba_dnlev[2 * (aba_dn0[k] + dd)];
       std::vector<int> todo;
-      for (int i = 0; i < nv; i++) if (in[i] && dep[i] == dd) todo.push_back(i);
+      for (int i = 0; i < nv; i++) if (in[i] && dep[i] == dd && !skip_dn(i)) todo.push_back(i);
+      if (todo.empty()) continue;
+      aba_dnlev.resize(aba_dnlev.size() + 2, 0);
+      int* L = &aba_dnlev[aba_dnlev.size() - 2];
+      aba_ndn[k]++;
       L[0] = (int)aba_dn.size() / 16;
       for (size_t pos = 0; pos < todo.size(); pos += 4)
         for (int g = 0; g < 4; g++) {
@@ -315,7 +327,6 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
         }
       L[1] = (int)aba_dn.size() / 16;
     }
-    aba_ndn[k] = dmax + 1;
   }
   for (int i = 0; i < d->n_scaled; i++)
     if (d->scaled_human_index[i] < 0 || d->scaled_human_index[i] >= d->n_human) return fail(-5, "scaled_human_index out of range");
@@ -424,6 +435,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.task_childmask = (const unsigned*)(B0 + o_chm); h.tasklev_start = (const int*)(B0 + o_tls);
   for (int k = 0; k < 2; k++) {
     h.aba_nup[k] = aba_nup[k]; h.aba_ndn[k] = aba_ndn[k]; h.aba_nmerge[k] = aba_nmerge[k];
+    h.aba_root[k] = aba_root[k]; h.aba_rootdof[k] = aba_rootdof[k];
     h.aba_kktmask[k] = aba_kktmask[k]; h.aba_up0[k] = aba_up0[k]; h.aba_dn0[k] = aba_dn0[k];
   }
   h.aba_doubles = aba_doubles;
@@ -480,7 +492,7 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h, 
   L.S = take(GMR_SS * nv);
   L.Ud = take(8 * nv);
   const int region2 = o;
-  L.e = take(GMR_ES * m);
+  L.e = take(std::max(GMR_ES * m, 32));                      // also the scratch of the solver's root block (27) and its task forces
   L.K = take(std::max(blocks, GMR_KS * m));
   L.tl = L.K; L.ql = L.tl + ((3 * nbody + 1) & ~1);          // FK local transforms alias the blocks
   o = std::max(o, L.ql + ((GMR_QS * nbody + 1) & ~1));

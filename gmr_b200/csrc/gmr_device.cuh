@@ -77,6 +77,7 @@ struct DevModel {
   // the per-warp block array (Lay::K): n_task packed task blocks [K_t | g_t] of GMR_KS doubles, then the dofs'
   // accumulators X = [I (6x6 rows) | p] of GMR_XS doubles
   int aba_nup[2], aba_ndn[2], aba_up0[2], aba_dn0[2], aba_nmerge[2];
+  int aba_root[2], aba_rootdof[2];   // floating base solved as one block: byte offset of the base link's accumulator (-1: none), first base dof
   unsigned aba_kktmask[2];       // tasks whose block is not merged into another task's (same dof)
   int aba_doubles;               // doubles of the block array a warp needs (max over stages)
   const int2* aba_uplev;         // [aba_up0[stage] + level] per level (by height): passes [x,y)

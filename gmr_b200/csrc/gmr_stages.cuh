@@ -637,6 +637,15 @@ __device__ __noinline__ int qp_solve(int n, const double* __restrict__ H, const 
   return spd ? nfact : -nfact;
 }
 
+// 1 / D for D >= damping > 0 and far inside the float range: single-precision seed, two Newton steps (<= 1 ulp)
+__device__ __forceinline__ double rcp_pos(double D) {
+  float seed;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(seed) : "f"((float)D));
+  double inv = (double)seed;
+  inv = fma(inv, fma(-D, inv, 1.0), inv);
+  return fma(inv, fma(-D, inv, 1.0), inv);
+}
+
 // ------------------------------------------------------------------ Kernel 3: exact box QP on the kinematic tree
 // Same problem and same pivoting rules as qp_solve above, but neither H nor c is ever formed.  With v_i the
 // "spatial velocity" of dof i's link (v_i = v_parent + S_i x_i), the objective of mink's build_ik is
@@ -694,6 +703,10 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   char* const Udb = (char*)Ud;
   char* const vb = (char*)v;
   const int i8b = 8 * i8;
+  const int rootX = M.aba_root[stage], rootdof = M.aba_rootdof[stage];
+  int ra = 0, rb = 0;                       // lane e of the root block: M(ra, rb) for e < 21, r(ra) for 21 <= e < 27
+  if (lane < 21) { while ((ra + 1) * (ra + 2) / 2 <= lane) ra++; rb = lane - ra * (ra + 1) / 2; }
+  else if (lane < GMR_KS) ra = lane - 21;
   const int i0 = lane, i1 = lane + 32;
   const bool has0 = i0 < n, has1 = i1 < n;
   // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs
@@ -774,15 +787,77 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
 #pragma unroll
         for (int o = 1; o < 8; o <<= 1) { t += __shfl_xor_sync(GMR_FULL, t, o); w += __shfl_xor_sync(GMR_FULL, w, o); }
         const bool isact = valid && (((en.x < 32 ? actw0 : actw1) >> (en.x & 31)) & 1u);
-        // 1 / D, D = S'U + d >= damping > 0 and far inside the float range: single-precision seed + two Newton steps
-        const double D = t + diag;
-        float seed;
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(seed) : "f"((float)D));
-        double inv = (double)seed;
-        inv = fma(inv, fma(-D, inv, 1.0), inv);
-        inv = fma(inv, fma(-D, inv, 1.0), inv);
+        const double inv = rcp_pos(t + diag);                    // D = S'U + d
         // lanes 0..5 store U, lane 6 alpha = 1/D, lane 7 beta = S'p / D (a locked dof keeps the pair its owner lane wrote)
         if (valid && (i8 < 6 || !isact)) *(double*)(Udb + en.w + i8b) = i8 < 6 ? U : (i8 == 6 ? inv : w * inv);
+      }
+      __syncwarp();
+    }
+    // ---- floating base: its six dofs span R^6 and are never limited, so they are solved as one 6x6 block
+    // (M = S_b' I S_b + d, M x_b = -S_b' p) instead of six more levels up and six down
+    if (rootX >= 0) {
+      const char* Xr = XAc + rootX;
+      if (i8 < 6) {                                             // Y_b = I S_b, group g: b = g, g + 4 -> Ud of the base dofs
+        const double* row = (const double*)(Xr + 6 * i8b);
+        const double r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3], r4 = row[4], r5 = row[5];
+        for (int b = g8; b < 6; b += 4) {
+          const double* Sd = S + GMR_SS * (rootdof + b);
+          Ud[8 * (rootdof + b) + i8] = (r0 * Sd[0] + r2 * Sd[2] + r4 * Sd[4]) + (r1 * Sd[1] + r3 * Sd[3] + r5 * Sd[5]);
+        }
+      }
+      __syncwarp();
+      if (lane < GMR_KS) {                                      // M(a,b), a >= b (lane < 21); r_a (lanes 21..26)
+        const double* Sa = S + GMR_SS * (rootdof + ra);
+        const double* Y = lane < 21 ? Ud + 8 * (rootdof + rb) : (const double*)(Xr + 288);
+        double acc = (Sa[0] * Y[0] + Sa[2] * Y[2] + Sa[4] * Y[4]) + (Sa[1] * Y[1] + Sa[3] * Y[3] + Sa[5] * Y[5]);
+        if (lane < 21 && ra == rb) acc += diag;
+        fv[lane] = acc;
+      }
+      __syncwarp();
+      if (lane < 6) {                                           // lanes 0..5 each solve the block (L D L'); lane i forms v_i
+        double Lm[21], dinv[6], y[6];
+#pragma unroll
+        for (int k = 0; k < 21; k++) Lm[k] = fv[k];
+#pragma unroll
+        for (int j = 0; j < 6; j++) {
+          double tmp[6];
+          double dj = Lm[j * (j + 1) / 2 + j];
+#pragma unroll
+          for (int k = 0; k < j; k++) { tmp[k] = Lm[j * (j + 1) / 2 + k] * Lm[k * (k + 1) / 2 + k]; dj -= Lm[j * (j + 1) / 2 + k] * tmp[k]; }
+          Lm[j * (j + 1) / 2 + j] = dj;
+          dinv[j] = rcp_pos(dj);
+#pragma unroll
+          for (int i = j + 1; i < 6; i++) {
+            double sacc = Lm[i * (i + 1) / 2 + j];
+#pragma unroll
+            for (int k = 0; k < j; k++) sacc -= Lm[i * (i + 1) / 2 + k] * tmp[k];
+            Lm[i * (i + 1) / 2 + j] = sacc * dinv[j];
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 6; i++) {
+          double sacc = -fv[21 + i];
+#pragma unroll
+          for (int k = 0; k < i; k++) sacc -= Lm[i * (i + 1) / 2 + k] * y[k];
+          y[i] = sacc;
+        }
+#pragma unroll
+        for (int i = 0; i < 6; i++) y[i] *= dinv[i];
+#pragma unroll
+        for (int i = 5; i >= 0; i--) {
+          double sacc = y[i];
+#pragma unroll
+          for (int k = i + 1; k < 6; k++) sacc -= Lm[k * (k + 1) / 2 + i] * y[k];
+          y[i] = sacc;
+        }
+        double vi = 0.0;
+#pragma unroll
+        for (int b = 0; b < 6; b++) vi += S[GMR_SS * (rootdof + b) + lane] * y[b];
+        v[6 * (rootdof + 5) + lane] = vi;                       // velocity of the base link: the parent of everything below
+        if (lane == 0) {
+#pragma unroll
+          for (int b = 0; b < 6; b++) x[rootdof + b] = y[b];
+        }
       }
       __syncwarp();
     }
