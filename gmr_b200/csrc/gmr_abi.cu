@@ -550,14 +550,20 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
     // the fused kernel is compiled for 128 registers (16 warps per SM): pick the CTA width that puts
     // the most warps on an SM; ties go to the wider CTA (the staged model is per CTA)
     const size_t blob = n_models == 1 ? models[0]->staged_bytes : 0;
-    const size_t fixed = 2048 + 1024;   // static shared memory of the kernel + the per-CTA reservation
+    // static shared memory of the fused kernel (the staged DevModel) + the 1 KB the hardware reserves per CTA
+    cudaFuncAttributes fa{};
+    size_t stat = 0;
+    for (int dt : {GMR_F32, GMR_F64})
+      for (int st = 0; st < 2; st++)
+        if (cudaFuncGetAttributes(&fa, clip_kernel_ptr(dt, st != 0)) == cudaSuccess) stat = std::max(stat, fa.sharedSizeBytes);
+    const size_t fixed = stat + 1024;
     const size_t sm_total = 228 * 1024;
     b->smem_model = n_models == 1 && per_warp + blob + fixed <= (size_t)dev_smem && !getenv("GMR_DEBUG_GLOBAL_MODEL");
     const size_t extra = fixed + (b->smem_model ? blob : 0);
     const int max_w = GMR_CTA_THREADS / 32;
     int best_w = 1, best_total = 0;
     for (int w = 1; w <= max_w; w++) {
-      if ((size_t)w * per_warp + extra > (size_t)dev_smem + 1024) break;
+      if ((size_t)w * per_warp + extra > (size_t)dev_smem + 1024) break;      // dynamic + static <= the opt-in limit
       int ctas = (int)std::min<size_t>(sm_total / ((size_t)w * per_warp + extra), (size_t)(max_w / w));
       if (ctas * w >= best_total) { best_total = ctas * w; best_w = w; }
     }
@@ -565,7 +571,7 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
     b->warps_per_cta = std::min(best_w, B);
     b->smem_bytes = per_warp * b->warps_per_cta;
     b->clip_smem_bytes = b->smem_bytes + (b->smem_model ? blob : 0);
-    if (b->clip_smem_bytes + 2048 > (size_t)dev_smem) e = cudaErrorInvalidConfiguration;
+    if (b->clip_smem_bytes + stat > (size_t)dev_smem) e = cudaErrorInvalidConfiguration;
   }
   const void* kf = clip_kernel_ptr(GMR_F32, b->smem_model);
   const void* kd = clip_kernel_ptr(GMR_F64, b->smem_model);
