@@ -364,3 +364,32 @@ def test_frame_range_boundaries(T):
     ref = oc.run_clips(dm.desc, human, scale=synth.clip_scales(t, heights), nthreads=8)
     assert _check_clip(qpos[..., :m.nq], ref["qpos"], m, f"T={T}") < 1e-7
     np.testing.assert_array_equal(br.state().cpu().numpy()[:, :m.nq], qpos[:, -1, :m.nq])
+
+
+def test_two_tasks_on_one_dof():
+    """Two task frames that hang on the same dof (a jointed body and a body welded to it): the solver sums their
+    stiffness blocks before its sweeps.  None of the shipped configs does this, so the table is edited here:
+    stage-1 task `left_knee_link` moves to `left_toe_link`, which is welded to `left_ankle_roll_link` (task 3)."""
+    import copy
+    from gmr_b200 import model_pack, synth
+    from gmr_b200.abi import ModelDesc
+    from gmr_b200.engine import BatchedRetargeter, DeviceModel
+    from oracle import oracle as oc
+    m, t = model_pack.build_tables("bvh", "unitree_g1")
+    B, T = 16, 24
+    human, heights, names = synth.synth_human_clips(m, t, "bvh", B=B, T=T, seed=9)
+    t2 = copy.deepcopy(t)
+    toe, ankle = m.body_names.index("left_toe_link"), m.body_names.index("left_ankle_roll_link")
+    assert m.body_jntnum[toe] == 0 and m.body_parentid[toe] == ankle
+    k = t2.task_frame_names[0].index("left_knee_link")
+    assert ankle in list(t2.task_body[0])
+    t2.task_body[0] = np.array(t2.task_body[0]).copy()
+    t2.task_body[0][k] = toe
+    t2.task_frame_names[0][k] = "left_toe_link"
+    dm = DeviceModel(ModelDesc(m, t2, names))
+    br = BatchedRetargeter(dm, B)
+    br.set_heights(heights)
+    qpos, diag = br.run(human, diag=True)
+    ref = oc.run_clips(dm.desc, human, scale=synth.clip_scales(t2, heights), nthreads=8)
+    assert _check_clip(qpos.cpu().numpy()[..., :m.nq], ref["qpos"], m, "merged tasks") < 1e-7
+    np.testing.assert_array_equal(diag["iters"].cpu().numpy(), ref["iters"])
