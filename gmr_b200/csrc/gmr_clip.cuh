@@ -1,10 +1,12 @@
 // gmr_clip.cuh - the fused clip kernel (Kernels 1-4 of the north star in one launch) and the
 // per-stage kernels that expose the same device code for parity tests.
 //
-// Work decomposition: one warp = one IK instance (clip x robot) for the whole clip; frames are
-// strictly sequential inside a clip (warm start, motion_retarget.py:185), clips are independent.
-// Warps pull instances from a global atomic queue (optionally in a host-given order, longest
-// first), so ragged clip lengths balance across the 148 SMs without a tail.
+// Work decomposition: one warp = one IK instance (clip x robot) at a time; frames are strictly
+// sequential inside a clip (warm start, motion_retarget.py:185), clips are independent.  Warps pull
+// work units (32 consecutive frames of one clip, range-major, optionally in a host-given clip order,
+// longest first) from a global atomic queue; the warm start crosses units through the batch state.
+// A launch is therefore bounded below by its slowest clip (a sequential chain of solves): see
+// DESIGN.md section 4 for the measured batch sizes from which the throughput bound takes over.
 #pragma once
 #include "gmr_stages.cuh"
 

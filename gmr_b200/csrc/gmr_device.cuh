@@ -39,7 +39,7 @@ struct DevModel {
   const short* fk_body;      // [n_fk] increasing body ids, entry 0 = world
   int fk_rounds;             // ceil(log2(deepest body))
   const short* fk_jump;      // [fk_rounds*nbody] 2^r-th ancestor of each body, -1 once that is the world
-  const int* level_start;    // [nlevel+1] into level_body (level 1 = children of world)
+  const int* level_start;    // [nlevel+1] into level_body (level 1 = children of world); kept for tools, no kernel reads it
   const int* level_body;     // [nbody-1] body ids sorted by depth
   // joints
   const int* jnt_type;       // [njnt]
