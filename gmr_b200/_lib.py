@@ -18,7 +18,7 @@ EXPORTS = [
     "gmr_batch_destroy", "gmr_batch_reset", "gmr_batch_set_scale", "gmr_batch_get_state",
     "gmr_batch_set_order", "gmr_batch_launch_info", "gmr_batch_dims", "gmr_batch_step", "gmr_batch_run",
     "gmr_target_prep", "gmr_fk", "gmr_build_qp", "gmr_qp_solve", "gmr_fk_bodies_f32", "gmr_probe_fma_peak", "gmr_solve_ik", "gmr_batch_run_host",
-    "gmr_bvh_to_stream", "gmr_smplx_to_stream",
+    "gmr_bvh_to_stream", "gmr_smplx_to_stream", "gmr_model_table",
 ]
 
 _lib = None
@@ -43,6 +43,7 @@ def lib():
     vp, i32 = C.c_void_p, C.c_int32
     L.gmr_model_create.argtypes = [C.POINTER(gmr_model_desc), C.c_int, C.POINTER(vp)]
     L.gmr_model_destroy.argtypes = [vp]
+    L.gmr_model_table.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int]
     L.gmr_batch_create.argtypes = [C.POINTER(vp), C.c_int, vp, C.c_int, vp, C.POINTER(vp)]
     L.gmr_batch_destroy.argtypes = [vp]
     L.gmr_batch_reset.argtypes = [vp, vp]

@@ -23,7 +23,8 @@ static int fail(int code, const std::string& msg) { g_err = msg; return code; }
 struct gmr_model {
   int device = 0;
   DevModel host{};           // device pointers inside
-  char* blob = nullptr;      // one device allocation holding every table
+  char* blob = nullptr;      // one device allocation holding every table (device < 0: = host_blob.data())
+  std::vector<char> host_blob;   // host-only model (device = GMR_HOST_ONLY): the tables, for gmr_model_table
   size_t blob_bytes = 0;
   size_t staged_bytes = 0;   // leading part of the blob that the fused kernel stages in shared memory
   int max_task = 0;
@@ -390,16 +391,22 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
 
   gmr_model* m = new gmr_model();
   m->device = device;
-  int prev = 0;
-  cudaGetDevice(&prev);
-  cudaError_t e = cudaSetDevice(device);
-  if (e == cudaSuccess) e = cudaMalloc(&m->blob, bl.bytes.size());
-  if (e == cudaSuccess) e = cudaMemcpy(m->blob, bl.bytes.data(), bl.bytes.size(), cudaMemcpyHostToDevice);
   Blob tb;
   size_t t_p = tb.push(t_parent), t_t = tb.push(t_trans), t_r = tb.push(t_rot), t_a = tb.push(t_axis), t_d = tb.push(t_dof);
-  if (e == cudaSuccess) e = cudaMalloc(&m->tail_blob, tb.bytes.size());
-  if (e == cudaSuccess) e = cudaMemcpy(m->tail_blob, tb.bytes.data(), tb.bytes.size(), cudaMemcpyHostToDevice);
-  cudaSetDevice(prev);
+  cudaError_t e = cudaSuccess;
+  if (device < 0) {          // host-only: no CUDA call at all; the table pointers below point into host memory
+    m->host_blob = bl.bytes;
+    m->blob = m->host_blob.data();
+  } else {
+    int prev = 0;
+    cudaGetDevice(&prev);
+    e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaMalloc(&m->blob, bl.bytes.size());
+    if (e == cudaSuccess) e = cudaMemcpy(m->blob, bl.bytes.data(), bl.bytes.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMalloc(&m->tail_blob, tb.bytes.size());
+    if (e == cudaSuccess) e = cudaMemcpy(m->tail_blob, tb.bytes.data(), tb.bytes.size(), cudaMemcpyHostToDevice);
+    cudaSetDevice(prev);
+  }
   if (e != cudaSuccess) {
     if (m->blob) cudaFree(m->blob);
     if (m->tail_blob) cudaFree(m->tail_blob);
@@ -456,14 +463,48 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
 
 extern "C" int gmr_model_destroy(gmr_model* m) {
   if (!m) return 0;
-  int prev = 0;
-  cudaGetDevice(&prev);
-  cudaSetDevice(m->device);
-  if (m->blob) cudaFree(m->blob);
-  if (m->tail_blob) cudaFree(m->tail_blob);
-  cudaSetDevice(prev);
+  if (m->device >= 0) {
+    int prev = 0;
+    cudaGetDevice(&prev);
+    cudaSetDevice(m->device);
+    if (m->blob) cudaFree(m->blob);
+    if (m->tail_blob) cudaFree(m->tail_blob);
+    cudaSetDevice(prev);
+  }
   delete m;
   return 0;
+}
+
+// Host-side view of the static schedule of the box-QP solver (DevModel.aba_*), for tests of the flattener:
+// copies table `which` of `stage` into out[0..cap) and returns the number of int32 it holds (or < 0).
+extern "C" int gmr_model_table(const gmr_model* m, int which, int stage, int32_t* out, int cap) {
+  if (!m || stage < 0 || stage > 1) return fail(-1, "bad argument");
+  if (m->device >= 0) return fail(-6, "gmr_model_table needs a host-only model (device = GMR_HOST_ONLY)");
+  const DevModel& h = m->host;
+  std::vector<int32_t> v;
+  auto span = [&](const void* p, size_t n) { const int32_t* q = (const int32_t*)p; v.assign(q, q + n); };
+  int p1_end = 0, dn_end = 0, ch_end = 0;
+  for (int lv = 0; lv < h.aba_nup[stage]; lv++) p1_end = std::max(p1_end, h.aba_uplev[h.aba_up0[stage] + lv].y);
+  for (int lv = 0; lv < h.aba_ndn[stage]; lv++) dn_end = std::max(dn_end, h.aba_dnlev[h.aba_dn0[stage] + lv].y);
+  for (int i = 0; i < p1_end * 4; i++) ch_end = std::max(ch_end, h.aba_p1[2 * i + 1].z);
+  switch (which) {
+    case GMR_TABLE_INFO:
+      v = {h.nv, h.n_task[stage], h.aba_nup[stage], h.aba_ndn[stage], h.aba_nmerge[stage], h.aba_root[stage],
+           h.aba_rootdof[stage], (int32_t)h.aba_kktmask[stage], h.aba_doubles, GMR_KS, GMR_XS, GMR_SS};
+      break;
+    case GMR_TABLE_UPLEV: span(h.aba_uplev + h.aba_up0[stage], 2 * (size_t)h.aba_nup[stage]); break;
+    case GMR_TABLE_UP: span(h.aba_p1, 32 * (size_t)p1_end); break;          // pass indices are global: from pass 0
+    case GMR_TABLE_CHILD: span(h.aba_ch, 2 * (size_t)ch_end); break;
+    case GMR_TABLE_DNLEV: span(h.aba_dnlev + h.aba_dn0[stage], 2 * (size_t)h.aba_ndn[stage]); break;
+    case GMR_TABLE_DN: span(h.aba_dn, 16 * (size_t)dn_end); break;
+    case GMR_TABLE_MERGE: span(h.aba_merge + stage * GMR_MAX_TASKS, 2 * (size_t)h.aba_nmerge[stage]); break;
+    case GMR_TABLE_TASK_DOF: span(h.task_dof + stage * GMR_MAX_TASKS, (size_t)h.n_task[stage]); break;
+    case GMR_TABLE_DOF_PARENT: span(h.dof_parent, (size_t)h.nv); break;
+    case GMR_TABLE_TASKMASK: span(h.dof_taskmask + stage * h.nv, (size_t)h.nv); break;
+    default: return fail(-1, "unknown table");
+  }
+  if (out) for (size_t i = 0; i < v.size() && (int)i < cap; i++) out[i] = v[i];
+  return (int)v.size();
 }
 
 // ---------------------------------------------------------------- batch
@@ -515,7 +556,7 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   std::vector<DevModel> hm;
   for (int i = 0; i < n_models; i++) {
     gmr_model* m = models[i];
-    if (!m || m->device != b->device) { delete b; return fail(-1, "models must live on one device"); }
+    if (!m || m->device < 0 || m->device != b->device) { delete b; return fail(-1, "models must live on one device"); }
     b->models.push_back(m);
     hm.push_back(m->host);
     b->nq_max = std::max(b->nq_max, m->host.nq); b->s_max = std::max(b->s_max, m->host.n_scaled);
@@ -888,7 +929,7 @@ extern "C" int gmr_qp_solve(int device, void* stream, int n_qp, int n, const dou
 
 extern "C" int gmr_fk_bodies_f32(gmr_model* m, void* stream, int N, const float* root_pos_dev, const float* root_rot_xyzw_dev,
                                  const float* dof_pos_dev, float* body_pos_out_dev, float* body_rot_out_dev) {
-  if (!m || N < 1 || !root_pos_dev || !root_rot_xyzw_dev || !dof_pos_dev || !body_pos_out_dev) return fail(-1, "bad argument");
+  if (!m || m->device < 0 || N < 1 || !root_pos_dev || !root_rot_xyzw_dev || !dof_pos_dev || !body_pos_out_dev) return fail(-1, "bad argument");
   DevGuard g(m->device);
   float* scratch = nullptr;
   if (!body_rot_out_dev) CU(cudaMallocAsync(&scratch, sizeof(float) * (size_t)N * m->tail.nbody * 4, (cudaStream_t)stream));

@@ -105,8 +105,26 @@ typedef struct gmr_batch gmr_batch;
 const char* gmr_last_error(void);
 int gmr_abi_version(void);
 
+/* device = a CUDA device ordinal, or GMR_HOST_ONLY: the flattened tables stay in host memory and no CUDA call is
+ * made (such a model cannot back a batch; it exists so that the flattener can be tested without a GPU). */
+#define GMR_HOST_ONLY (-1)
 int gmr_model_create(const gmr_model_desc* desc, int device, gmr_model** out);
 int gmr_model_destroy(gmr_model* m);
+/* Static schedule of the fused kernel's box-QP solver for one stage (host-only models): copies table `which`
+ * into out[0..cap) and returns the number of int32 it holds.  Byte offsets in the tables are relative to a warp's
+ * block array / Ud / v / S arrays as laid out in csrc/gmr_device.cuh (DevModel.aba_*). */
+#define GMR_TABLE_INFO       0   /* nv, n_task, n_up_levels, n_down_levels, n_merge, root block offset (-1: none), first base dof,
+                                    kkt task mask, doubles of the block array, GMR_KS, GMR_XS, GMR_SS */
+#define GMR_TABLE_UPLEV      1   /* per level: pass range [begin, end) */
+#define GMR_TABLE_UP         2   /* per (pass, 8-lane group) 8 ints: dof (-1 idle), X, S, Ud offsets, task block (-1), children [b, e), 0 */
+#define GMR_TABLE_CHILD      3   /* per child: accumulator offset, Ud offset */
+#define GMR_TABLE_DNLEV      4
+#define GMR_TABLE_DN         5   /* per (pass, group) 4 ints: dof (-1 idle), v_parent offset (-1: none), v offset, S offset */
+#define GMR_TABLE_MERGE      6   /* pairs (dst task, src task) hanging on one dof */
+#define GMR_TABLE_TASK_DOF   7
+#define GMR_TABLE_DOF_PARENT 8
+#define GMR_TABLE_TASKMASK   9
+int gmr_model_table(const gmr_model* m, int which, int stage, int32_t* out, int cap);
 
 /* B independent IK instances (clip x robot).  n_models > 1 = heterogeneous launch;
  * model_of_instance (host, [B]) may be NULL when n_models == 1.  State starts at qpos0. */
