@@ -501,6 +501,7 @@ extern "C" int gmr_model_table(const gmr_model* m, int which, int stage, int32_t
     case GMR_TABLE_TASK_DOF: span(h.task_dof + stage * GMR_MAX_TASKS, (size_t)h.n_task[stage]); break;
     case GMR_TABLE_DOF_PARENT: span(h.dof_parent, (size_t)h.nv); break;
     case GMR_TABLE_TASKMASK: span(h.dof_taskmask + stage * h.nv, (size_t)h.nv); break;
+    case GMR_TABLE_FK_BODY: v.resize(h.n_fk); for (int i = 0; i < h.n_fk; i++) v[i] = h.fk_body[i]; break;
     default: return fail(-1, "unknown table");
   }
   if (out) for (size_t i = 0; i < v.size() && (int)i < cap; i++) out[i] = v[i];

@@ -124,6 +124,7 @@ int gmr_model_destroy(gmr_model* m);
 #define GMR_TABLE_TASK_DOF   7
 #define GMR_TABLE_DOF_PARENT 8
 #define GMR_TABLE_TASKMASK   9
+#define GMR_TABLE_FK_BODY   10   /* bodies the fused kernel's forward kinematics sweeps (world first) */
 int gmr_model_table(const gmr_model* m, int which, int stage, int32_t* out, int cap);
 
 /* B independent IK instances (clip x robot).  n_models > 1 = heterogeneous launch;

@@ -216,3 +216,24 @@ def test_host_only_model_cannot_back_a_batch():
     out = C.c_void_p()
     assert _lib.lib().gmr_batch_create(arr, 1, None, 4, None, C.byref(out)) != 0
     hm.close()
+
+
+@pytest.mark.parametrize("src,robot", PAIRS)
+def test_fk_sweeps_every_body_the_ik_reads(src, robot):
+    """DevModel.fk_body: the world, every body with joints, every task frame, closed under `parent`."""
+    from gmr_b200 import model_pack, synth
+    from gmr_b200.abi import ModelDesc
+    m, t = model_pack.build_tables(src, robot)
+    hm = HostModel(ModelDesc(m, t, synth.human_body_names(src, t)))
+    fk = list(hm.table(10, 0))
+    hm.close()
+    assert fk == sorted(set(fk)) and fk[0] == 0
+    need = {0} | {b for b in range(1, m.nbody) if m.body_jntnum[b] > 0}
+    for k in range(2):
+        if t.use_table[k]:
+            need |= {int(b) for b in t.task_body[k]}
+    for b in sorted(need, reverse=True):
+        while b > 0:
+            need.add(int(b))
+            b = int(m.body_parentid[b])
+    assert set(fk) == need
