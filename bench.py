@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--frames", type=int, default=300)
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the extra blocks (other configs, strong scaling, B=1 shim)")
     ap.add_argument("--e2e-chunks", type=int, default=0,
                     help="gmr_batch_run_host mode: 0 = zero-copy on the pinned host buffers, k >= 1 = k staged frame ranges")
     return ap.parse_args()

@@ -4,6 +4,7 @@ nvcc cross-compiles for sm_100a without a GPU; the .so travels to the GPU box wi
 """
 from __future__ import annotations
 
+import glob
 import os
 import subprocess
 import sys
@@ -11,8 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "gmr_abi.cu")
 OUT = os.path.join(HERE, "libgmr_b200.so")
-DEPS = [SRC] + [os.path.join(HERE, "csrc", f) for f in ("gmr_device.cuh", "gmr_stages.cuh", "gmr_clip.cuh")] + [
-    os.path.join(HERE, "..", "include", "gmr_b200.h")]
+DEPS = sorted(glob.glob(os.path.join(HERE, "csrc", "*"))) + [os.path.join(HERE, "..", "include", "gmr_b200.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]

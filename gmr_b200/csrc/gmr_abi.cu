@@ -615,10 +615,10 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
     b->clip_smem_bytes = b->smem_bytes + (b->smem_model ? blob : 0);
     if (b->clip_smem_bytes + stat > (size_t)dev_smem) e = cudaErrorInvalidConfiguration;
   }
+  // The dynamic shared-memory opt-in is a per-function, process-wide attribute: another batch (another robot, a
+  // narrower CTA) would lower it under this one, so launch_clips sets it again right before every launch.
   const void* kf = clip_kernel_ptr(GMR_F32, b->smem_model);
-  const void* kd = clip_kernel_ptr(GMR_F64, b->smem_model);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->clip_smem_bytes);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(kd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->clip_smem_bytes);
   int per_sm = 0;
   if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kf, 32 * b->warps_per_cta, b->clip_smem_bytes);
   if (e == cudaSuccess) {
@@ -748,7 +748,9 @@ static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const in
   CU(cudaMemsetAsync(b->d_counter, 0, sizeof(int), b->stream));
   const dim3 grid(b->grid), block(32 * b->warps_per_cta);
   void* kargs[] = {(void*)&a};
-  CU(cudaLaunchKernel(clip_kernel_ptr(dtype, b->smem_model), grid, block, kargs, b->clip_smem_bytes, b->stream));
+  const void* kern = clip_kernel_ptr(dtype, b->smem_model);
+  CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->clip_smem_bytes));
+  CU(cudaLaunchKernel(kern, grid, block, kargs, b->clip_smem_bytes, b->stream));
   CU(cudaGetLastError());
   return 0;
 }

@@ -135,6 +135,12 @@ class BatchedRetargeter:
         self.set_scale(sc)
 
     def set_order(self, order=None):
+        """Processing order of the work queue: a permutation of range(B) (longest clips first), or None."""
+        if order is not None:
+            o = torch.as_tensor(order).to("cpu", torch.int64).reshape(-1)
+            if o.numel() != self.B or not torch.equal(torch.sort(o).values, torch.arange(self.B)):
+                raise ValueError("order must be a permutation of range(B): a duplicate would make two warps race on one "
+                                 "clip and leave another one untouched")
         order = None if order is None else self._dev(order, torch.int32, (self.B,))
         _lib.check(_lib.lib().gmr_batch_set_order(self._h, _ptr(order)), "gmr_batch_set_order")
 
@@ -217,7 +223,12 @@ class BatchedRetargeter:
             self._h, C.c_void_p(human_host.data_ptr()), F32 if human_host.dtype == torch.float32 else F64,
             None if t_of is None else t_of.ctypes.data_as(C.c_void_p), T, int(bool(offset_to_ground)), int(bool(cold_start)),
             int(n_chunks), C.c_void_p(qpos_host.data_ptr())), "gmr_batch_run_host")
-        self._keep_host = (human_host, qpos_host)      # alive until the stream has consumed them
+        # the launch is asynchronous and torch's pinned-memory allocator does not know the kernel uses these blocks:
+        # every pair stays referenced until an event recorded behind its launch has completed
+        ev = torch.cuda.Event()
+        ev.record(self.stream)
+        self._inflight = [x for x in getattr(self, "_inflight", []) if not x[0].query()]
+        self._inflight.append((ev, human_host, qpos_host))
         return qpos_host
 
     def step(self, human, offset_to_ground=False, diag=False, want_scaled=False):
