@@ -8,7 +8,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-from .abi import gmr_diag, gmr_model_desc
+from .abi import ABI_VERSION, gmr_diag, gmr_model_desc
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GMR_B200_LIB") or os.path.join(HERE, "libgmr_b200.so")
@@ -18,7 +18,8 @@ EXPORTS = [
     "gmr_batch_destroy", "gmr_batch_reset", "gmr_batch_set_scale", "gmr_batch_get_state",
     "gmr_batch_set_order", "gmr_batch_launch_info", "gmr_batch_dims", "gmr_batch_step", "gmr_batch_run",
     "gmr_target_prep", "gmr_fk", "gmr_build_qp", "gmr_qp_solve", "gmr_fk_bodies_f32", "gmr_probe_fma_peak", "gmr_solve_ik", "gmr_batch_run_host",
-    "gmr_bvh_to_stream", "gmr_smplx_to_stream", "gmr_model_table",
+    "gmr_bvh_to_stream", "gmr_smplx_to_stream", "gmr_model_table", "gmr_batch_run_csr", "gmr_batch_run_host_csr",
+    "gmr_batch_step_host",
 ]
 
 _lib = None
@@ -58,6 +59,9 @@ def lib():
     L.gmr_fk.argtypes = [vp, vp, vp, vp]
     L.gmr_build_qp.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp, vp]
     L.gmr_batch_run_host.argtypes = [vp, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+    L.gmr_batch_run_csr.argtypes = [vp, vp, C.c_int, vp, C.c_int, C.c_int, vp, C.POINTER(gmr_diag)]
+    L.gmr_batch_run_host_csr.argtypes = [vp, vp, C.c_int, vp, C.c_int, C.c_int, vp, vp]
+    L.gmr_batch_step_host.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, C.c_int]
     L.gmr_solve_ik.argtypes = [vp, C.c_int, vp, vp, vp]
     L.gmr_qp_solve.argtypes = [C.c_int, vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]
     L.gmr_fk_bodies_f32.argtypes = [vp, vp, C.c_int, vp, vp, vp, vp, vp]
@@ -65,7 +69,7 @@ def lib():
     L.gmr_smplx_to_stream.argtypes = [C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp]
     L.gmr_bvh_to_stream.argtypes = [C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, C.POINTER(i32), vp, vp, C.c_int,
                                     C.c_int, vp, C.c_int, C.POINTER(i32), vp]
-    if L.gmr_abi_version() != 1:
+    if L.gmr_abi_version() != ABI_VERSION:
         raise EngineError("ABI version mismatch between gmr_b200/abi.py and libgmr_b200.so")
     _lib = L
     return L

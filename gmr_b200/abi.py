@@ -13,7 +13,7 @@ import numpy as np
 from .ik_config import RetargetTables
 from .mjcf import RobotModel
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 MAX_NV, MAX_NBODY, MAX_TASKS, MAX_SCALED = 64, 64, 32, 32
 F32, F64 = 0, 1
 
@@ -37,18 +37,26 @@ class gmr_model_desc(C.Structure):
         ("task_body", _pi * 2), ("task_src", _pi * 2), ("task_wpos", _pd * 2), ("task_wrot", _pd * 2),
         ("damping", C.c_double), ("max_iter", C.c_int32), ("converge_eps", C.c_double),
         ("limit_gain", C.c_double), ("lm_damping", C.c_double),
+        ("dof_vmax", _pd),
     ]
 
 
 class gmr_diag(C.Structure):
-    _fields_ = [("err_dev", C.c_void_p), ("iters_dev", C.c_void_p), ("nfact_dev", C.c_void_p)]
+    _fields_ = [("err_dev", C.c_void_p), ("iters_dev", C.c_void_p), ("nfact_dev", C.c_void_p), ("status_dev", C.c_void_p)]
+
+
+# gmr_diag.status_dev bits (include/gmr_b200.h)
+STATUS_MAX_ITER1, STATUS_MAX_ITER2, STATUS_QP_CAP, STATUS_BAD_INPUT, STATUS_BAD_OUTPUT = 1, 2, 4, 8, 16
+STATUS_FAILED = STATUS_QP_CAP | STATUS_BAD_INPUT | STATUS_BAD_OUTPUT      # what makes a driver skip a clip
 
 
 class ModelDesc:
     """Owns the numpy arrays a ``gmr_model_desc`` points to."""
 
     def __init__(self, model: RobotModel, tables: RetargetTables, human_names=None,
-                 damping: float = 0.5, max_iter: int = 10):
+                 damping: float = 0.5, max_iter: int = 10, dof_vmax=None):
+        """dof_vmax: optional velocity limit per dof in rad/s or m/s ([nv], +inf = none; a scalar applies to every
+        hinge/slide dof).  None = off, the reference's behaviour (motion_retarget.py:147-149 passes no limits)."""
         self.model, self.tables = model, tables
         if human_names is None:
             human_names = list(tables.scaled_names)
@@ -99,6 +107,17 @@ class ModelDesc:
             d.task_wrot[k] = ad(tables.task_wrot[k] if use else [0.0])
         d.damping, d.max_iter = float(damping), int(max_iter)
         d.converge_eps, d.limit_gain, d.lm_damping = 0.001, 0.95, 1.0
+        self.dof_vmax = None
+        if dof_vmax is not None:
+            vm = np.full(model.nv, np.inf)
+            if np.ndim(dof_vmax) == 0:
+                for j in range(model.njnt):
+                    if model.jnt_type[j] != 0:
+                        vm[model.jnt_dofadr[j]] = float(dof_vmax)
+            else:
+                vm[:] = np.asarray(dof_vmax, np.float64)
+            self.dof_vmax = vm
+            d.dof_vmax = ad(vm)
         self.c = d
 
     @property

@@ -54,6 +54,7 @@ struct gmr_batch {
   void* stage_in = nullptr; size_t stage_in_bytes = 0;
   void* stage_out = nullptr; size_t stage_out_bytes = 0;
   int* stage_T = nullptr;
+  int64_t* stage_cs = nullptr;   // clip_start of the CSR host call
   cudaStream_t s_in = nullptr, s_out = nullptr;
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
   bool smem_model = false;
@@ -229,8 +230,14 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
         if (((mk >> t) & 1u) && (tparent[t] < 0 || !((mk >> tparent[t]) & 1u))) topmask[k * nv + l] |= 1u << t;
     }
   }
-  // ---- static schedule of the articulated-body solver (qp_solve_aba), per stage
-  std::vector<int> aba_uplev, aba_dnlev, aba_p1, aba_ch, aba_dn;      // level tables: stage 0's levels, then stage 1's
+  // ---- static schedule of the articulated-body solver (qp_solve_aba), per stage.
+  // The scheduled dofs (those with a task below them) are cut into CHAINS: every dof continues into its tallest
+  // child, its other children are the tops of side chains.  A chain runs bottom-up on one 8-lane group with the
+  // accumulator X = [I | p] carried in REGISTERS from dof to dof; only a chain's top stores X in shared memory
+  // (for the dof that gathers it as a side child, or for the floating-base block).  A pass handles one dof per
+  // group; a chain idles (registers kept) while a side chain it gathers is still running.  The downward sweep
+  // uses the same chains top-down with the link velocity v carried in registers.
+  std::vector<int> aba_up, aba_ch, aba_dn;            // passes of stage 0, then of stage 1
   int aba_up0[2] = {0, 0}, aba_dn0[2] = {0, 0};
   std::vector<int> aba_merge(2 * MT * 2, 0), task_dof(2 * MT, -1);
   int aba_nup[2] = {0, 0}, aba_ndn[2] = {0, 0}, aba_nmerge[2] = {0, 0}, aba_root[2] = {-1, -1}, aba_rootdof[2] = {0, 0}, aba_doubles = GMR_KS;
@@ -246,16 +253,8 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       if (own[a] < 0) { own[a] = t; aba_kktmask[k] |= 1u << t; }
       else { aba_merge[2 * (k * MT + aba_nmerge[k])] = own[a]; aba_merge[2 * (k * MT + aba_nmerge[k]) + 1] = t; aba_nmerge[k]++; }
     }
-    // dofs with a task in their subtree, their heights among themselves, depths
     std::vector<char> in(nv, 0);
     for (int i = 0; i < nv; i++) in[i] = taskmask[k * nv + i] != 0;
-    std::vector<int> hgt(nv, 0), nchild(nv, 0);
-    int hmax = -1;
-    for (int i = nv - 1; i >= 0; i--) {
-      if (!in[i]) continue;
-      hmax = std::max(hmax, hgt[i]);
-      if (dof_parent[i] >= 0) { hgt[dof_parent[i]] = std::max(hgt[dof_parent[i]], hgt[i] + 1); nchild[dof_parent[i]]++; }
-    }
     // floating base (six unlimited dofs at the top of the tree): solved as one block by the kernel, so dofs
     // fb .. fb+4 leave the upward schedule (fb+5, the base link, still gathers its X) and all six the downward one
     int fb = -1;
@@ -263,72 +262,120 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
       if (dof_kind[i] == DOF_FREE_T && dof_parent[i] < 0 && in[i + 5]) fb = i;
     auto skip_up = [&](int i) { return fb >= 0 && i >= fb && i < fb + 5; };
     auto skip_dn = [&](int i) { return fb >= 0 && i >= fb && i <= fb + 5; };
-    // accumulators behind the task blocks: one per chain (a dof writes its X over its first child's, row by row)
-    const int accbase = (m_k * GMR_KS * 8 + 15) & ~15;
-    std::vector<int> acc(nv, -1);
+    std::vector<int> hgt(nv, 0);
     std::vector<std::vector<int>> kids(nv);
-    for (int i = 0; i < nv; i++) if (in[i] && dof_parent[i] >= 0) kids[dof_parent[i]].push_back(i);
-    int nacc = 0;
-    aba_up0[k] = (int)aba_uplev.size() / 2;
-    for (int hh = 0; hh <= hmax; hh++) {
-      std::vector<int> todo;
-      for (int i = nv - 1; i >= 0; i--) if (in[i] && hgt[i] == hh && !skip_up(i)) todo.push_back(i);
-      if (todo.empty()) continue;
-      aba_uplev.resize(aba_uplev.size() + 2, 0);
-      int* L = &aba_uplev[aba_uplev.size() - 2];
-      aba_nup[k]++;
-      L[0] = (int)aba_p1.size() / 32;
-      for (size_t pos = 0; pos < todo.size(); pos += 4)
-        for (int g = 0; g < 4; g++) {
-          const bool have = pos + g < todo.size();
-          const int c = have ? todo[pos + g] : 0;
-          int cb = (int)aba_ch.size() / 2, ce = cb;
-          if (have) {
-            acc[c] = kids[c].empty() ? nacc++ : acc[kids[c][0]];
-            for (int kid : kids[c]) { aba_ch.push_back(accbase + acc[kid] * GMR_XS * 8); aba_ch.push_back(kid * 64); }
-            ce = (int)aba_ch.size() / 2;
-          }
-          aba_p1.push_back(have ? c : -1);
-          aba_p1.push_back(have ? accbase + acc[c] * GMR_XS * 8 : 0);
-          aba_p1.push_back(c * GMR_SS * 8);
-          aba_p1.push_back(c * 64);
-          aba_p1.push_back(have && own[c] >= 0 ? own[c] * GMR_KS * 8 : -1);
-          aba_p1.push_back(cb); aba_p1.push_back(ce); aba_p1.push_back(0);
-        }
-      L[1] = (int)aba_p1.size() / 32;
+    for (int i = nv - 1; i >= 0; i--) {
+      if (!in[i] || skip_up(i)) continue;
+      const int pr = dof_parent[i];
+      if (pr >= 0 && !skip_up(pr)) { hgt[pr] = std::max(hgt[pr], hgt[i] + 1); kids[pr].push_back(i); }
     }
-    aba_root[k] = fb >= 0 ? accbase + acc[fb + 5] * GMR_XS * 8 : -1;
+    for (int i = 0; i < nv; i++) std::sort(kids[i].begin(), kids[i].end());
+    // chains: cont[c] = the child c continues into (tallest, lowest index on ties)
+    std::vector<int> cont(nv, -1), chain_of(nv, -1);
+    for (int i = 0; i < nv; i++)
+      for (int c : kids[i]) if (cont[i] < 0 || hgt[c] > hgt[cont[i]]) cont[i] = c;
+    std::vector<std::vector<int>> chains;               // bottom -> top
+    for (int i = nv - 1; i >= 0; i--) {
+      if (!in[i] || skip_up(i) || cont[i] >= 0) continue;     // chain bottoms = scheduled dofs without children
+      std::vector<int> ch{i};
+      for (int c = i;;) {
+        const int pr = dof_parent[c];
+        if (pr < 0 || skip_up(pr) || cont[pr] != c) break;
+        ch.push_back(pr); c = pr;
+      }
+      for (int c : ch) chain_of[c] = (int)chains.size();
+      chains.push_back(ch);
+    }
+    const int nchain = (int)chains.size();
+    // accumulators behind the task blocks: one per chain (its top's X)
+    const int accbase = (m_k * GMR_KS * 8 + 15) & ~15;
+    auto accoff = [&](int chain) { return accbase + chain * GMR_XS * 8; };
+    aba_doubles = std::max(aba_doubles, accbase / 8 + nchain * GMR_XS);
+    aba_root[k] = fb >= 0 ? accoff(chain_of[fb + 5]) : -1;
     aba_rootdof[k] = std::max(fb, 0);
-    aba_doubles = std::max(aba_doubles, accbase / 8 + nacc * GMR_XS);
-    // downward levels by depth among the scheduled dofs
-    std::vector<int> dep(nv, 0);
-    int dmax = -1;
-    for (int i = 0; i < nv; i++) {
-      if (!in[i]) continue;
-      dep[i] = dof_parent[i] < 0 ? 0 : dep[dof_parent[i]] + 1;
-      dmax = std::max(dmax, dep[i]);
-    }
-    aba_dn0[k] = (int)aba_dnlev.size() / 2;
-    for (int dd = 0; dd <= dmax; dd++) {
-      std::vector<int> todo;
-      for (int i = 0; i < nv; i++) if (in[i] && dep[i] == dd && !skip_dn(i)) todo.push_back(i);
-      if (todo.empty()) continue;
-      aba_dnlev.resize(aba_dnlev.size() + 2, 0);
-      int* L = &aba_dnlev[aba_dnlev.size() - 2];
-      aba_ndn[k]++;
-      L[0] = (int)aba_dn.size() / 16;
-      for (size_t pos = 0; pos < todo.size(); pos += 4)
+    // ---- upward passes: chains start in order of their top's height (what a chain gathers always tops out lower)
+    {
+      std::vector<int> order(nchain);
+      for (int c = 0; c < nchain; c++) order[c] = c;
+      std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return hgt[chains[a].back()] < hgt[chains[b].back()]; });
+      std::vector<int> done(nv, -1);
+      int next = 0, finished = 0, cur[4] = {-1, -1, -1, -1}, pos[4] = {0, 0, 0, 0};
+      aba_up0[k] = (int)aba_up.size() / 32;
+      for (int t = 0; finished < nchain; t++) {
+        if (t > 4 * nv + 8) return fail(-4, "internal: upward schedule does not terminate");
+        for (int g = 0; g < 4; g++) if (cur[g] < 0 && next < nchain) { cur[g] = order[next++]; pos[g] = 0; }
         for (int g = 0; g < 4; g++) {
-          const bool have = pos + g < todo.size();
-          const int c = have ? todo[pos + g] : 0, pr = have ? dof_parent[c] : -1;
-          aba_dn.push_back(have ? c : -1);
-          aba_dn.push_back(pr >= 0 ? pr * 48 : -1);
-          aba_dn.push_back(c * 48);
-          aba_dn.push_back(c * GMR_SS * 8);
+          int c = -1;
+          if (cur[g] >= 0) {
+            c = chains[cur[g]][pos[g]];
+            bool ready = true;                            // every side chain it gathers finished in an earlier pass
+            for (int kid : kids[c]) if (kid != cont[c] && !(done[kid] >= 0 && done[kid] < t)) ready = false;
+            if (!ready) c = -1;
+          }
+          if (c < 0) { for (int z = 0; z < 8; z++) aba_up.push_back(z == 0 ? -1 : 0); continue; }
+          const bool top = pos[g] + 1 == (int)chains[cur[g]].size();
+          const int cb = (int)aba_ch.size() / 2;
+          for (int kid : kids[c]) if (kid != cont[c]) { aba_ch.push_back(accoff(chain_of[kid])); aba_ch.push_back(kid * 64); }
+          const int flags = (pos[g] > 0 ? 1 : 0) | (top ? 2 : 0) | ((pos[g] > 0 ? cont[c] : 0) << 8);
+          aba_up.push_back(c); aba_up.push_back(flags); aba_up.push_back(c * GMR_SS * 8); aba_up.push_back(c * 64);
+          aba_up.push_back(own[c] >= 0 ? own[c] * GMR_KS * 8 : -1);
+          aba_up.push_back(cb); aba_up.push_back((int)aba_ch.size() / 2); aba_up.push_back(accoff(cur[g]));
+          done[c] = t;
+          if (top) { cur[g] = -1; finished++; } else pos[g]++;
         }
-      L[1] = (int)aba_dn.size() / 16;
+        aba_nup[k]++;
+      }
+    }
+    // ---- downward passes: the same chains top-down; a chain starts once its top's parent has stored its velocity
+    {
+      std::vector<std::vector<int>> dch;                 // chains without the dofs of the floating-base block
+      for (auto& ch : chains) {
+        std::vector<int> r;
+        for (int i = (int)ch.size() - 1; i >= 0; i--) if (!skip_dn(ch[i])) r.push_back(ch[i]);
+        if (!r.empty()) dch.push_back(r);
+      }
+      const int nd = (int)dch.size();
+      std::vector<int> dep(nv, 0);
+      for (int i = 0; i < nv; i++) if (in[i]) dep[i] = dof_parent[i] < 0 ? 0 : dep[dof_parent[i]] + 1;
+      std::vector<int> order(nd);
+      for (int c = 0; c < nd; c++) order[c] = c;
+      std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return dep[dch[a][0]] < dep[dch[b][0]]; });
+      // v is stored for dofs another chain starts from and for dofs that carry a task (the KKT check reads it)
+      std::vector<char> store(nv, 0);
+      for (auto& ch : dch) { const int pr = dof_parent[ch[0]]; if (pr >= 0) store[pr] = 1; }
+      for (int i = 0; i < nv; i++) if (own[i] >= 0) store[i] = 1;
+      std::vector<int> done(nv, -1);
+      int next = 0, finished = 0, cur[4] = {-1, -1, -1, -1}, pos[4] = {0, 0, 0, 0};
+      aba_dn0[k] = (int)aba_dn.size() / 16;
+      for (int t = 0; finished < nd; t++) {
+        if (t > 4 * nv + 8) return fail(-4, "internal: downward schedule does not terminate");
+        for (int g = 0; g < 4; g++) if (cur[g] < 0 && next < nd) { cur[g] = order[next++]; pos[g] = 0; }
+        for (int g = 0; g < 4; g++) {
+          int c = -1;
+          if (cur[g] >= 0) {
+            c = dch[cur[g]][pos[g]];
+            const int pr = dof_parent[c];
+            if (pos[g] == 0 && pr >= 0 && !skip_dn(pr) && !(done[pr] >= 0 && done[pr] < t)) c = -1;   // parent's v not stored yet
+          }
+          if (c < 0) { aba_dn.push_back(-1); aba_dn.push_back(0); aba_dn.push_back(-1); aba_dn.push_back(0); continue; }
+          const int pr = dof_parent[c];
+          aba_dn.push_back(c); aba_dn.push_back((pos[g] > 0 ? 1 : 0) | (store[c] ? 2 : 0));
+          aba_dn.push_back(pr >= 0 ? pr * 48 : -1); aba_dn.push_back(0);
+          done[c] = t;
+          if (pos[g] + 1 == (int)dch[cur[g]].size()) { cur[g] = -1; finished++; } else pos[g]++;
+        }
+        aba_ndn[k]++;
+      }
     }
   }
+  std::vector<double> dof_vmax(nv, INFINITY);
+  if (d->dof_vmax)
+    for (int i = 0; i < nv; i++) {
+      dof_vmax[i] = d->dof_vmax[i];
+      if (!(dof_vmax[i] >= 0)) return fail(-5, "dof_vmax must be >= 0 (+inf: unlimited)");
+      if ((dof_kind[i] == DOF_FREE_T || dof_kind[i] == DOF_FREE_R) && std::isfinite(dof_vmax[i]))
+        return fail(-5, "dof_vmax of a free joint's dofs must be +inf (the floating base is solved as an unconstrained block)");
+    }
   for (int i = 0; i < d->n_scaled; i++)
     if (d->scaled_human_index[i] < 0 || d->scaled_human_index[i] >= d->n_human) return fail(-5, "scaled_human_index out of range");
 
@@ -357,9 +404,8 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
          o_sc = bl.push(vec(d->scale, d->n_scaled)), o_po = bl.push(vec(d->pos_off, 3 * d->n_scaled)),
          o_ro = bl.push(vec(d->rot_off, 4 * d->n_scaled)), o_ft = bl.push(vec(d->is_foot, d->n_scaled)),
          o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot),
-         o_fj = bl.push(fk_jump), o_fb = bl.push(fk_body), o_aul = bl.push(aba_uplev), o_adl = bl.push(aba_dnlev),
-         o_ap1 = bl.push(aba_p1), o_ach = bl.push(aba_ch), o_adn = bl.push(aba_dn), o_amg = bl.push(aba_merge),
-         o_atd = bl.push(task_dof);
+         o_fj = bl.push(fk_jump), o_fb = bl.push(fk_body), o_ap1 = bl.push(aba_up), o_ach = bl.push(aba_ch), o_adn = bl.push(aba_dn), o_amg = bl.push(aba_merge),
+         o_atd = bl.push(task_dof), o_vm = bl.push(dof_vmax);
   const size_t staged_bytes = (bl.bytes.size() + 15) & ~size_t(15);
   // tables only the stage kernels read (gmr_build_qp: the assembly of H), from global memory
   size_t o_lstart = bl.push(level_start), o_lbody = bl.push(level_body), o_dp = bl.push(dof_parent),
@@ -430,6 +476,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.jnt_axis = (const double*)(B0 + o_jaxis); h.qpos0 = (const double*)(B0 + o_q0);
   h.dof_kind = (const int*)(B0 + o_dk); h.dof_qadr = (const int*)(B0 + o_dq); h.dof_parent = (const int*)(B0 + o_dp);
   h.dof_body = (const int*)(B0 + o_db); h.blob = B0; h.blob_bytes = (int)staged_bytes;
+  h.has_vmax = d->dof_vmax ? 1 : 0; h.dof_vmax = (const double*)(B0 + o_vm);
   h.dof_limited = (const int*)(B0 + o_dl); h.dof_lo = (const double*)(B0 + o_dlo); h.dof_hi = (const double*)(B0 + o_dhi);
   h.dof_taskmask = (const unsigned*)(B0 + o_tm); h.scaled_index = (const int*)(B0 + o_si);
   h.scale = (const double*)(B0 + o_sc); h.pos_off = (const double*)(B0 + o_po); h.rot_off = (const double*)(B0 + o_ro);
@@ -446,7 +493,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
     h.aba_kktmask[k] = aba_kktmask[k]; h.aba_up0[k] = aba_up0[k]; h.aba_dn0[k] = aba_dn0[k];
   }
   h.aba_doubles = aba_doubles;
-  h.aba_uplev = (const int2*)(B0 + o_aul); h.aba_dnlev = (const int2*)(B0 + o_adl); h.aba_p1 = (const int4*)(B0 + o_ap1);
+  h.aba_up = (const int4*)(B0 + o_ap1);
   h.aba_ch = (const int2*)(B0 + o_ach); h.aba_dn = (const int4*)(B0 + o_adn); h.aba_merge = (const int2*)(B0 + o_amg);
   h.task_dof = (const int*)(B0 + o_atd);
   h.fk_rounds = fk_rounds; h.fk_jump = (const short*)(B0 + o_fj);
@@ -483,20 +530,17 @@ extern "C" int gmr_model_table(const gmr_model* m, int which, int stage, int32_t
   const DevModel& h = m->host;
   std::vector<int32_t> v;
   auto span = [&](const void* p, size_t n) { const int32_t* q = (const int32_t*)p; v.assign(q, q + n); };
-  int p1_end = 0, dn_end = 0, ch_end = 0;
-  for (int lv = 0; lv < h.aba_nup[stage]; lv++) p1_end = std::max(p1_end, h.aba_uplev[h.aba_up0[stage] + lv].y);
-  for (int lv = 0; lv < h.aba_ndn[stage]; lv++) dn_end = std::max(dn_end, h.aba_dnlev[h.aba_dn0[stage] + lv].y);
-  for (int i = 0; i < p1_end * 4; i++) ch_end = std::max(ch_end, h.aba_p1[2 * i + 1].z);
+  const int up_end = h.aba_up0[stage] + h.aba_nup[stage];
+  int ch_end = 0;
+  for (int i = 0; i < up_end * 4; i++) ch_end = std::max(ch_end, h.aba_up[2 * i + 1].z);
   switch (which) {
     case GMR_TABLE_INFO:
       v = {h.nv, h.n_task[stage], h.aba_nup[stage], h.aba_ndn[stage], h.aba_nmerge[stage], h.aba_root[stage],
            h.aba_rootdof[stage], (int32_t)h.aba_kktmask[stage], h.aba_doubles, GMR_KS, GMR_XS, GMR_SS};
       break;
-    case GMR_TABLE_UPLEV: span(h.aba_uplev + h.aba_up0[stage], 2 * (size_t)h.aba_nup[stage]); break;
-    case GMR_TABLE_UP: span(h.aba_p1, 32 * (size_t)p1_end); break;          // pass indices are global: from pass 0
-    case GMR_TABLE_CHILD: span(h.aba_ch, 2 * (size_t)ch_end); break;
-    case GMR_TABLE_DNLEV: span(h.aba_dnlev + h.aba_dn0[stage], 2 * (size_t)h.aba_ndn[stage]); break;
-    case GMR_TABLE_DN: span(h.aba_dn, 16 * (size_t)dn_end); break;
+    case GMR_TABLE_UP: span(h.aba_up + 8 * (size_t)h.aba_up0[stage], 32 * (size_t)h.aba_nup[stage]); break;
+    case GMR_TABLE_CHILD: span(h.aba_ch, 2 * (size_t)ch_end); break;          // child indices are global: from child 0
+    case GMR_TABLE_DN: span(h.aba_dn + 4 * (size_t)h.aba_dn0[stage], 16 * (size_t)h.aba_ndn[stage]); break;
     case GMR_TABLE_MERGE: span(h.aba_merge + stage * GMR_MAX_TASKS, 2 * (size_t)h.aba_nmerge[stage]); break;
     case GMR_TABLE_TASK_DOF: span(h.task_dof + stage * GMR_MAX_TASKS, (size_t)h.n_task[stage]); break;
     case GMR_TABLE_DOF_PARENT: span(h.dof_parent, (size_t)h.nv); break;
@@ -647,7 +691,7 @@ extern "C" int gmr_batch_destroy(gmr_batch* b) {
   cudaSetDevice(b->device);
   cudaFree(b->d_models); cudaFree(b->d_q); cudaFree(b->d_scale); cudaFree(b->d_counter); cudaFree(b->d_done);
   cudaFree(b->d_model_of); cudaFree(b->d_order);
-  cudaFree(b->stage_in); cudaFree(b->stage_out); cudaFree(b->stage_T);
+  cudaFree(b->stage_in); cudaFree(b->stage_out); cudaFree(b->stage_T); cudaFree(b->stage_cs);
   if (b->s_in) { cudaStreamDestroy(b->s_in); cudaStreamDestroy(b->s_out); for (int i = 0; i < 3; i++) cudaEventDestroy(b->ev[i]); }
   cudaSetDevice(prev);
   delete b;
@@ -726,19 +770,22 @@ extern "C" int gmr_batch_launch_info(const gmr_batch* b, int32_t* grid, int32_t*
 }
 
 static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const int32_t* T_of_dev, int T_max, int to_ground,
-                        double* qpos_out, double* scaled_out, const gmr_diag* diag, int t_begin = 0, int t_end = -1) {
+                        double* qpos_out, double* scaled_out, const gmr_diag* diag, int t_begin = 0, int t_end = -1,
+                        const int64_t* clip_start_dev = nullptr, int32_t* status_out = nullptr) {
   if (!b || !human_dev) return fail(-1, "null argument");
   if (dtype != GMR_F32 && dtype != GMR_F64) return fail(-1, "human_dtype must be GMR_F32 or GMR_F64");
   if (T_max < 1) return fail(-1, "T_max must be >= 1");
   DevGuard g(b->device);
   RunArgs a{};
   a.models = b->d_models; a.model_of = b->d_model_of;
-  a.human = human_dev; a.human_frame_stride = (long long)b->h_max * 7; a.human_inst_stride = a.human_frame_stride * T_max;
+  a.human = human_dev; a.human_frame_stride = (long long)b->h_max * 7;
+  a.clip_start = (const long long*)clip_start_dev;
   a.T_of = T_of_dev; a.T_max = T_max; a.to_ground = to_ground;
   a.t_begin = t_begin; a.t_end = t_end < 0 ? T_max : std::min(t_end, T_max);
   a.scale = b->d_scale; a.s_max = b->s_max; a.q_state = b->d_q; a.nq_max = b->nq_max;
   a.qpos_out = qpos_out; a.scaled_out = scaled_out;
   a.err_out = diag ? diag->err_dev : nullptr; a.iters_out = diag ? diag->iters_dev : nullptr; a.nfact_out = diag ? diag->nfact_dev : nullptr;
+  a.status_out = diag && diag->status_dev ? diag->status_dev : status_out;
   a.counter = b->d_counter; a.order = b->d_order; a.B = b->B; a.lay = b->lay;
   a.unit_frames = 32;
   if (const char* ev = getenv("GMR_DEBUG_UNIT_FRAMES")) a.unit_frames = std::max(1, atoi(ev));
@@ -763,6 +810,85 @@ extern "C" int gmr_batch_step(gmr_batch* b, const void* human_dev, int human_dty
 extern "C" int gmr_batch_run(gmr_batch* b, const void* human_dev, int human_dtype, const int32_t* T_of_instance_dev,
                              int T_max, int offset_to_ground, double* qpos_out_dev, const gmr_diag* diag) {
   return launch_clips(b, human_dev, human_dtype, T_of_instance_dev, T_max, offset_to_ground, qpos_out_dev, nullptr, diag);
+}
+
+extern "C" int gmr_batch_run_csr(gmr_batch* b, const void* human_dev, int human_dtype, const int64_t* clip_start_dev,
+                                 int T_max, int offset_to_ground, double* qpos_out_dev, const gmr_diag* diag) {
+  if (!clip_start_dev) return fail(-1, "null clip_start");
+  return launch_clips(b, human_dev, human_dtype, nullptr, T_max, offset_to_ground, qpos_out_dev, nullptr, diag, 0, -1, clip_start_dev);
+}
+
+namespace {
+// device pointer of a page-locked host buffer (null if the memory is not page-locked)
+void* mapped_ptr(const void* host) {
+  cudaPointerAttributes at{};
+  if (cudaPointerGetAttributes(&at, host) != cudaSuccess || at.type != cudaMemoryTypeHost || !at.devicePointer) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return at.devicePointer;
+}
+}  // namespace
+
+extern "C" int gmr_batch_step_host(gmr_batch* b, const void* human_host, int human_dtype, int offset_to_ground,
+                                   double* qpos_out_host, double* scaled_out_host, int sync) {
+  if (!b || !human_host || !qpos_out_host) return fail(-1, "null argument");
+  DevGuard g(b->device);
+  void* hi = mapped_ptr(human_host);
+  void* qo = mapped_ptr(qpos_out_host);
+  void* so = scaled_out_host ? mapped_ptr(scaled_out_host) : nullptr;
+  if (!hi || !qo || (scaled_out_host && !so)) return fail(-6, "gmr_batch_step_host needs page-locked host buffers");
+  int rc = launch_clips(b, hi, human_dtype, nullptr, 1, offset_to_ground, (double*)qo, (double*)so, nullptr);
+  if (rc) return rc;
+  if (sync) CU(cudaStreamSynchronize(b->stream));
+  return 0;
+}
+
+extern "C" int gmr_batch_run_host_csr(gmr_batch* b, const void* human_host, int human_dtype, const int64_t* clip_start_host,
+                                      int offset_to_ground, int cold_start, double* qpos_out_host, int32_t* status_out_host) {
+  if (!b || !human_host || !qpos_out_host || !clip_start_host) return fail(-1, "null argument");
+  if (human_dtype != GMR_F32 && human_dtype != GMR_F64) return fail(-1, "human_dtype must be GMR_F32 or GMR_F64");
+  DevGuard g(b->device);
+  int T_max = 0;
+  for (int i = 0; i < b->B; i++) {
+    const int64_t len = clip_start_host[i + 1] - clip_start_host[i];
+    if (len < 0 || len > INT32_MAX) return fail(-1, "clip_start must be non-decreasing");
+    T_max = std::max(T_max, (int)len);
+  }
+  const int64_t N = clip_start_host[b->B] - clip_start_host[0];
+  if (clip_start_host[0] != 0) return fail(-1, "clip_start[0] must be 0");
+  if (N == 0) return 0;
+  if (!b->stage_cs) CU(cudaMalloc(&b->stage_cs, sizeof(int64_t) * ((size_t)b->B + 1)));
+  CU(cudaMemcpyAsync(b->stage_cs, clip_start_host, sizeof(int64_t) * ((size_t)b->B + 1), cudaMemcpyHostToDevice, b->stream));
+  if (cold_start) { int rc = gmr_batch_reset(b, nullptr); if (rc) return rc; }
+  void* hi = mapped_ptr(human_host);
+  void* qo = mapped_ptr(qpos_out_host);
+  void* so = status_out_host ? mapped_ptr(status_out_host) : nullptr;
+  if (hi && qo && (!status_out_host || so))       // zero-copy: the warps read / write the page-locked buffers over the bus
+    return launch_clips(b, hi, human_dtype, nullptr, T_max, offset_to_ground, (double*)qo, nullptr, nullptr, 0, -1, b->stage_cs, (int32_t*)so);
+  // pageable memory: one copy in, the launch, one copy out through device staging
+  const size_t esz = human_dtype == GMR_F32 ? 4 : 8;
+  const size_t in_bytes = (size_t)N * b->h_max * 7 * esz, out_bytes = (size_t)N * b->nq_max * sizeof(double) + (size_t)N * sizeof(int32_t);
+  if (b->stage_in_bytes < in_bytes) {
+    if (b->stage_in) cudaFree(b->stage_in);
+    b->stage_in = nullptr; b->stage_in_bytes = 0;
+    CU(cudaMalloc(&b->stage_in, in_bytes));
+    b->stage_in_bytes = in_bytes;
+  }
+  if (b->stage_out_bytes < out_bytes) {
+    if (b->stage_out) cudaFree(b->stage_out);
+    b->stage_out = nullptr; b->stage_out_bytes = 0;
+    CU(cudaMalloc(&b->stage_out, out_bytes));
+    b->stage_out_bytes = out_bytes;
+  }
+  int32_t* st_dev = (int32_t*)((char*)b->stage_out + (size_t)N * b->nq_max * sizeof(double));
+  CU(cudaMemcpyAsync(b->stage_in, human_host, in_bytes, cudaMemcpyHostToDevice, b->stream));
+  int rc = launch_clips(b, b->stage_in, human_dtype, nullptr, T_max, offset_to_ground, (double*)b->stage_out, nullptr, nullptr, 0, -1,
+                        b->stage_cs, status_out_host ? st_dev : nullptr);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(qpos_out_host, b->stage_out, (size_t)N * b->nq_max * sizeof(double), cudaMemcpyDeviceToHost, b->stream));
+  if (status_out_host) CU(cudaMemcpyAsync(status_out_host, st_dev, (size_t)N * sizeof(int32_t), cudaMemcpyDeviceToHost, b->stream));
+  return 0;
 }
 
 // Host-buffer form of gmr_batch_run: the dataset drivers' loop (scripts/bvh_to_robot_dataset.py:96-113)

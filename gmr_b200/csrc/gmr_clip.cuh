@@ -12,6 +12,13 @@
 
 namespace gmr {
 
+// per-frame status bits (include/gmr_b200.h: GMR_STATUS_*)
+#define GMR_STATUS_MAX_ITER1 1
+#define GMR_STATUS_MAX_ITER2 2
+#define GMR_STATUS_QP_CAP 4
+#define GMR_STATUS_BAD_INPUT 8
+#define GMR_STATUS_BAD_OUTPUT 16
+
 // One CTA of up to 16 warps per SM, 128 registers per thread.  (Registers are allocated to a CTA in groups of
 // four warps, so the next step up is 20 warps at 96 registers: measured 17 % slower on the bench workload.)
 #define GMR_CTA_THREADS 512
@@ -19,11 +26,11 @@ namespace gmr {
 struct RunArgs {
   const DevModel* models;        // [n_models]
   const int* model_of;           // [B] or null (all 0)
-  const void* human;             // [B, T_max, h_max, 7]
-  long long human_inst_stride;   // elements between instances
-  long long human_frame_stride;  // elements between frames
-  const int* T_of;               // [B] or null
-  int T_max;
+  const void* human;             // dense [B, T_max, h_max, 7], or CSR [N, h_max, 7] (clip_start != null)
+  long long human_frame_stride;  // elements between frames (rows)
+  const long long* clip_start;   // CSR layout: [B+1] first row of every clip (null: dense, clip i starts at row i * T_max)
+  const int* T_of;               // dense layout: [B] clip lengths or null (= T_max)
+  int T_max;                     // dense: frames per clip slot; CSR: the longest clip
   int t_begin, t_end;            // frames [t_begin, min(T, t_end)) of every clip are processed by this launch
   int to_ground;
   const double* scale;           // [B, s_max]
@@ -35,6 +42,7 @@ struct RunArgs {
   double* err_out;               // [B, T_max, 2] or null
   int* iters_out;                // [B, T_max, 2] or null
   int* nfact_out;                // [B, T_max] or null
+  int* status_out;               // [B, T_max] or null: GMR_STATUS_* bits of every frame
   int* counter;                  // work queue head
   const int* order;              // [B] or null
   int B;
@@ -50,6 +58,8 @@ struct Slot {
   int t, T;                      // current frame, clip length
   int stage, it;                 // stage being solved, loop counter of motion_retarget.py:152/171
   int nfact;                     // sweeps of the box QP in this frame (1 per solve_ik + 1 per change of the active set)
+  int flags;                     // GMR_STATUS_* bits of the frame
+  long long row0;                // row of the clip's frame 0 in the stream / the outputs
   bool new_frame, fresh, need_fk;
   double curr;                   // curr_error of the reference loop
   unsigned long long act_lo, act_hi;   // active set of the previous solve of this frame/stage
@@ -93,7 +103,7 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
   }
   __syncthreads();
   Slot s;
-  s.inst = -1; s.t = s.T = 0; s.stage = 2; s.it = 0; s.nfact = 0; s.curr = 0; s.act_lo = s.act_hi = 0;
+  s.inst = -1; s.t = s.T = 0; s.stage = 2; s.it = 0; s.nfact = 0; s.flags = 0; s.row0 = 0; s.curr = 0; s.act_lo = s.act_hi = 0;
   s.new_frame = s.fresh = s.need_fk = false;
   int range = 0;
   const int n_units = a.n_ranges * a.B;
@@ -112,7 +122,9 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
       range = slot / a.B;
       const int c = slot - range * a.B;
       const int inst = a.order ? a.order[c] : c;
-      const int T_inst = min(a.T_of ? min(a.T_of[inst], a.T_max) : a.T_max, a.t_end);
+      const long long r0 = a.clip_start ? a.clip_start[inst] : (long long)inst * a.T_max;
+      const int T_len = a.clip_start ? (int)(a.clip_start[inst + 1] - r0) : (a.T_of ? min(a.T_of[inst], a.T_max) : a.T_max);
+      const int T_inst = min(T_len, a.t_end);
       const int t0 = a.t_begin + range * a.unit_frames;
       if (t0 >= T_inst) continue;                      // the clip ended before this range
       if (!SM) mv.m = a.models + (a.model_of ? a.model_of[inst] : 0);
@@ -121,7 +133,7 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
         __syncwarp();
         __threadfence();
       }
-      s.inst = inst; s.t = t0; s.T = min(T_inst, t0 + a.unit_frames);
+      s.inst = inst; s.t = t0; s.T = min(T_inst, t0 + a.unit_frames); s.row0 = r0;
       const double* qs = a.q_state + (size_t)inst * a.nq_max;
       for (int i = lane; i < mv.M().nq; i += 32) sm[lay.q + i] = __ldcg(qs + i);     // written by another SM: bypass L1
       __syncwarp();
@@ -133,10 +145,11 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
     // ---- Kernel 4: control
     bool solve = false;
     for (;;) {
-      const size_t o = (size_t)s.inst * a.T_max + s.t;
+      const size_t o = (size_t)(s.row0 + s.t);
       if (s.new_frame) {      // Kernel 1 on frame t
-        const TIn* human = (const TIn*)a.human + (size_t)s.inst * a.human_inst_stride + (size_t)s.t * a.human_frame_stride;
-        stage_prep<TIn>(mv, lay, sm, human, a.scale + (size_t)s.inst * a.s_max, a.to_ground != 0, lane);
+        const TIn* human = (const TIn*)a.human + o * a.human_frame_stride;
+        const bool finite = stage_prep<TIn>(mv, lay, sm, human, a.scale + (size_t)s.inst * a.s_max, a.to_ground != 0, lane);
+        s.flags = finite ? 0 : GMR_STATUS_BAD_INPUT;
         if (a.scaled_out) {
           double* so = a.scaled_out + o * a.s_max * 7;
           for (int i = lane; i < M.n_scaled * 7; i += 32) so[i] = sm[lay.scaled + i];
@@ -155,7 +168,10 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
       if (s.stage < 2) {
         const double err = stage_errors(mv, lay, sm, s.stage, lane);
         if (s.fresh) { s.curr = err; s.fresh = false; solve = true; break; }                           // :145 / :165
-        if (s.curr - err > M.converge_eps && s.it < M.max_iter) { s.curr = err; s.it++; solve = true; break; }   // :153 / :172
+        if (s.curr - err > M.converge_eps) {                                                                  // :153 / :172
+          if (s.it < M.max_iter) { s.curr = err; s.it++; solve = true; break; }
+          s.flags |= GMR_STATUS_MAX_ITER1 << s.stage;        // the loop ended on its counter, not on the error test
+        }
         if (lane == 0) {
           if (a.err_out) a.err_out[2 * o + s.stage] = err;
           if (a.iters_out) a.iters_out[2 * o + s.stage] = s.it + 1;
@@ -166,9 +182,18 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
       }
       // frame finished (:185)
       if (lane == 0 && a.nfact_out) a.nfact_out[o] = s.nfact;
-      if (a.qpos_out) {
-        double* qo = a.qpos_out + o * a.nq_max;
-        for (int i = lane; i < M.nq; i += 32) qo[i] = sm[lay.q + i];
+      {
+        bool fin = true;
+        double* qo = a.qpos_out ? a.qpos_out + o * a.nq_max : nullptr;
+        for (int i = lane; i < M.nq; i += 32) {
+          const double qi = sm[lay.q + i];
+          fin = fin && isfinite(qi);
+          if (qo) qo[i] = qi;
+        }
+        if (a.status_out) {
+          if (!__all_sync(GMR_FULL, fin)) s.flags |= GMR_STATUS_BAD_OUTPUT;
+          if (lane == 0) a.status_out[o] = s.flags;
+        }
       }
       if (++s.t < s.T) { s.new_frame = true; continue; }
       double* qs = a.q_state + (size_t)s.inst * a.nq_max;
@@ -184,7 +209,8 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
     //      the task stiffnesses); Kernel 4: integrate
     const double mu = stage_stiffness(mv, lay, sm, s.stage, lane);
     const int nf = qp_solve_aba(mv, lay, sm, s.stage, mu, lane, s.act_lo, s.act_hi);
-    s.nfact += nf;
+    if (nf < 0) s.flags |= GMR_STATUS_QP_CAP;                // the active-set search hit its cap: last iterate used
+    s.nfact += abs(nf);
     stage_integrate(mv, lay, sm, lane);
     s.need_fk = true;
   }

@@ -55,6 +55,8 @@ struct DevModel {
   const int* dof_limited;    // [nv]
   const double* dof_lo;      // [nv] joint range lower
   const double* dof_hi;      // [nv]
+  int has_vmax;              // optional velocity box |dq| <= dof_vmax * timestep (off: the reference passes no velocity limit)
+  const double* dof_vmax;    // [nv] (+inf: none)
   const unsigned* dof_taskmask;  // [2*nv] bit t set: task t of the stage is in the dof's subtree
   const unsigned* dof_topmask;   // [2*nv] the top-most of those tasks (no other task of the subtree above them)
   // task tree of each stage (task t's parent = the task on the nearest ancestor body that has one)
@@ -76,15 +78,19 @@ struct DevModel {
   // static schedule of the articulated-body box-QP solver (qp_solve_aba), per stage.  Byte offsets are relative to
   // the per-warp block array (Lay::K): n_task packed task blocks [K_t | g_t] of GMR_KS doubles, then the dofs'
   // accumulators X = [I (6x6 rows) | p] of GMR_XS doubles
-  int aba_nup[2], aba_ndn[2], aba_up0[2], aba_dn0[2], aba_nmerge[2];
+  int aba_nup[2], aba_ndn[2], aba_up0[2], aba_dn0[2], aba_nmerge[2];   // passes of each sweep, first pass of the stage
   int aba_root[2], aba_rootdof[2];   // floating base solved as one block: byte offset of the base link's accumulator (-1: none), first base dof
   unsigned aba_kktmask[2];       // tasks whose block is not merged into another task's (same dof)
   int aba_doubles;               // doubles of the block array a warp needs (max over stages)
-  const int2* aba_uplev;         // [aba_up0[stage] + level] per level (by height): passes [x,y)
-  const int4* aba_p1;            // per (pass, 8-lane group) two words: {dof (-1: idle), X_dof, S_dof, Ud_dof} {task block (-1), children [y,z) of aba_ch, -}
-  const int2* aba_ch;            // per child: its accumulator, its Ud
-  const int2* aba_dnlev;         // [aba_dn0[stage] + level] per level (by depth): passes [x,y)
-  const int4* aba_dn;            // per (pass, 8-lane group): dof (-1: idle), byte offsets of v_parent (-1: none), v_dof, S_dof
+  // upward sweep, per (pass, 8-lane group) two words:
+  //   {dof (-1: idle), flags, S_dof, Ud_dof}  flags: 1 = X carried in registers from the previous dof of the chain
+  //                                                  (bits 8..: that dof), 2 = store X (the chain's top)
+  //   {own task block (-1: none), side children [y,z) of aba_ch, X_dof (where a chain top stores)}
+  const int4* aba_up;
+  const int2* aba_ch;            // per side child: its accumulator, its Ud
+  // downward sweep, per (pass, group): {dof (-1: idle), flags, v_parent (-1: none), -}
+  //   flags: 1 = v carried in registers from the parent (previous dof of the chain), 2 = store v
+  const int4* aba_dn;
   const int2* aba_merge;         // [2*GMR_MAX_TASKS] (dst task, src task) hanging on the same dof
   const int* task_dof;           // [2*GMR_MAX_TASKS] dof the task's body hangs on (-1: none, the task moves nothing)
   // target preparation
@@ -119,9 +125,10 @@ struct ModelView {
 // Body quaternions are stored with a stride of 5 doubles: lane = body accesses with a stride of 4 doubles
 // (32 bytes) hit every bank four times over, 40 bytes spread a half-warp over all 32 banks.
 #define GMR_QS 5
-// Spatial axes S_k and the assembly's F_l are 6-vectors stored with a stride of 7 doubles: an even stride
-// puts 16 consecutive dofs on 8 bank pairs (2-way conflicts for lane = dof and for the H fill), 7 on 16.
-#define GMR_SS 7
+// Spatial axes S_k and the assembly's F_l are 6-vectors stored with a stride of 6 doubles = 48 bytes: 16-byte
+// aligned, so the solver's sweeps fetch an axis with three 128-bit loads (the lanes of an 8-lane group read the same
+// axis: a broadcast); lane = dof accesses (FK pass C) pay a 2-way bank conflict for it.
+#define GMR_SS 6
 // Task error e_t is stored with a stride of 8: 6 components, then sin and cos of its rotation angle.
 #define GMR_ES 8
 // Task stiffness block: K_t (21, packed lower 6x6) followed by g_t (6).
@@ -201,6 +208,41 @@ __device__ __forceinline__ void mtm3(const double* A, const double* B, double* C
 }
 __device__ __forceinline__ void skew3(const double* w, double* S) {
   S[0] = 0; S[1] = -w[2]; S[2] = w[1]; S[3] = w[2]; S[4] = 0; S[5] = -w[0]; S[6] = -w[1]; S[7] = w[0]; S[8] = 0;
+}
+
+// ---------------------------------------------------------------- short reciprocal / root / arctangent
+// The library's double-precision 1/x, sqrt and atan2 carry slow paths for denormals, infinities and signed zeros
+// (20-150 instructions each, inlined at every call site of a kernel whose instruction footprint is what stalls it).
+// The arguments here are plain normal numbers far inside the float range, so a single-precision seed plus two
+// Newton steps (quadratic: 2^-23 -> 2^-46 -> 2^-92) gives the same result to the last bit or two in ~8 instructions.
+__device__ __forceinline__ double rcp_pos(double D) {            // 1 / D, D > 0
+  float seed;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(seed) : "f"((float)D));
+  double inv = (double)seed;
+  inv = fma(inv, fma(-D, inv, 1.0), inv);
+  return fma(inv, fma(-D, inv, 1.0), inv);
+}
+__device__ __forceinline__ double rsqrt_pos(double x) {          // 1 / sqrt(x), x > 0
+  float seed;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(seed) : "f"((float)x));
+  double y = (double)seed;
+  const double hx = 0.5 * x;
+  y = fma(y, fma(-hx * y, y, 0.5), y);
+  return fma(y, fma(-hx * y, y, 0.5), y);
+}
+// atan(lo / hi) for 0 <= lo <= hi, hi > 0: odd polynomial in t = lo / hi on [0, 1] (interpolant at 20 Chebyshev
+// nodes of atan(sqrt(s)) / sqrt(s), s = t^2; error 2.2e-16 = one ulp at pi/4)
+__device__ __forceinline__ double atan_ratio(double lo, double hi) {
+  const double t = lo * rcp_pos(hi), s = t * t;
+  double p = -1.93423475928923e-05;
+  p = fma(p, s, 0.00021423810738603946); p = fma(p, s, -0.0011252544302234645); p = fma(p, s, 0.003751138483965141);
+  p = fma(p, s, -0.00899108054265826); p = fma(p, s, 0.01671959606350739); p = fma(p, s, -0.02556862364437174);
+  p = fma(p, s, 0.03387126702700675); p = fma(p, s, -0.040811247503178855); p = fma(p, s, 0.04668745304848529);
+  p = fma(p, s, -0.052374234719188166); p = fma(p, s, 0.058768281144872724); p = fma(p, s, -0.06665764910689723);
+  p = fma(p, s, 0.07692198997458294); p = fma(p, s, -0.09090899793217341); p = fma(p, s, 0.11111110578002083);
+  p = fma(p, s, -0.14285714266926733); p = fma(p, s, 0.1999999999964796); p = fma(p, s, -0.333333333333307);
+  p = fma(p, s, 1.0);
+  return p * t;
 }
 
 __device__ __forceinline__ double warp_sum(double v) {

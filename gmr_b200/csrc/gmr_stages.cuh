@@ -25,8 +25,9 @@ namespace gmr {
 // ------------------------------------------------------------------ Kernel 1: target preparation
 // lane i < s handles scaled body i (entry 0 = human root).  Reads one frame of the human
 // stream (7 numbers per body, float or double), writes sm[scaled + 7*i .. +7] = pos, quat wxyz.
+// Returns whether every number the frame contributed is finite (warp-uniform).
 template <typename TIn, class MV>
-__device__ __forceinline__ void stage_prep(const MV& mv, const Lay& lay, double* sm, const TIn* frame,
+__device__ __forceinline__ bool stage_prep(const MV& mv, const Lay& lay, double* sm, const TIn* frame,
                                            const double* scale, bool to_ground, int lane) {
   const DevModel& M = mv.M();
   const int s = M.n_scaled;
@@ -75,7 +76,9 @@ __device__ __forceinline__ void stage_prep(const MV& mv, const Lay& lay, double*
 #pragma unroll
     for (int k = 0; k < 7; k++) d[k] = out[k];
   }
+  const bool fin = isfinite(((out[0] + out[1]) + (out[2] + out[3])) + ((out[4] + out[5]) + out[6]));
   __syncwarp();
+  return __all_sync(GMR_FULL, fin);
 }
 
 // ------------------------------------------------------------------ Kernel 2: forward kinematics
@@ -224,19 +227,25 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
 // the Jlog coefficients in stage_stiffness.
 __device__ __forceinline__ void se3_log_dev(const double* q, const double* p, double* out, double& sin_th, double& cos_th) {
   const double qw = q[0], n2 = q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
-  const double n = sqrt(n2), aw = fabs(qw);
-  double f;
-  if (n2 < LIE_EPS) f = 2.0 / qw - 2.0 / 3.0 * n2 / (qw * qw * qw);
-  else if (aw < LIE_EPS) f = (qw > 0 ? 1.0 : -1.0) * 3.14159265358979323846 / n;
-  else f = 2.0 * atan2(qw < 0 ? -n : n, aw) / n;
-  const double in2 = 1.0 / (n2 + qw * qw);
+  const double aw = fabs(qw);
+  const double rn = n2 > 1e-30 ? rsqrt_pos(n2) : 0.0, n = n2 * rn;
+  double f, k;
+  if (n2 < LIE_EPS) {                       // mink SO3.log: Taylor branch; th^2 = f^2 n2 < 4.1e-10, where
+    f = 2.0 / qw - 2.0 / 3.0 * n2 / (qw * qw * qw);       // (1 - th/2 cot(th/2)) / th^2 = 1/12 + th^2/720 to 1e-21
+    k = 1.0 / 12.0 + (f * f * n2) * (1.0 / 720.0);
+  } else {
+    // phi = atan2(n, |qw|) in [0, pi/2] (half the rotation angle); mink: 2 atan2(qw < 0 ? -n : n, |qw|) / n
+    double phi;
+    if (aw < LIE_EPS) phi = 1.5707963267948966;
+    else phi = n <= aw ? atan_ratio(n, aw) : 1.5707963267948966 - atan_ratio(aw, n);
+    f = (qw < 0 ? -2.0 : 2.0) * phi * rn;
+    // |w| = 2 phi, so V^-1's coefficient (1 - th/2 cot(th/2)) / th^2 needs no second root: cot(phi) = |qw| / n
+    k = (1.0 - phi * (aw * rn)) * rcp_pos(4.0 * phi * phi);
+  }
+  const double in2 = rcp_pos(n2 + qw * qw);
   sin_th = 2.0 * n * aw * in2;
   cos_th = (qw * qw - n2) * in2;
   const double w0 = f * q[1], w1 = f * q[2], w2 = f * q[3];
-  const double th2 = w0 * w0 + w1 * w1 + w2 * w2;
-  double k;
-  if (th2 < LIE_EPS) k = 1.0 / 12.0;
-  else k = (1.0 - 0.5 * sqrt(th2) * (aw / n)) / th2;       // cos(th/2) / sin(th/2) = |qw| / |xyz|
   // V^-1 p = p - 1/2 w x p + k w x (w x p)
   double w[3] = {w0, w1, w2}, c1[3], c2[3];
   cross3(w, p, c1);
@@ -637,15 +646,6 @@ __device__ __noinline__ int qp_solve(int n, const double* __restrict__ H, const 
   return spd ? nfact : -nfact;
 }
 
-// 1 / D for D >= damping > 0 and far inside the float range: single-precision seed, two Newton steps (<= 1 ulp)
-__device__ __forceinline__ double rcp_pos(double D) {
-  float seed;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(seed) : "f"((float)D));
-  double inv = (double)seed;
-  inv = fma(inv, fma(-D, inv, 1.0), inv);
-  return fma(inv, fma(-D, inv, 1.0), inv);
-}
-
 // ------------------------------------------------------------------ Kernel 3: exact box QP on the kinematic tree
 // Same problem and same pivoting rules as qp_solve above, but neither H nor c is ever formed.  With v_i the
 // "spatial velocity" of dof i's link (v_i = v_parent + S_i x_i), the objective of mink's build_ik is
@@ -660,13 +660,18 @@ __device__ __forceinline__ double rcp_pos(double D) {
 // A dof held at a bound b_c is a locked joint: alpha_c = 0, beta_c = -b_c (then X^a_c = [I_c | p_c + U_c b_c] and
 // the same downward formula returns x_c = b_c).  Its multiplier is (Hx + c)_c = S_c' sum_{t below c} f_t + d x_c with
 // f_t = K_t v + g_t.  All spatial quantities are expressed about the one reference point O of stage_fk, so nothing is
-// transformed between links.  The schedule is static (DevModel.aba_*, built at model creation per stage): dofs without a
-// task below them are left out (x = 0 or their bound), dofs of equal height share a level.
-// Lanes: a pass of the upward sweep handles 4 dofs, 8 lanes each: lane i < 6 gathers row i of X_c (its own task block,
-// packed, plus the children's accumulators minus their rank-1 terms), stores it in the dof's accumulator (full rows,
-// in place over the first child's), forms U_i and the partial sums of D and S'p; lanes 6 and 7 store alpha and beta.
-// The downward pass handles 4 dofs per pass the same way.  One __syncwarp per level in each direction.
-// `act_lo`/`act_hi` seed the search and return the final active set; returns #passes of the pivoting loop.
+// transformed between links.
+// Schedule (DevModel.aba_*, static, built at model creation per stage): dofs without a task below them are left out
+// (x = 0 or their bound); the others are cut into chains (a dof continues into its tallest child).  A pass handles
+// one dof on each of the warp's four 8-lane groups; a chain stays on its group, and lane i < 6 of the group keeps
+// row i of the chain's X = [I | p] in REGISTERS from one dof to the next: per dof it subtracts the previous dof's
+// rank-1 term (U, alpha, beta come back from Ud with four 128-bit loads), adds the dof's own task block (packed) and
+// the accumulators of side chains that end here (shared memory, stored by their tops), forms U_i = X_i S and the
+// partial sums of D and S'p (three shuffle rounds inside the group); lanes 6 and 7 store alpha and beta.  Only a
+// chain's top writes X to shared memory.  The downward sweep runs the same chains top-down with v in registers.
+// One __syncwarp per pass.  `act_lo`/`act_hi` seed the search and return the final active set; returns #sweeps of the
+// pivoting loop, negative if the search hit its cap (the caller flags the frame; the last iterate is returned).
+#define QP_MAX_SWEEPS 100
 template <class MV>
 __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double* __restrict__ sm, int stage, double mu_sum,
                                             int lane, unsigned long long& act_lo, unsigned long long& act_hi) {
@@ -680,13 +685,11 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   double* x = sm + lay.x;
   double* fv = sm + lay.e;                  // task forces of the KKT check (e is dead during the solve)
   const double* q = sm + lay.q;
-  const int2* uplev = mv(M.aba_uplev) + M.aba_up0[stage];
-  const int2* dnlev = mv(M.aba_dnlev) + M.aba_dn0[stage];
-  const int4* p1 = mv(M.aba_p1);
-  const int2* chl = mv(M.aba_ch);
-  const int4* dn = mv(M.aba_dn);
   const int nup = M.aba_nup[stage], ndn = M.aba_ndn[stage];
   const int g8 = lane >> 3, i8 = lane & 7;
+  const int4* const up0 = mv(M.aba_up) + 8 * M.aba_up0[stage] + 2 * g8;
+  const int4* const dn0 = mv(M.aba_dn) + 4 * M.aba_dn0[stage] + g8;
+  const int2* chl = mv(M.aba_ch);
   // row i8 of a packed symmetric block: byte offsets of K(i8, 0..5), one byte each
   unsigned row_lo = 0, row_hi = 0;
   {
@@ -709,7 +712,8 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   else if (lane < GMR_KS) ra = lane - 21;
   const int i0 = lane, i1 = lane + 32;
   const bool has0 = i0 < n, has1 = i1 < n;
-  // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs
+  // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs, intersected with the
+  // optional velocity box |dq| <= vmax dt (off by default: the reference passes no velocity limit, motion_retarget.py:147-149)
   double lo0 = -INFINITY, hi0 = INFINITY, lo1 = -INFINITY, hi1 = INFINITY;
   if (has0 && mv(M.dof_limited)[i0]) {
     const double qv = q[mv(M.dof_qadr)[i0]];
@@ -718,6 +722,11 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   if (has1 && mv(M.dof_limited)[i1]) {
     const double qv = q[mv(M.dof_qadr)[i1]];
     hi1 = M.limit_gain * (mv(M.dof_hi)[i1] - qv); lo1 = -M.limit_gain * (qv - mv(M.dof_lo)[i1]);
+  }
+  if (M.has_vmax) {
+    const double* vm = mv(M.dof_vmax);
+    if (has0) { const double b = vm[i0] * M.timestep; hi0 = fmin(hi0, b); lo0 = fmax(lo0, -b); }
+    if (has1) { const double b = vm[i1] * M.timestep; hi1 = fmin(hi1, b); lo1 = fmax(lo1, -b); }
   }
   // tasks that hang on the same dof are summed into the first of them
   {
@@ -732,9 +741,10 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   if (has1) st1 = ((act_lo >> i1) & 1ull) && lo1 > -INFINITY ? -1 : (((act_hi >> i1) & 1ull) && hi1 < INFINITY ? 1 : 0);
   unsigned long long act = (unsigned long long)__ballot_sync(GMR_FULL, st0 != 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 != 0) << 32);
   int best = n + 1, p = 3, nfact = 0;
+  bool restarted = act == 0, capped = false;      // a warm-started search that hits its cap starts over cold once
   double r0 = 0, r1 = 0;
 #pragma unroll 1
-  for (int it = 0; it < 400; it++) {
+  for (int it = 0;; it++) {
     // dofs at a bound carry it; free dofs without a task below them stay at 0 (the sweeps skip them)
     const double xa0 = st0 < 0 ? lo0 : (st0 > 0 ? hi0 : 0.0), xa1 = st1 < 0 ? lo1 : (st1 > 0 ? hi1 : 0.0);
     if (has0) { x[i0] = xa0; if (st0) { Ud[8 * i0 + 6] = 0.0; Ud[8 * i0 + 7] = -xa0; } }      // locked joint: alpha = 0, beta = -bound
@@ -742,56 +752,67 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
     __syncwarp();
     // ---- upward sweep
     const unsigned actw0 = (unsigned)act, actw1 = (unsigned)(act >> 32);
+    {
+      double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0, a5 = 0, pi = 0, Uprev = 0;      // row i8 of the chain's X, U_i8 of its last dof
+      const int4* e = up0;
 #pragma unroll 1
-    for (int lv = 0; lv < nup; lv++) {
-      const int2 L = uplev[lv];
-#pragma unroll 1
-      for (int ps = L.x; ps < L.y; ps++) {
-        // dof (-1: idle), byte offsets of its accumulator X_c, of S_c, of Ud_c | its task block (-1: none), children [y, z)
-        const int4 en = p1[(ps * 4 + g8) * 2], eb = p1[(ps * 4 + g8) * 2 + 1];
+      for (int ps = 0; ps < nup; ps++, e += 8) {
+        // {dof (-1: idle), flags, S_c, Ud_c} {own task block (-1: none), side children [y, z), X_c}
+        const int4 en = e[0], eb = e[1];
         const bool valid = en.x >= 0;
-        const char* Sc = Sb + en.z;
-        double U = 0.0, t = 0.0, w = 0.0;
-        if (i8 < 6) {
-          // row i8 of X_c = [I_c | p_c] = own tasks + sum over children of [I - U U' alpha | p - U beta]
-          double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0, a5 = 0, pi = 0;
-          if (eb.x >= 0) {
+        double t = 0.0, w = 0.0, U = 0.0;
+        if (valid && i8 < 6) {
+          if (en.y & 1) {                                      // the chain's previous dof: X -= [U U' alpha | U beta]
+            const double2* ud = (const double2*)(Udb + ((en.y >> 8) << 6));
+            const double2 u01 = ud[0], u23 = ud[1], u45 = ud[2], ab = ud[3];
+            const double ua = -Uprev * ab.x;
+            a0 = fma(ua, u01.x, a0); a1 = fma(ua, u01.y, a1); a2 = fma(ua, u23.x, a2);
+            a3 = fma(ua, u23.y, a3); a4 = fma(ua, u45.x, a4); a5 = fma(ua, u45.y, a5);
+            pi = fma(-Uprev, ab.y, pi);
+          } else {
+            a0 = a1 = a2 = a3 = a4 = a5 = pi = 0.0;
+          }
+          if (eb.x >= 0) {                                     // own task block, packed symmetric
             const char* own = XAc + eb.x;
-            a0 = *(const double*)(own + __byte_perm(row_lo, 0, 0x4440)); a1 = *(const double*)(own + __byte_perm(row_lo, 0, 0x4441));
-            a2 = *(const double*)(own + __byte_perm(row_lo, 0, 0x4442)); a3 = *(const double*)(own + __byte_perm(row_lo, 0, 0x4443));
-            a4 = *(const double*)(own + __byte_perm(row_hi, 0, 0x4440)); a5 = *(const double*)(own + __byte_perm(row_hi, 0, 0x4441));
-            pi = *(const double*)(own + 168 + i8b);
+            a0 += *(const double*)(own + __byte_perm(row_lo, 0, 0x4440)); a1 += *(const double*)(own + __byte_perm(row_lo, 0, 0x4441));
+            a2 += *(const double*)(own + __byte_perm(row_lo, 0, 0x4442)); a3 += *(const double*)(own + __byte_perm(row_lo, 0, 0x4443));
+            a4 += *(const double*)(own + __byte_perm(row_hi, 0, 0x4440)); a5 += *(const double*)(own + __byte_perm(row_hi, 0, 0x4441));
+            pi += *(const double*)(own + 168 + i8b);
           }
 #pragma unroll 1
-          for (int ch = eb.y; ch < eb.z; ch++) {
-            const int2 cd = chl[ch];                             // byte offsets of the child's accumulator and of its Ud
-            const double* Xr = (const double*)(XAc + cd.x + 6 * i8b);
-            const double* ud = (const double*)(Udb + cd.y);
-            const double ui = *(const double*)(Udb + cd.y + i8b), al = ud[6];
-            a0 += Xr[0] - (ui * ud[0]) * al; a1 += Xr[1] - (ui * ud[1]) * al; a2 += Xr[2] - (ui * ud[2]) * al;
-            a3 += Xr[3] - (ui * ud[3]) * al; a4 += Xr[4] - (ui * ud[4]) * al; a5 += Xr[5] - (ui * ud[5]) * al;
-            pi += *(const double*)(XAc + cd.x + 288 + i8b) - ui * ud[7];
+          for (int ch = eb.y; ch < eb.z; ch++) {               // side chains that end here: X from shared memory
+            const int2 cd = chl[ch];                           // byte offsets of the child's accumulator and of its Ud
+            const double2* Xr = (const double2*)(XAc + cd.x + 6 * i8b);
+            const double2* ud = (const double2*)(Udb + cd.y);
+            const double2 x01 = Xr[0], x23 = Xr[1], x45 = Xr[2], u01 = ud[0], u23 = ud[1], u45 = ud[2], ab = ud[3];
+            const double ui = *(const double*)(Udb + cd.y + i8b), ua = -ui * ab.x;
+            a0 += fma(ua, u01.x, x01.x); a1 += fma(ua, u01.y, x01.y); a2 += fma(ua, u23.x, x23.x);
+            a3 += fma(ua, u23.y, x23.y); a4 += fma(ua, u45.x, x45.x); a5 += fma(ua, u45.y, x45.y);
+            pi += fma(-ui, ab.y, *(const double*)(XAc + cd.x + 288 + i8b));
           }
-          if (valid) {
-            double* Xd = (double*)(XAc + en.y + 6 * i8b);
-            Xd[0] = a0; Xd[1] = a1; Xd[2] = a2; Xd[3] = a3; Xd[4] = a4; Xd[5] = a5;
-            *(double*)(XAc + en.y + 288 + i8b) = pi;
+          if (en.y & 2) {                                      // a chain's top: X to shared memory
+            double2* Xd = (double2*)(XAc + eb.w + 6 * i8b);
+            Xd[0] = make_double2(a0, a1); Xd[1] = make_double2(a2, a3); Xd[2] = make_double2(a4, a5);
+            *(double*)(XAc + eb.w + 288 + i8b) = pi;
           }
-          const double* Sd = (const double*)Sc;
-          U = a0 * Sd[0] + a2 * Sd[2] + a4 * Sd[4];
-          U += a1 * Sd[1] + a3 * Sd[3] + a5 * Sd[5];
-          const double si = *(const double*)(Sc + i8b);
+          const double2* Sd = (const double2*)(Sb + en.z);
+          const double2 s01 = Sd[0], s23 = Sd[1], s45 = Sd[2];
+          U = fma(a4, s45.x, fma(a2, s23.x, a0 * s01.x)) + fma(a5, s45.y, fma(a3, s23.y, a1 * s01.y));
+          const double si = *(const double*)(Sb + en.z + i8b);
           t = si * U;
           w = si * pi;
+          Uprev = U;
         }
 #pragma unroll
         for (int o = 1; o < 8; o <<= 1) { t += __shfl_xor_sync(GMR_FULL, t, o); w += __shfl_xor_sync(GMR_FULL, w, o); }
-        const bool isact = valid && (((en.x < 32 ? actw0 : actw1) >> (en.x & 31)) & 1u);
-        const double inv = rcp_pos(t + diag);                    // D = S'U + d
-        // lanes 0..5 store U, lane 6 alpha = 1/D, lane 7 beta = S'p / D (a locked dof keeps the pair its owner lane wrote)
-        if (valid && (i8 < 6 || !isact)) *(double*)(Udb + en.w + i8b) = i8 < 6 ? U : (i8 == 6 ? inv : w * inv);
+        if (valid) {
+          const bool isact = ((en.x < 32 ? actw0 : actw1) >> (en.x & 31)) & 1u;
+          const double inv = rcp_pos(t + diag);                  // D = S'U + d
+          // lanes 0..5 store U, lane 6 alpha = 1/D, lane 7 beta = S'p / D (a locked dof keeps the pair its owner lane wrote)
+          if (i8 < 6 || !isact) *(double*)(Udb + en.w + i8b) = i8 < 6 ? U : (i8 == 6 ? inv : w * inv);
+        }
+        __syncwarp();
       }
-      __syncwarp();
     }
     // ---- floating base: its six dofs span R^6 and are never limited, so they are solved as one 6x6 block
     // (M = S_b' I S_b + d, M x_b = -S_b' p) instead of six more levels up and six down
@@ -862,27 +883,32 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
       __syncwarp();
     }
     nfact++;
-    // ---- downward sweep
+    // ---- downward sweep: the same chains top-down, v_i8 of the chain's current link in a register
+    {
+      double vi = 0.0;
+      const int4* e = dn0;
 #pragma unroll 1
-    for (int lv = 0; lv < ndn; lv++) {
-      const int2 L = dnlev[lv];
-#pragma unroll 1
-      for (int ps = L.x; ps < L.y; ps++) {
-        const int4 en = dn[ps * 4 + g8];                         // dof (-1: idle), byte offsets of v_parent (-1: none), v_c, S_c
+      for (int ps = 0; ps < ndn; ps++, e += 4) {
+        const int4 en = *e;                                      // dof (-1: idle), flags, byte offset of v_parent (-1: none)
         const bool valid = en.x >= 0;
-        const int c = valid ? en.x : 0;
-        const double vp = (en.y >= 0 && i8 < 6) ? *(const double*)(vb + en.y + i8b) : 0.0;
-        const char* ud = Udb + 64 * c;
-        double dot = i8 < 6 ? *(const double*)(ud + i8b) * vp : 0.0;
+        const char* ud = Udb + 64 * (valid ? en.x : 0);
+        double dot = 0.0;
+        if (valid && i8 < 6) {
+          if (!(en.y & 1)) vi = en.z >= 0 ? *(const double*)(vb + en.z + i8b) : 0.0;     // a chain's top: v_parent from shared memory
+          dot = *(const double*)(ud + i8b) * vi;
+        }
 #pragma unroll
         for (int o = 1; o < 8; o <<= 1) dot += __shfl_xor_sync(GMR_FULL, dot, o);
-        const double xc = -dot * *(const double*)(ud + 48) - *(const double*)(ud + 56);
         if (valid) {
-          if (i8 < 6) *(double*)(vb + en.z + i8b) = vp + *(const double*)(Sb + en.w + i8b) * xc;
-          else if (i8 == 6) x[c] = xc;
+          const double2 ab = *(const double2*)(ud + 48);
+          const double xc = fma(-dot, ab.x, -ab.y);
+          if (i8 < 6) {
+            vi = fma(*(const double*)(Sb + GMR_SS * 8 * en.x + i8b), xc, vi);
+            if (en.y & 2) *(double*)(vb + 48 * en.x + i8b) = vi;
+          } else if (i8 == 6) x[en.x] = xc;
         }
+        __syncwarp();
       }
-      __syncwarp();
     }
     r0 = has0 ? x[i0] : 0.0;
     r1 = has1 ? x[i1] : 0.0;
@@ -932,6 +958,12 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
     const unsigned b0 = __ballot_sync(GMR_FULL, bad0), b1 = __ballot_sync(GMR_FULL, bad1);
     const int nbad = __popc(b0) + __popc(b1);
     if (nbad == 0) break;
+    if (it + 1 >= QP_MAX_SWEEPS) {
+      if (restarted) { capped = true; break; }
+      restarted = true;                                          // cycling on a stale seed: once more from the empty set
+      it = -1; st0 = st1 = 0; act = 0; best = n + 1; p = 3;
+      continue;
+    }
     bool all;
     if (nbad < best) { best = nbad; p = 3; all = true; }
     else if (p > 0) { p--; all = true; }
@@ -946,7 +978,7 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   act_lo = (unsigned long long)__ballot_sync(GMR_FULL, st0 < 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 < 0) << 32);
   act_hi = (unsigned long long)__ballot_sync(GMR_FULL, st0 > 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 > 0) << 32);
   __syncwarp();
-  return nfact;
+  return capped ? -nfact : nfact;
 }
 
 // H(i,j) of the tree layout (0 if neither dof is an ancestor of the other)

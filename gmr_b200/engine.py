@@ -170,8 +170,9 @@ class BatchedRetargeter:
             return None, {}
         out = {"err": torch.zeros((self.B, T, 2), dtype=torch.float64, device=self.tdev),
                "iters": torch.zeros((self.B, T, 2), dtype=torch.int32, device=self.tdev),
-               "nfact": torch.zeros((self.B, T), dtype=torch.int32, device=self.tdev)}
-        d = gmr_diag(out["err"].data_ptr(), out["iters"].data_ptr(), out["nfact"].data_ptr())
+               "nfact": torch.zeros((self.B, T), dtype=torch.int32, device=self.tdev),
+               "status": torch.zeros((self.B, T), dtype=torch.int32, device=self.tdev)}
+        d = gmr_diag(out["err"].data_ptr(), out["iters"].data_ptr(), out["nfact"].data_ptr(), out["status"].data_ptr())
         return d, out
 
     # ---------------------------------------------------------------- hot path

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define GMR_ABI_VERSION 1
+#define GMR_ABI_VERSION 2
 
 /* hard limits of the kernels (largest shipped robot: nv = 49, nbody = 53, 15 tasks) */
 #define GMR_MAX_NV     64
@@ -90,13 +90,29 @@ typedef struct gmr_model_desc {
   double  converge_eps;             /* 0.001 (:153,172) */
   double  limit_gain;               /* mink ConfigurationLimit gain 0.95 */
   double  lm_damping;               /* FrameTask lm_damping = 1 (:88,106) */
+  /* optional velocity limit (north_star; mink.VelocityLimit): per dof |dq| <= dof_vmax * timestep, intersected with
+   * the position box of every solve.  NULL = off = the reference's behaviour (it passes no limits to solve_ik,
+   * :147-149, so only mink's default ConfigurationLimit applies).  [nv], +inf = unlimited; the six dofs of a free
+   * joint must be +inf. */
+  const double*  dof_vmax;
 } gmr_model_desc;
 
-/* per-frame diagnostics (reference: error1()/error2() :188-200, loop counters :152,171) */
+/* per-frame status bits (gmr_diag.status_dev).  The reference has no such report: its loops end silently on
+ * max_iter (:153,172), and a frame mink/daqp cannot solve raises and the driver skips the file
+ * (scripts/bvh_to_robot_dataset.py:75-80 pattern); the batch cannot raise per clip, so it flags. */
+#define GMR_STATUS_MAX_ITER1  1   /* stage 1 left its loop on the iteration counter, not on the error test */
+#define GMR_STATUS_MAX_ITER2  2   /* same for stage 2 */
+#define GMR_STATUS_QP_CAP     4   /* the box QP's active-set search hit its cap (even after a cold restart) */
+#define GMR_STATUS_BAD_INPUT  8   /* a non-finite number in the frame's targets */
+#define GMR_STATUS_BAD_OUTPUT 16  /* a non-finite number in the frame's qpos (poisons the rest of the clip through the warm start) */
+
+/* per-frame diagnostics (reference: error1()/error2() :188-200, loop counters :152,171); rows are [B,T] for the
+ * dense calls and [N] (one per frame of the CSR stream) for the *_csr calls */
 typedef struct gmr_diag {
   double*  err_dev;      /* [B,T,2] final error1/error2 of the frame, or NULL */
   int32_t* iters_dev;    /* [B,T,2] QP solves per stage (1..max_iter+1), or NULL */
   int32_t* nfact_dev;    /* [B,T]   sweeps of the box-QP solver in the frame (one per solve_ik + one per change of the active set), or NULL */
+  int32_t* status_dev;   /* [B,T]   GMR_STATUS_* bits, or NULL */
 } gmr_diag;
 
 typedef struct gmr_model gmr_model;
@@ -113,13 +129,12 @@ int gmr_model_destroy(gmr_model* m);
 /* Static schedule of the fused kernel's box-QP solver for one stage (host-only models): copies table `which`
  * into out[0..cap) and returns the number of int32 it holds.  Byte offsets in the tables are relative to a warp's
  * block array / Ud / v / S arrays as laid out in csrc/gmr_device.cuh (DevModel.aba_*). */
-#define GMR_TABLE_INFO       0   /* nv, n_task, n_up_levels, n_down_levels, n_merge, root block offset (-1: none), first base dof,
+#define GMR_TABLE_INFO       0   /* nv, n_task, n_up_passes, n_down_passes, n_merge, root block offset (-1: none), first base dof,
                                     kkt task mask, doubles of the block array, GMR_KS, GMR_XS, GMR_SS */
-#define GMR_TABLE_UPLEV      1   /* per level: pass range [begin, end) */
-#define GMR_TABLE_UP         2   /* per (pass, 8-lane group) 8 ints: dof (-1 idle), X, S, Ud offsets, task block (-1), children [b, e), 0 */
-#define GMR_TABLE_CHILD      3   /* per child: accumulator offset, Ud offset */
-#define GMR_TABLE_DNLEV      4
-#define GMR_TABLE_DN         5   /* per (pass, group) 4 ints: dof (-1 idle), v_parent offset (-1: none), v offset, S offset */
+#define GMR_TABLE_UP         2   /* per (pass, 8-lane group) 8 ints: dof (-1 idle), flags (1: X carried in registers from dof
+                                    flags >> 8, 2: store X), S, Ud offsets, own task block (-1), side children [b, e), X offset */
+#define GMR_TABLE_CHILD      3   /* per side child: accumulator offset, Ud offset */
+#define GMR_TABLE_DN         5   /* per (pass, group) 4 ints: dof (-1 idle), flags (1: v carried, 2: store v), v_parent offset (-1: none), 0 */
 #define GMR_TABLE_MERGE      6   /* pairs (dst task, src task) hanging on one dof */
 #define GMR_TABLE_TASK_DOF   7
 #define GMR_TABLE_DOF_PARENT 8
@@ -159,6 +174,26 @@ int gmr_batch_step(gmr_batch* b, const void* human_dev, int human_dtype, int off
 int gmr_batch_run(gmr_batch* b, const void* human_dev, int human_dtype,
                   const int32_t* T_of_instance_dev, int T_max, int offset_to_ground,
                   double* qpos_out_dev, const gmr_diag* diag);
+
+/* gmr_batch_run on a CSR stream: the clips lie back to back, clip i owns rows [clip_start[i], clip_start[i+1]) of
+ * human_dev [N,h,7] and of qpos_out_dev [N,nq_max] (and of the diag arrays); nothing is padded to the longest clip,
+ * so a dataset with lengths from 60 to 3000 frames costs its frames, not B x 3000.  clip_start_dev: int64 [B+1]
+ * (device); T_max = the longest clip (the caller knows the lengths). */
+int gmr_batch_run_csr(gmr_batch* b, const void* human_dev, int human_dtype, const int64_t* clip_start_dev,
+                      int T_max, int offset_to_ground, double* qpos_out_dev, const gmr_diag* diag);
+
+/* gmr_batch_run_csr for HOST buffers: human_host [N,h,7], clip_start_host int64 [B+1], qpos_out_host [N,nq_max],
+ * status_out_host int32 [N] or NULL.  Zero-copy when all buffers are page-locked (the kernel reads and writes them
+ * over the bus), else one H2D copy, the launch, one D2H copy through device staging.  cold_start as below.
+ * Asynchronous on the batch's stream. */
+int gmr_batch_run_host_csr(gmr_batch* b, const void* human_host, int human_dtype, const int64_t* clip_start_host,
+                           int offset_to_ground, int cold_start, double* qpos_out_host, int32_t* status_out_host);
+
+/* one retarget() for every instance straight from / to page-locked HOST buffers (the B = 1 shim's call: one
+ * launch, no staging copies): human_host [B,h,7], qpos_out_host [B,nq_max], scaled_out_host [B,s_max,7] or NULL.
+ * sync != 0: returns after the batch's stream has finished. */
+int gmr_batch_step_host(gmr_batch* b, const void* human_host, int human_dtype, int offset_to_ground,
+                        double* qpos_out_host, double* scaled_out_host, int sync);
 
 /* gmr_batch_run for clips held in HOST memory (pinned for full overlap): what the dataset drivers
  * call per folder (scripts/bvh_to_robot_dataset.py:96-113, smplx_to_robot_dataset.py:83-104).

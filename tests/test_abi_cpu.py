@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(L, n), f"{n} declared in the header but not exported"
     assert sorted(_lib.EXPORTS) == names
-    assert L.gmr_abi_version() == 1
+    assert L.gmr_abi_version() == 2
 
 
 def test_struct_layout_matches_header():
@@ -31,17 +31,20 @@ def test_struct_layout_matches_header():
     import tempfile
     from gmr_b200.abi import gmr_diag, gmr_model_desc
     src = '#include <stdio.h>\n#include "gmr_b200.h"\nint main(){printf("%zu %zu %zu %zu\\n", sizeof(gmr_model_desc), sizeof(gmr_diag), ' \
-          '__builtin_offsetof(gmr_model_desc, damping), __builtin_offsetof(gmr_model_desc, task_wrot));return 0;}\n'
+          '__builtin_offsetof(gmr_model_desc, damping), __builtin_offsetof(gmr_model_desc, task_wrot));' \
+          'printf("%zu %zu\\n", __builtin_offsetof(gmr_model_desc, dof_vmax), __builtin_offsetof(gmr_diag, status_dev));return 0;}\n'
     with tempfile.TemporaryDirectory() as td:
         c = os.path.join(td, "t.c")
         open(c, "w").write(src)
         exe = os.path.join(td, "t")
         subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe])
-        a, b, off1, off2 = map(int, subprocess.check_output([exe]).split())
+        a, b, off1, off2, off3, off4 = map(int, subprocess.check_output([exe]).split())
     assert ctypes.sizeof(gmr_model_desc) == a
     assert ctypes.sizeof(gmr_diag) == b
     assert gmr_model_desc.damping.offset == off1
     assert gmr_model_desc.task_wrot.offset == off2
+    assert gmr_model_desc.dof_vmax.offset == off3
+    assert gmr_diag.status_dev.offset == off4
 
 
 def test_engine_fails_loudly_without_library(monkeypatch, tmp_path):

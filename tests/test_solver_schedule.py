@@ -2,7 +2,7 @@
 
 A host-only model (device = GMR_HOST_ONLY, no CUDA call) exposes the tables through gmr_model_table; this test
 walks them exactly as csrc/gmr_stages.cuh::qp_solve_aba does - same block array, same byte offsets, same order of
-levels, passes and 8-lane groups - with random task stiffnesses on the real kinematic trees, and compares the
+passes and 8-lane groups, the chains' accumulators and velocities in per-group registers - with random task stiffnesses on the real kinematic trees, and compares the
 result (solution and multipliers of locked dofs) with a dense solve of the same QP.  All ten (source, robot) pairs,
 both stages, plus an edited table with two task frames on one dof.
 """
@@ -15,7 +15,7 @@ import pytest
 PAIRS = [("bvh", "unitree_g1"), ("smplx", "unitree_g1_with_hands"), ("smplx", "galaxea_r1pro"),
          ("bvh", "engineai_pm01"), ("smplx", "hightorque_hi"), ("smplx", "kuavo_s45"), ("smplx", "booster_k1"),
          ("bvh", "booster_t1"), ("smplx", "stanford_toddy"), ("bvh", "fourier_n1")]
-INFO, UPLEV, UP, CHILD, DNLEV, DN, MERGE, TASK_DOF, DOF_PARENT, TASKMASK = range(10)
+INFO, UP, CHILD, DN, MERGE, TASK_DOF, DOF_PARENT, TASKMASK = 0, 2, 3, 5, 6, 7, 8, 9
 
 
 class HostModel:
@@ -51,18 +51,19 @@ def _sym_unpack(v):
 
 
 def _walk(hm, stage, S, K, g, d, locked, bound):
-    """qp_solve_aba's sweeps for a fixed set of locked dofs -> (x, multipliers)."""
+    """qp_solve_aba's sweeps for a fixed set of locked dofs -> (x, multipliers, dofs swept).
+    Mirrors the kernel: four 8-lane groups, each with a REGISTER copy of its chain's accumulator (rows, p, U of the
+    last dof) in the upward sweep and of the link velocity in the downward sweep; shared memory (XA, Ud, v) is only
+    touched where the kernel touches it, and starts as NaN so that anything read before it is written shows up."""
     nv, m, nup, ndn, nmerge, rootX, rootdof, kkt, doubles, KS, XS, SS = hm.table(INFO, stage)
-    uplev = hm.table(UPLEV, stage).reshape(-1, 2)
     up = hm.table(UP, stage).reshape(-1, 8)
     ch = hm.table(CHILD, stage).reshape(-1, 2)
-    dnlev = hm.table(DNLEV, stage).reshape(-1, 2)
     dn = hm.table(DN, stage).reshape(-1, 4)
     merge = hm.table(MERGE, stage).reshape(-1, 2)
     task_dof = hm.table(TASK_DOF, stage)
     tmask = hm.table(TASKMASK, stage).astype(np.uint32)
-    assert len(uplev) == nup and len(dnlev) == ndn and len(merge) == nmerge and (KS, XS) == (27, 42)
-    XA = np.full(doubles, np.nan)                       # anything read before it is written shows up as NaN
+    assert len(up) == 4 * nup and len(dn) == 4 * ndn and len(merge) == nmerge and (KS, XS, SS) == (27, 42, 6)
+    XA = np.full(doubles, np.nan)
     for t in range(m):
         XA[KS * t:KS * t + 21] = _sym_pack(K[t])
         XA[KS * t + 21:KS * t + 27] = g[t]
@@ -77,54 +78,89 @@ def _walk(hm, stage, S, K, g, d, locked, bound):
     for c in np.nonzero(locked)[0]:
         Ud[8 * c + 6], Ud[8 * c + 7] = 0.0, -bound[c]
     seen = set()
-    for b, e in uplev:
-        for ps in range(b, e):
-            for grp in range(4):
-                c, Xo, So, Uo, own, cb, ce, _ = up[ps * 4 + grp]
-                if c < 0:
-                    continue
-                assert c not in seen and So == c * SS * 8 and Uo == c * 64 and Xo % 16 == 0
-                seen.add(int(c))
+    reg = [dict(rows=np.full((6, 6), np.nan), p=np.full(6, np.nan), U=np.full(6, np.nan), dof=-1) for _ in range(4)]
+    stored = set()
+    for ps in range(nup):
+        writes = []                                       # shared-memory stores become visible after the pass (__syncwarp)
+        for grp in range(4):
+            c, flags, So, Uo, own, cb, ce, Xo = up[ps * 4 + grp]
+            if c < 0:
+                continue
+            assert c not in seen and So == c * SS * 8 and Uo == c * 64 and Xo % 16 == 0
+            seen.add(int(c))
+            r = reg[grp]
+            if flags & 1:
+                prev = flags >> 8
+                assert r["dof"] == prev, "carried accumulator is not the previous dof of this group"
+                al, be = Ud[8 * prev + 6], Ud[8 * prev + 7]
+                Uc = Ud[8 * prev:8 * prev + 6]
+                np.testing.assert_array_equal(Uc, r["U"])
+                rows = r["rows"] - np.outer(r["U"], Uc) * al
+                p = r["p"] - r["U"] * be
+            else:
                 rows, p = np.zeros((6, 6)), np.zeros(6)
-                if own >= 0:
-                    rows += _sym_unpack(XA[own // 8:own // 8 + 21])
-                    p += XA[own // 8 + 21:own // 8 + 27]
-                for Xc, udc in ch[cb:ce]:
-                    U, al, be = Ud[udc // 8:udc // 8 + 6], Ud[udc // 8 + 6], Ud[udc // 8 + 7]
-                    rows += XA[Xc // 8:Xc // 8 + 36].reshape(6, 6) - np.outer(U, U) * al
-                    p += XA[Xc // 8 + 36:Xc // 8 + 42] - U * be
-                XA[Xo // 8:Xo // 8 + 36] = rows.ravel()
-                XA[Xo // 8 + 36:Xo // 8 + 42] = p
-                Sc = Sarr[So // 8:So // 8 + 6]
-                U = rows @ Sc
-                Ud[Uo // 8:Uo // 8 + 6] = U
-                if not locked[c]:
-                    D = Sc @ U + d
-                    Ud[Uo // 8 + 6], Ud[Uo // 8 + 7] = 1.0 / D, (Sc @ p) / D
+            if own >= 0:
+                rows = rows + _sym_unpack(XA[own // 8:own // 8 + 21])
+                p = p + XA[own // 8 + 21:own // 8 + 27]
+            for Xc, udc in ch[cb:ce]:
+                assert Xc in stored
+                U, al, be = Ud[udc // 8:udc // 8 + 6], Ud[udc // 8 + 6], Ud[udc // 8 + 7]
+                rows = rows + XA[Xc // 8:Xc // 8 + 36].reshape(6, 6) - np.outer(U, U) * al
+                p = p + XA[Xc // 8 + 36:Xc // 8 + 42] - U * be
+            if flags & 2:
+                writes.append((Xo // 8, np.concatenate([rows.ravel(), p])))
+                stored.add(int(Xo))
+            Sc = Sarr[So // 8:So // 8 + 6]
+            U = rows @ Sc
+            w = [(Uo // 8, U.copy())]
+            if not locked[c]:
+                D = Sc @ U + d
+                w.append((Uo // 8 + 6, np.array([1.0 / D, (Sc @ p) / D])))
+            writes += w
+            reg[grp] = dict(rows=rows, p=p, U=U, dof=int(c))
+        for off, val in writes:
+            tgt = Ud if val.size <= 6 else XA
+            tgt[off:off + val.size] = val
     if rootX >= 0:
+        assert rootX in stored
         I = XA[rootX // 8:rootX // 8 + 36].reshape(6, 6)
         p = XA[rootX // 8 + 36:rootX // 8 + 42]
         Sb = np.stack([S[rootdof + b] for b in range(6)], 1)
         xb = np.linalg.solve(Sb.T @ I @ Sb + d * np.eye(6), -Sb.T @ p)
         x[rootdof:rootdof + 6] = xb
         v[6 * (rootdof + 5):6 * (rootdof + 5) + 6] = Sb @ xb
-    for b, e in dnlev:
-        for ps in range(b, e):
-            for grp in range(4):
-                c, vpo, vo, So = dn[ps * 4 + grp]
-                if c < 0:
-                    continue
-                vp = v[vpo // 8:vpo // 8 + 6] if vpo >= 0 else np.zeros(6)
-                xc = -(Ud[8 * c:8 * c + 6] @ vp) * Ud[8 * c + 6] - Ud[8 * c + 7]
-                v[vo // 8:vo // 8 + 6] = vp + Sarr[So // 8:So // 8 + 6] * xc
-                x[c] = xc
+    vreg = [dict(v=np.full(6, np.nan), dof=-1) for _ in range(4)]
+    down_seen = set()
+    for ps in range(ndn):
+        writes = []
+        for grp in range(4):
+            c, flags, vpo, _ = dn[ps * 4 + grp]
+            if c < 0:
+                continue
+            assert c not in down_seen
+            down_seen.add(int(c))
+            if flags & 1:
+                vp = vreg[grp]["v"]
+            else:
+                vp = v[vpo // 8:vpo // 8 + 6].copy() if vpo >= 0 else np.zeros(6)
+            xc = -(Ud[8 * c:8 * c + 6] @ vp) * Ud[8 * c + 6] - Ud[8 * c + 7]
+            vc = vp + Sarr[SS * c:SS * c + 6] * xc
+            vreg[grp] = dict(v=vc, dof=int(c))
+            if flags & 2:
+                writes.append((6 * c, vc))
+            x[c] = xc
+        for off, val in writes:
+            v[off:off + 6] = val
     assert np.isfinite(x).all()
+    skipped = set(range(rootdof, rootdof + 6)) if rootX >= 0 else set()
+    assert down_seen == seen - skipped
     # multipliers the KKT check forms for locked dofs
     f = np.zeros((m, 6))
     for t in range(m):
         a = task_dof[t]
         Kt, gt = _sym_unpack(XA[KS * t:KS * t + 21]), XA[KS * t + 21:KS * t + 27]
         f[t] = gt + (Kt @ v[6 * a:6 * a + 6] if a >= 0 else 0.0)
+    assert np.isfinite(f).all()
     lam = np.zeros(nv)
     for i in np.nonzero(locked)[0]:
         F = sum((f[t] for t in range(m) if (int(tmask[i]) & int(kkt)) >> t & 1), np.zeros(6))

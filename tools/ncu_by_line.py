@@ -40,6 +40,8 @@ def main():
     ap.add_argument("so")
     ap.add_argument("kernel", help="substring of the mangled kernel name")
     ap.add_argument("--top", type=int, default=30)
+    ap.add_argument("--ranges", default="", help="label=file:first-last,... : samples and instructions of source-line ranges "
+                    "(an inlined helper counts for the outermost line of that file in its inline chain)")
     args = ap.parse_args()
 
     tmp = tempfile.mkdtemp()
@@ -92,6 +94,13 @@ def main():
               "stall_long_sb", "stall_math", "stall_dispatch", "stall_mio"]
     stall_outer = collections.defaultdict(collections.Counter); inst_outer = collections.Counter()
     exc_line = collections.Counter(); wav_line = collections.Counter()
+    rng = []
+    for spec in filter(None, args.ranges.split(",")):
+        label, rest = spec.split("=")
+        f, ab = rest.split(":")
+        a, b = ab.split("-")
+        rng.append((label, f, int(a), int(b)))
+    rng_smp = collections.Counter(); rng_inst = collections.Counter(); rng_thr = collections.Counter(); rng_fp64 = collections.Counter()
     total = 0
     for r in rows[hdr_i + 1:]:
         if len(r) < len(hdr):
@@ -104,8 +113,15 @@ def main():
         ins = int(r[col["Instructions Executed"]] or 0)
         thr = int(r[col["Thread Instructions Executed"]] or 0)
         noi = int(r[col["stall_no_inst"]] or 0) if "stall_no_inst" in col else 0
-        cur, chain, _ = addr_line.get(off, (("?", 0), [("?", 0)], ""))
+        cur, chain, opcode = addr_line.get(off, (("?", 0), [("?", 0)], ""))
         fn = func_of(cur)
+        for label, f, a, b in rng:
+            hit = [fl for fl in chain if fl[0] == f]
+            if hit and a <= hit[-1][1] <= b:
+                rng_smp[label] += smp; rng_inst[label] += ins; rng_thr[label] += thr
+                if opcode.startswith(("DFMA", "DMUL", "DADD", "DSETP", "MUFU.RCP64H", "MUFU.RSQ64H")):
+                    rng_fp64[label] += ins
+                break
         # outermost stage function (the call made from gmr_clip.cuh)
         outer = fn
         for fl in chain:
@@ -136,6 +152,11 @@ def main():
     print("\n-- shared-memory wavefronts beyond the ideal (bank conflicts), top lines: excess, total")
     for (f, ln), x in exc_line.most_common(12):
         print(f"{x:14d} {wav_line[(f, ln)]:14d}  {f}:{ln}")
+    if rng:
+        print("\n-- source ranges: samples %, warp-instr executed, FP64 share, avg active threads")
+        for label, f, a, b in rng:
+            ie = rng_inst[label]
+            print(f"{100 * rng_smp[label] / total:6.2f}%  inst {ie:14d}  fp64 {100 * rng_fp64[label] / max(ie, 1):5.1f}%  thr/inst {rng_thr[label] / max(ie, 1):5.1f}  {label} ({f}:{a}-{b})")
     print("\n-- top lines")
     for (f, ln), s in by_line.most_common(args.top):
         print(f"{100 * s / total:6.2f}%  inst {inst_line[(f, ln)]:13d}  static {static_line[(f, ln)]:4d}  {f}:{ln}")
