@@ -466,7 +466,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.nlevel = nlevel; h.ref_body = ref_body;
   for (int k = 0; k < 2; k++) { h.use[k] = d->use_table[k] ? 1 : 0; h.n_task[k] = d->use_table[k] ? d->n_task[k] : 0; }
   h.max_iter = d->max_iter; h.damping = d->damping; h.converge_eps = d->converge_eps;
-  h.limit_gain = d->limit_gain; h.lm_damping = d->lm_damping; h.timestep = d->timestep;
+  h.limit_gain = d->limit_gain; h.lm_damping = d->lm_damping; h.timestep = d->timestep; h.inv_timestep = 1.0 / d->timestep;
   char* B0 = m->blob;
   h.body_parent = (const int*)(B0 + o_parent); h.body_pos = (const double*)(B0 + o_bpos);
   h.body_quat = (const double*)(B0 + o_bquat); h.body_jntadr = (const int*)(B0 + o_jadr);

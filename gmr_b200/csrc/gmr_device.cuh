@@ -28,7 +28,7 @@ struct DevModel {
   int nbody, njnt, nq, nv, n_human, n_scaled, nlevel, ref_body;
   int use[2], n_task[2];
   int max_iter;
-  double damping, converge_eps, limit_gain, lm_damping, timestep;
+  double damping, converge_eps, limit_gain, lm_damping, timestep, inv_timestep;
   // bodies
   const int* body_parent;    // [nbody]
   const double* body_pos;    // [nbody*3]
@@ -153,63 +153,6 @@ struct Lay {
 __device__ __forceinline__ int colbase(int n, int j) { return j * n - ((j * (j + 1)) >> 1); }
 __device__ __forceinline__ int tri(int i) { return i * (i + 1) / 2; }
 
-// ---------------------------------------------------------------- quaternion / vector helpers (wxyz)
-__device__ __forceinline__ void qmul(const double* a, const double* b, double* o) {
-  double w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
-  double x = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
-  double y = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
-  double z = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
-  o[0] = w; o[1] = x; o[2] = y; o[3] = z;
-}
-// v' = R(q) v
-__device__ __forceinline__ void qrot(const double* q, const double* v, double* o) {
-  double tx = 2.0 * (q[2] * v[2] - q[3] * v[1]);
-  double ty = 2.0 * (q[3] * v[0] - q[1] * v[2]);
-  double tz = 2.0 * (q[1] * v[1] - q[2] * v[0]);
-  double ox = v[0] + q[0] * tx + (q[2] * tz - q[3] * ty);
-  double oy = v[1] + q[0] * ty + (q[3] * tx - q[1] * tz);
-  double oz = v[2] + q[0] * tz + (q[1] * ty - q[2] * tx);
-  o[0] = ox; o[1] = oy; o[2] = oz;
-}
-// v' = R(q)^T v
-__device__ __forceinline__ void qrot_inv(const double* q, const double* v, double* o) {
-  double c[4] = {q[0], -q[1], -q[2], -q[3]};
-  qrot(c, v, o);
-}
-__device__ __forceinline__ void q2mat(const double* q, double* m) {
-  double w = q[0], x = q[1], y = q[2], z = q[3];
-  m[0] = 1 - 2 * (y * y + z * z); m[1] = 2 * (x * y - w * z); m[2] = 2 * (x * z + w * y);
-  m[3] = 2 * (x * y + w * z); m[4] = 1 - 2 * (x * x + z * z); m[5] = 2 * (y * z - w * x);
-  m[6] = 2 * (x * z - w * y); m[7] = 2 * (y * z + w * x); m[8] = 1 - 2 * (x * x + y * y);
-}
-__device__ __forceinline__ void normalize4(double* q) {   // mju_normalize4
-  double n2 = q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
-  if (n2 < 1e-30) { q[0] = 1; q[1] = q[2] = q[3] = 0; return; }
-  double inv = rsqrt(n2);
-  q[0] *= inv; q[1] *= inv; q[2] *= inv; q[3] *= inv;
-}
-__device__ __forceinline__ void cross3(const double* a, const double* b, double* o) {
-  double x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2], z = a[0] * b[1] - a[1] * b[0];
-  o[0] = x; o[1] = y; o[2] = z;
-}
-// C = A B (3x3 row-major); C may alias neither input
-__device__ __forceinline__ void mm3(const double* A, const double* B, double* C) {
-#pragma unroll
-  for (int i = 0; i < 3; i++)
-#pragma unroll
-    for (int j = 0; j < 3; j++) C[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
-}
-// C = A^T B
-__device__ __forceinline__ void mtm3(const double* A, const double* B, double* C) {
-#pragma unroll
-  for (int i = 0; i < 3; i++)
-#pragma unroll
-    for (int j = 0; j < 3; j++) C[3 * i + j] = A[i] * B[j] + A[3 + i] * B[3 + j] + A[6 + i] * B[6 + j];
-}
-__device__ __forceinline__ void skew3(const double* w, double* S) {
-  S[0] = 0; S[1] = -w[2]; S[2] = w[1]; S[3] = w[2]; S[4] = 0; S[5] = -w[0]; S[6] = -w[1]; S[7] = w[0]; S[8] = 0;
-}
-
 // ---------------------------------------------------------------- short reciprocal / root / arctangent
 // The library's double-precision 1/x, sqrt and atan2 carry slow paths for denormals, infinities and signed zeros
 // (20-150 instructions each, inlined at every call site of a kernel whose instruction footprint is what stalls it).
@@ -243,6 +186,63 @@ __device__ __forceinline__ double atan_ratio(double lo, double hi) {
   p = fma(p, s, -0.14285714266926733); p = fma(p, s, 0.1999999999964796); p = fma(p, s, -0.333333333333307);
   p = fma(p, s, 1.0);
   return p * t;
+}
+
+// ---------------------------------------------------------------- quaternion / vector helpers (wxyz)
+__device__ __forceinline__ void qmul(const double* a, const double* b, double* o) {
+  double w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+  double x = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  double y = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
+  double z = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+  o[0] = w; o[1] = x; o[2] = y; o[3] = z;
+}
+// v' = R(q) v
+__device__ __forceinline__ void qrot(const double* q, const double* v, double* o) {
+  double tx = 2.0 * (q[2] * v[2] - q[3] * v[1]);
+  double ty = 2.0 * (q[3] * v[0] - q[1] * v[2]);
+  double tz = 2.0 * (q[1] * v[1] - q[2] * v[0]);
+  double ox = v[0] + q[0] * tx + (q[2] * tz - q[3] * ty);
+  double oy = v[1] + q[0] * ty + (q[3] * tx - q[1] * tz);
+  double oz = v[2] + q[0] * tz + (q[1] * ty - q[2] * tx);
+  o[0] = ox; o[1] = oy; o[2] = oz;
+}
+// v' = R(q)^T v
+__device__ __forceinline__ void qrot_inv(const double* q, const double* v, double* o) {
+  double c[4] = {q[0], -q[1], -q[2], -q[3]};
+  qrot(c, v, o);
+}
+__device__ __forceinline__ void q2mat(const double* q, double* m) {
+  double w = q[0], x = q[1], y = q[2], z = q[3];
+  m[0] = 1 - 2 * (y * y + z * z); m[1] = 2 * (x * y - w * z); m[2] = 2 * (x * z + w * y);
+  m[3] = 2 * (x * y + w * z); m[4] = 1 - 2 * (x * x + z * z); m[5] = 2 * (y * z - w * x);
+  m[6] = 2 * (x * z - w * y); m[7] = 2 * (y * z + w * x); m[8] = 1 - 2 * (x * x + y * y);
+}
+__device__ __forceinline__ void normalize4(double* q) {   // mju_normalize4
+  double n2 = q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+  if (n2 < 1e-30) { q[0] = 1; q[1] = q[2] = q[3] = 0; return; }
+  double inv = rsqrt_pos(n2);
+  q[0] *= inv; q[1] *= inv; q[2] *= inv; q[3] *= inv;
+}
+__device__ __forceinline__ void cross3(const double* a, const double* b, double* o) {
+  double x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2], z = a[0] * b[1] - a[1] * b[0];
+  o[0] = x; o[1] = y; o[2] = z;
+}
+// C = A B (3x3 row-major); C may alias neither input
+__device__ __forceinline__ void mm3(const double* A, const double* B, double* C) {
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) C[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+}
+// C = A^T B
+__device__ __forceinline__ void mtm3(const double* A, const double* B, double* C) {
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) C[3 * i + j] = A[i] * B[j] + A[3 + i] * B[3 + j] + A[6 + i] * B[6 + j];
+}
+__device__ __forceinline__ void skew3(const double* w, double* S) {
+  S[0] = 0; S[1] = -w[2]; S[2] = w[1]; S[3] = w[2]; S[4] = 0; S[5] = -w[0]; S[6] = -w[1]; S[7] = w[0]; S[8] = 0;
 }
 
 __device__ __forceinline__ double warp_sum(double v) {

@@ -52,14 +52,14 @@ __device__ __forceinline__ bool stage_prep(const MV& mv, const Lay& lay, double*
     if (lane == 0) { pos[0] = s0 * r0; pos[1] = s0 * r1; pos[2] = s0 * r2; }
     else { pos[0] = (p[0] - r0) * sc + s0 * r0; pos[1] = (p[1] - r1) * sc + s0 * r1; pos[2] = (p[2] - r2) * sc + s0 * r2; }
     // scipy Rotation normalises on from_quat and the product is unit again
-    double n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
-    q[0] /= n; q[1] /= n; q[2] /= n; q[3] /= n;
+    double n = rsqrt_pos(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    q[0] *= n; q[1] *= n; q[2] *= n; q[3] *= n;
     const double* rop = mv(M.rot_off) + 4 * lane;
     double ro[4] = {rop[0], rop[1], rop[2], rop[3]};
     double uq[4];
     qmul(q, ro, uq);
-    n = sqrt(uq[0] * uq[0] + uq[1] * uq[1] + uq[2] * uq[2] + uq[3] * uq[3]);
-    uq[0] /= n; uq[1] /= n; uq[2] /= n; uq[3] /= n;
+    n = rsqrt_pos(uq[0] * uq[0] + uq[1] * uq[1] + uq[2] * uq[2] + uq[3] * uq[3]);
+    uq[0] *= n; uq[1] *= n; uq[2] *= n; uq[3] *= n;
     const double* pop = mv(M.pos_off) + 3 * lane;
     double po[3] = {pop[0], pop[1], pop[2]}, off[3];
     qrot(uq, po, off);
@@ -314,9 +314,9 @@ __device__ __forceinline__ double stage_stiffness(const MV& mv, const Lay& lay, 
 #pragma unroll
       for (int i = 0; i < 9; i++) { P[i] = Rt[i]; Pr[i] = 0; }
     } else {
-      const double th = sqrt(th2);
+      const double ith = rsqrt_pos(th2), th = th2 * ith, ith2 = ith * ith;       // th2 >= LIE_EPS here
       const double s = e[6], c = e[7];                                         // sin th, cos th from stage_errors
-      const double A = (1.0 / th2) * (1.0 - (th * s / (2.0 * (1.0 - c))));
+      const double A = ith2 * (1.0 - (th * s * 0.5 * rcp_pos(1.0 - c)));
       // products of skew matrices in closed form: [a]x[b]x = b a' - (a.b) I, so with cw = w.v, u = v x w:
       //   W^2 = w w' - th2 I,  WV = v w' - cw I,  VW = w v' - cw I,  WVW = -cw W,
       //   VWW = u w' - th2 V,  WWV = -(VWW)',  WVWW + WWVW = -2 cw W^2
@@ -326,8 +326,9 @@ __device__ __forceinline__ double stage_stiffness(const MV& mv, const Lay& lay, 
       cross3(ev, w, u);
       const double cw = w[0] * ev[0] + w[1] * ev[1] + w[2] * ev[2];
       // Barfoot Q(v, w)
-      const double Bc = (th - s) / (th2 * th), Cc = (1.0 - 0.5 * th2 - c) / (th2 * th2),
-                   Dc = (2.0 * th - 3.0 * s + th * c) / (2.0 * th2 * th2 * th);
+      const double ith3 = ith2 * ith;
+      const double Bc = (th - s) * ith3, Cc = (1.0 - 0.5 * th2 - c) * (ith2 * ith2),
+                   Dc = (2.0 * th - 3.0 * s + th * c) * (0.5 * ith3 * ith2);
       const double kV = 0.5 + 2.0 * Cc * th2, kW = -cw * (Bc + 3.0 * Cc), kI = -2.0 * cw * (Bc - Dc * th2), kWW = -2.0 * Dc * cw;
 #pragma unroll
       for (int i = 0; i < 3; i++)
@@ -992,25 +993,25 @@ __device__ __forceinline__ double tree_at(const MV& mv, const double* H, int i, 
 }
 
 // ------------------------------------------------------------------ Kernel 4: integrate
-// solve_ik returns v = dq/dt and integrate_inplace applies q <- q (+) v dt (mj_integratePos);
-// the divide/multiply is kept so rounding follows the reference.
+// solve_ik returns v = dq/dt and integrate_inplace applies q <- q (+) v dt (mj_integratePos); v is formed with the
+// host-computed 1/dt (one rounding away from the reference's division, far below the parity tolerances).
 template <class MV>
 __device__ __forceinline__ void stage_integrate(const MV& mv, const Lay& lay, double* sm, int lane) {
   const DevModel& M = mv.M();
   double* q = sm + lay.q;
   const double* x = sm + lay.x;
-  const double dt = M.timestep;
+  const double dt = M.timestep, idt = M.inv_timestep;
   for (int i = lane; i < M.nv; i += 32) {
     const int kind = mv(M.dof_kind)[i], qa = mv(M.dof_qadr)[i];
     if (kind == DOF_FREE_R) {
       if (qa >= 0) {     // first rotational dof of the free joint updates the quaternion
-        double w[3] = {x[i] / dt, x[i + 1] / dt, x[i + 2] / dt};
-        double n = sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+        double w[3] = {x[i] * idt, x[i + 1] * idt, x[i + 2] * idt};
+        const double n2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
         double quat[4] = {q[qa], q[qa + 1], q[qa + 2], q[qa + 3]};
         normalize4(quat);
-        if (n < 1e-15) { w[0] = 1; w[1] = w[2] = 0; n = 0; } else { const double in = 1.0 / n; w[0] *= in; w[1] *= in; w[2] *= in; }
-        const double ang = dt * n;
-        if (ang != 0.0) {
+        if (n2 >= 1e-30) {                                   // mju_quatIntegrate: nothing to do for |w| < 1e-15
+          const double in = rsqrt_pos(n2), ang = dt * (n2 * in);
+          w[0] *= in; w[1] *= in; w[2] *= in;
           double sh, ch;
           sincos(0.5 * ang, &sh, &ch);
           double qr[4] = {ch, sh * w[0], sh * w[1], sh * w[2]}, nq[4];
@@ -1020,7 +1021,7 @@ __device__ __forceinline__ void stage_integrate(const MV& mv, const Lay& lay, do
         q[qa] = quat[0]; q[qa + 1] = quat[1]; q[qa + 2] = quat[2]; q[qa + 3] = quat[3];
       }
     } else {
-      q[qa] += dt * (x[i] / dt);
+      q[qa] += dt * (x[i] * idt);
     }
   }
   __syncwarp();

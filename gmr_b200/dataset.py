@@ -25,45 +25,16 @@ def link_body_list(model) -> list:
     return list(model.body_names[1:])
 
 
-def retarget_clips(src_human: str, tgt_robot: str, clips, heights=None, human_names=None, fps=30.0,
-                   height_adjust: bool = False, root_origin_offset: bool = False, offset_to_ground: bool = False,
-                   device: int = 0):
-    """clips: list of [T_i, h, 7] arrays (pos xyz + quat wxyz per body, frames in order).
-    heights: actual_human_height per clip (or None).  fps: scalar or per clip.
-    height_adjust / root_origin_offset: the HEIGHT_ADJUST / ROOT_ORIGIN_OFFSET switches of the reference
-    drivers (smplx driver: both True, :118-131; bvh driver: both False, :127-142).
-    -> list of motion dicts (numpy), one per clip, in input order."""
-    B = len(clips)
-    if B == 0:
-        return []
-    lengths = np.array([c.shape[0] for c in clips], np.int32)
-    T = int(lengths.max())
-    h = clips[0].shape[1]
-    dm = DeviceModel.load(src_human, tgt_robot, human_names, device=device)
-    model = dm.desc.model
-    if h != dm.desc.c.n_human:
-        raise ValueError(f"clips carry {h} bodies per frame, the model expects {dm.desc.c.n_human}")
-    if model.jnt_type[0] != 0:
-        # the reference drivers slice qpos[:3] / [3:7] / [7:] whatever the robot; for a robot without a floating
-        # base (galaxea_r1pro) that slicing is meaningless (SURVEY.md 8a-R) - refuse rather than write garbage
-        raise ValueError(f"{tgt_robot} has no floating base: the dataset format (root_pos/root_rot/dof_pos) does not apply")
-    br = BatchedRetargeter(dm, B, device=device)
-    br.set_heights(heights if heights is not None else [None] * B)
-    br.set_order(work_order(lengths))
-    human = torch.zeros((B, T, h, 7), dtype=torch.float32, pin_memory=True)
-    hn = human.numpy()
-    for i, c in enumerate(clips):
-        hn[i, :lengths[i]] = c
-        hn[i, lengths[i]:, :, 3] = 1.0                       # padding frames: identity quaternions (never read)
-    qpos_host = br.retarget_clips_host(human, T_of=lengths, offset_to_ground=offset_to_ground)
-    torch.cuda.synchronize(device)
-    nq = model.nq
-    qpos = qpos_host.numpy()[:, :, :nq]
-
-    # ---- driver tail on the device, all valid frames of all clips at once
-    tdev = torch.device("cuda", device)
-    valid = np.arange(T)[None, :] < lengths[:, None]                  # [B,T]
-    flat = torch.from_numpy(qpos[valid]).to(tdev)                      # [N,nq] float64
+def driver_tail(dm: DeviceModel, qpos, lengths, height_adjust: bool = False, root_origin_offset: bool = False):
+    """The reference drivers' post-processing of the stacked retarget() results, for all clips at once
+    (scripts/bvh_to_robot_dataset.py:110-142, scripts/smplx_to_robot_dataset.py:97-131).
+    qpos [N,nq] float64 (clips back to back, clip i = ``lengths[i]`` rows) ->
+    dict(root_pos [N,3] f64, root_rot [N,4] f64 xyzw, dof_pos [N,nq-7] f64, local_body_pos [N,nb,3] f32).
+    Pinned by tests/golden/tail_*.npz (the reference's own lines run on CPU, tools/make_golden_tail.py)."""
+    lengths = np.asarray(lengths, np.int64)
+    B = len(lengths)
+    tdev = torch.device("cuda", dm.device)
+    flat = torch.as_tensor(np.ascontiguousarray(qpos, np.float64)).to(tdev)
     root_pos = flat[:, :3].clone()
     root_rot_xyzw = flat[:, [4, 5, 6, 3]].contiguous()                 # wxyz -> xyzw (:112 / :103)
     dof_pos = flat[:, 7:].contiguous()
@@ -82,21 +53,124 @@ def retarget_clips(src_human: str, tgt_robot: str, clips, heights=None, human_na
     if root_origin_offset:
         first = torch.from_numpy(np.concatenate([[0], np.cumsum(lengths)[:-1]])).to(tdev)
         root_pos[:, :2] -= root_pos[first][clip_of][:, :2]               # :128-131
-    root_pos, root_rot_xyzw, dof_pos = root_pos.cpu().numpy(), root_rot_xyzw.cpu().numpy(), dof_pos.cpu().numpy()
-    local_body_pos = local_body_pos.cpu().numpy()
+    return {"root_pos": root_pos.cpu().numpy(), "root_rot": root_rot_xyzw.cpu().numpy(), "dof_pos": dof_pos.cpu().numpy(),
+            "local_body_pos": local_body_pos.cpu().numpy()}
+
+
+def retarget_clips(src_human: str, tgt_robot: str, clips, heights=None, human_names=None, fps=30.0,
+                   height_adjust: bool = False, root_origin_offset: bool = False, offset_to_ground: bool = False,
+                   device: int = 0, stream_dtype=np.float64, return_status: bool = False, dof_vmax=None):
+    """clips: list of [T_i, h, 7] arrays (pos xyz + quat wxyz per body, frames in order).
+    heights: actual_human_height per clip (or None).  fps: scalar or per clip.
+    height_adjust / root_origin_offset: the HEIGHT_ADJUST / ROOT_ORIGIN_OFFSET switches of the reference
+    drivers (smplx driver: both True, :118-131; bvh driver: both False, :127-142).
+    stream_dtype: float64 feeds the solver the frames the reference's retarget() sees (its loaders produce float64);
+    float32 halves the bytes that cross the bus at the price of ~1e-7 m in the targets.
+    -> list of motion dicts (numpy), one per clip, in input order; a clip the engine flagged as failed (non-finite
+    input or output, QP search cap: abi.STATUS_FAILED) yields None - the drivers skip and report it like the
+    reference's per-file try/except (scripts/bvh_to_robot_dataset.py:75-80).  With return_status also the per-clip
+    OR of the frames' GMR_STATUS_* bits.
+    The clips go to the device as one CSR stream (back to back, nothing padded to the longest clip)."""
+    from .abi import STATUS_FAILED
+    B = len(clips)
+    if B == 0:
+        return ([], np.zeros(0, np.int32)) if return_status else []
+    lengths = np.array([c.shape[0] for c in clips], np.int64)
+    h = clips[0].shape[1]
+    from . import model_pack
+    from .abi import ModelDesc
+    from .ik_config import build_retarget_tables
+    from .synth import human_body_names
+    model, cfg = model_pack.load_pair(src_human, tgt_robot)
+    tables = build_retarget_tables(model, cfg, src_human, tgt_robot)
+    if human_names is None:
+        human_names = human_body_names(src_human, tables)
+    dm = DeviceModel(ModelDesc(model, tables, human_names, dof_vmax=dof_vmax), device)
+    if h != dm.desc.c.n_human:
+        raise ValueError(f"clips carry {h} bodies per frame, the model expects {dm.desc.c.n_human}")
+    if model.jnt_type[0] != 0:
+        # the reference drivers slice qpos[:3] / [3:7] / [7:] whatever the robot; for a robot without a floating
+        # base (galaxea_r1pro) that slicing is meaningless (SURVEY.md 8a-R) - refuse rather than write garbage
+        raise ValueError(f"{tgt_robot} has no floating base: the dataset format (root_pos/root_rot/dof_pos) does not apply")
+    br = BatchedRetargeter(dm, B, device=device)
+    br.set_heights(heights if heights is not None else [None] * B)
+    br.set_order(work_order(lengths))
+    clip_start = np.concatenate([[0], np.cumsum(lengths)]).astype(np.int64)
+    N = int(clip_start[-1])
+    human = torch.empty((N, h, 7), dtype=torch.float64 if np.dtype(stream_dtype) == np.float64 else torch.float32, pin_memory=True)
+    hn = human.numpy()
+    for i, c in enumerate(clips):
+        hn[clip_start[i]:clip_start[i + 1]] = c
+    qpos_host, status_host = br.retarget_clips_host_csr(human, clip_start, offset_to_ground=offset_to_ground)
+    torch.cuda.synchronize(device)
+    nq = model.nq
+    qpos = qpos_host.numpy()[:, :nq]
+    status = np.bitwise_or.reduceat(status_host.numpy(), clip_start[:-1][lengths > 0]) if (lengths > 0).any() else np.zeros(0, np.int32)
+    clip_status = np.zeros(B, np.int32)
+    clip_status[lengths > 0] = status
+    tail = driver_tail(dm, qpos, lengths, height_adjust, root_origin_offset)
     names = link_body_list(model)
     fps = np.broadcast_to(np.asarray(fps, np.float64), (B,))
-    out, o = [], 0
+    out = []
     for i in range(B):
-        n = int(lengths[i])
+        a, b = int(clip_start[i]), int(clip_start[i + 1])
+        if clip_status[i] & STATUS_FAILED:
+            out.append(None)
+            continue
         out.append({"fps": float(fps[i]) if float(fps[i]) != int(fps[i]) else int(fps[i]),
-                    "root_pos": root_pos[o:o + n].copy(), "root_rot": root_rot_xyzw[o:o + n].copy(),
-                    "dof_pos": dof_pos[o:o + n].copy(), "local_body_pos": local_body_pos[o:o + n].copy(),
+                    "root_pos": tail["root_pos"][a:b].copy(), "root_rot": tail["root_rot"][a:b].copy(),
+                    "dof_pos": tail["dof_pos"][a:b].copy(), "local_body_pos": tail["local_body_pos"][a:b].copy(),
                     "link_body_list": list(names)})
-        o += n
     br.close()
     dm.close()
-    return out
+    return (out, clip_status) if return_status else out
+
+
+def describe_status(bits: int) -> str:
+    from . import abi
+    names = [(abi.STATUS_MAX_ITER1, "stage 1 ended on max_iter"), (abi.STATUS_MAX_ITER2, "stage 2 ended on max_iter"),
+             (abi.STATUS_QP_CAP, "QP active-set search hit its cap"), (abi.STATUS_BAD_INPUT, "non-finite input frame"),
+             (abi.STATUS_BAD_OUTPUT, "non-finite qpos")]
+    return ", ".join(n for b, n in names if bits & b) or "ok"
+
+
+def save_motion_pt(path: str, motion: dict) -> None:
+    """The .pt form of a motion file (scripts/convert_motion_pkl_to_pt.py:39-56,89-91): the same dict with every
+    ndarray as a torch tensor, root_rot kept in xyzw, everything else verbatim, written with torch.save."""
+    d = os.path.dirname(path)
+    if d:
+        os.makedirs(d, exist_ok=True)
+    torch.save({k: (torch.from_numpy(v) if isinstance(v, np.ndarray) else v) for k, v in motion.items()}, path)
+
+
+def load_motion(path: str) -> dict:
+    """.pkl or .pt motion file -> dict of numpy arrays (the converter's load_any + to_pickle_dict, :26-56)."""
+    if path.endswith(".pt"):
+        obj = torch.load(path, map_location="cpu", weights_only=False)
+        if not isinstance(obj, dict):
+            raise TypeError("Expected dict in .pt file")
+        return {k: (v.detach().cpu().numpy() if isinstance(v, torch.Tensor) else v) for k, v in obj.items()}
+    with open(path, "rb") as f:
+        return pickle.load(f)
+
+
+def rank_info():
+    """(rank, world_size, local device) of this process when launched under torchrun, else (0, 1, None)."""
+    return (int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")),
+            int(os.environ["LOCAL_RANK"]) if "LOCAL_RANK" in os.environ else None)
+
+
+def shard_files(todo, rank: int, world: int):
+    """This rank's share of the (src, tgt) file list: the reference hands files to a process pool
+    (scripts/smplx_to_robot_dataset.py:241-242); here a rank is a GPU and the list is cut by
+    gmr_b200.shard.shard_clips on the files' sizes (bytes stand in for frames before anything is parsed), every
+    rank computing the same partition.  No communication: each rank loads, retargets and writes its own files."""
+    if world <= 1:
+        return list(todo)
+    from .shard import shard_clips
+    sizes = [os.path.getsize(s) for s, _ in todo]
+    mine = shard_clips(sizes, world)[rank]
+    return [todo[i] for i in sorted(mine.tolist())]
 
 
 def save_motion(path: str, motion: dict) -> None:

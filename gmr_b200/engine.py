@@ -232,6 +232,79 @@ class BatchedRetargeter:
         self._inflight.append((ev, human_host, qpos_host))
         return qpos_host
 
+    def run_csr(self, human, clip_start, offset_to_ground=False, diag=False, out=None):
+        """CSR form of run(): human [N,h,7] holds the clips back to back, clip i = rows clip_start[i]:clip_start[i+1]
+        (clip_start: B+1 int64, starting at 0).  -> qpos [N,nq_max] on the device (+ diag arrays with N rows).
+        Nothing is padded to the longest clip."""
+        t = torch.as_tensor(human)
+        if t.dtype not in (torch.float32, torch.float64):
+            t = t.double()
+        t = t.to(self.tdev, non_blocking=True).contiguous()
+        cs = np.ascontiguousarray(clip_start, np.int64)
+        if cs.shape != (self.B + 1,) or cs[0] != 0 or (np.diff(cs) < 0).any():
+            raise ValueError("clip_start must be B+1 non-decreasing int64 offsets starting at 0")
+        N = int(cs[-1])
+        if t.dim() != 3 or t.shape[0] != N or t.shape[1] != self.h_max or t.shape[2] != 7:
+            raise ValueError(f"human stream must be [N={N},h={self.h_max},7], got {tuple(t.shape)}")
+        qpos = out if out is not None else torch.zeros((N, self.nq_max), dtype=torch.float64, device=self.tdev)
+        dout, d = {}, None
+        if diag:
+            dout = {"err": torch.zeros((N, 2), dtype=torch.float64, device=self.tdev),
+                    "iters": torch.zeros((N, 2), dtype=torch.int32, device=self.tdev),
+                    "nfact": torch.zeros((N,), dtype=torch.int32, device=self.tdev),
+                    "status": torch.zeros((N,), dtype=torch.int32, device=self.tdev)}
+            d = gmr_diag(dout["err"].data_ptr(), dout["iters"].data_ptr(), dout["nfact"].data_ptr(), dout["status"].data_ptr())
+        cs_dev = torch.from_numpy(cs).to(self.tdev)
+        T_max = int(np.diff(cs).max()) if self.B else 0
+        if N:
+            _lib.check(_lib.lib().gmr_batch_run_csr(self._h, _ptr(t), F32 if t.dtype == torch.float32 else F64, _ptr(cs_dev),
+                                                    max(T_max, 1), int(bool(offset_to_ground)), _ptr(qpos),
+                                                    C.byref(d) if d is not None else None), "gmr_batch_run_csr")
+        return (qpos, dout) if diag else qpos
+
+    def retarget_clips_host_csr(self, human_host, clip_start, qpos_host=None, status_host=None, offset_to_ground=False,
+                                cold_start=True):
+        """CSR form of retarget_clips_host(): human_host [N,h,7] (torch CPU tensor; pinned = zero-copy), clip_start
+        B+1 int64 -> (qpos_host [N,nq_max] float64, status_host [N] int32 GMR_STATUS_* bits), both pinned.
+        One C-ABI call (gmr_batch_run_host_csr); asynchronous on the batch's stream."""
+        human_host = torch.as_tensor(human_host)
+        if human_host.is_cuda:
+            raise ValueError("retarget_clips_host_csr takes host buffers; use run_csr() for device tensors")
+        if human_host.dtype not in (torch.float32, torch.float64):
+            human_host = human_host.double()
+        human_host = human_host.contiguous()
+        cs = np.ascontiguousarray(clip_start, np.int64)
+        if cs.shape != (self.B + 1,) or cs[0] != 0 or (np.diff(cs) < 0).any():
+            raise ValueError("clip_start must be B+1 non-decreasing int64 offsets starting at 0")
+        N = int(cs[-1])
+        if human_host.dim() != 3 or human_host.shape[0] != N or human_host.shape[1] != self.h_max or human_host.shape[2] != 7:
+            raise ValueError(f"human stream must be [N={N},h={self.h_max},7], got {tuple(human_host.shape)}")
+        if qpos_host is None:
+            qpos_host = torch.zeros((N, self.nq_max), dtype=torch.float64, pin_memory=True)
+        if status_host is None:
+            status_host = torch.zeros((N,), dtype=torch.int32, pin_memory=True)
+        if qpos_host.dtype != torch.float64 or tuple(qpos_host.shape) != (N, self.nq_max) or not qpos_host.is_contiguous():
+            raise ValueError("qpos_host must be a contiguous float64 [N,nq_max] host tensor")
+        if status_host.dtype != torch.int32 or tuple(status_host.shape) != (N,):
+            raise ValueError("status_host must be an int32 [N] host tensor")
+        _lib.check(_lib.lib().gmr_batch_run_host_csr(
+            self._h, C.c_void_p(human_host.data_ptr()), F32 if human_host.dtype == torch.float32 else F64,
+            cs.ctypes.data_as(C.c_void_p), int(bool(offset_to_ground)), int(bool(cold_start)),
+            C.c_void_p(qpos_host.data_ptr()), C.c_void_p(status_host.data_ptr())), "gmr_batch_run_host_csr")
+        ev = torch.cuda.Event()
+        ev.record(self.stream)
+        self._inflight = [x for x in getattr(self, "_inflight", []) if not x[0].query()]
+        self._inflight.append((ev, human_host, qpos_host, status_host, cs))
+        return qpos_host, status_host
+
+    def step_host(self, human_host, qpos_host, scaled_host=None, offset_to_ground=False, sync=True):
+        """One retarget() for every instance straight from / to pinned host tensors (gmr_batch_step_host): no staging
+        copies, one launch; with sync the result is readable on return."""
+        _lib.check(_lib.lib().gmr_batch_step_host(
+            self._h, C.c_void_p(human_host.data_ptr()), F32 if human_host.dtype == torch.float32 else F64,
+            int(bool(offset_to_ground)), C.c_void_p(qpos_host.data_ptr()),
+            None if scaled_host is None else C.c_void_p(scaled_host.data_ptr()), int(bool(sync))), "gmr_batch_step_host")
+
     def step(self, human, offset_to_ground=False, diag=False, want_scaled=False):
         """One retarget() call for every instance: human [B,h,7] -> qpos [B,nq_max]."""
         h, dt = self._human(human, 3)

@@ -159,21 +159,32 @@ class GeneralMotionRetargeting:
         if keep_state is not None:
             self._br.reset(keep_state)
         self._key = self._offsets_key()
+        self._scale_key = None
+        # page-locked buffers of the per-frame call, allocated once: the kernel reads the frame from, and writes
+        # qpos and the scaled targets to, host memory directly (gmr_batch_step_host: one launch, one sync per frame)
+        s, nq = len(self._names), self._br.nq_max
+        self._frame = torch.zeros((1, s, 7), dtype=torch.float64, pin_memory=True)
+        self._out = torch.zeros((nq + self._br.s_max * 7,), dtype=torch.float64, pin_memory=True)
+        self._frame_np, self._out_np = self._frame.numpy(), self._out.numpy()
+        self._qpos_view = self._out[:nq].view(1, nq)
+        self._scaled_view = self._out[nq:].view(1, self._br.s_max, 7)
 
     def _sync_tables(self):
         if self._offsets_key() != self._key:
             self._build_engine(keep_state=self._br.state())
-        sc = np.array([[self.human_scale_table[b] for b in self._names]], np.float64)
-        self._br.set_scale(sc)
+        key = tuple(self.human_scale_table[b] for b in self._names)     # re-read every frame like the reference (:120)
+        if key != self._scale_key:
+            self._br.set_scale(np.array([key], np.float64))
+            self._scale_key = key
 
     # ------------------------------------------------------------------ hot path
     def _pack(self, human_data):
-        frame = np.zeros((1, len(self._names), 7))
+        frame = self._frame_np
         for i, b in enumerate(self._names):
             pos, quat = human_data[b]                 # KeyError like the reference (:213 / :129)
             frame[0, i, :3] = pos
             frame[0, i, 3:] = quat
-        return frame
+        return self._frame
 
     def _unpack_scaled(self, scaled):
         out = {}
@@ -191,10 +202,11 @@ class GeneralMotionRetargeting:
     def retarget(self, human_data, offset_to_ground=False):
         human_data = self.to_numpy(human_data)
         self._sync_tables()
-        qpos, scaled = self._br.step(self._pack(human_data), offset_to_ground, want_scaled=True)
-        self._last_scaled = scaled
-        self.scaled_human_data = self._unpack_scaled(scaled[0].cpu().numpy())
-        return qpos[0, :self.model.nq].cpu().numpy().copy()
+        self._br.step_host(self._pack(human_data), self._qpos_view, self._scaled_view, offset_to_ground, sync=True)
+        nq = self.model.nq
+        self._last_scaled = self._scaled_view.clone()
+        self.scaled_human_data = self._unpack_scaled(self._out_np[self._br.nq_max:].reshape(-1, 7))
+        return self._out_np[:nq].copy()
 
     # ------------------------------------------------------------------ diagnostics
     def _qpos(self):
@@ -243,17 +255,22 @@ class GeneralMotionRetargeting:
                 pos_off[i] = pos_offsets[b]
                 rot_off[i] = rot_offsets[b].as_quat(scalar_first=True)
         t = self._tables
-        tt = RetargetTables(t.src_human, t.tgt_robot, names[0], t.robot_root_name, 0.0, t.human_height_assumption,
-                            (False, False), names, np.asarray(scale, np.float64), pos_off, rot_off,
-                            np.zeros(s, np.int32), [np.zeros(0, np.int32)] * 2, [np.zeros(0, np.int32)] * 2,
-                            [np.zeros(0)] * 2, [np.zeros(0)] * 2, [[], []], {})
-        dm = DeviceModel(ModelDesc(self._robot, tt, names), self._device)
-        br = BatchedRetargeter(dm, 1)
+        key = (tuple(names), pos_off.tobytes(), rot_off.tobytes())
+        cache = self.__dict__.setdefault("_prep_cache", {})
+        if key not in cache:
+            if len(cache) >= 4:                            # a handful of layouts at most (fbx_to_robot.py:1003-1041)
+                _, (odm, obr) = cache.popitem()
+                obr.close(); odm.close()
+            tt = RetargetTables(t.src_human, t.tgt_robot, names[0], t.robot_root_name, 0.0, t.human_height_assumption,
+                                (False, False), names, np.ones(s), pos_off, rot_off,
+                                np.zeros(s, np.int32), [np.zeros(0, np.int32)] * 2, [np.zeros(0, np.int32)] * 2,
+                                [np.zeros(0)] * 2, [np.zeros(0)] * 2, [[], []], {})
+            dm = DeviceModel(ModelDesc(self._robot, tt, names), self._device)
+            cache[key] = (dm, BatchedRetargeter(dm, 1))
+        dm, br = cache[key]
+        br.set_scale(np.asarray(scale, np.float64)[None])
         frame = np.zeros((1, s, 7))
         for i, b in enumerate(names):
             frame[0, i, :3], frame[0, i, 3:] = human_data[b][0], human_data[b][1]
         out = br.target_prep(frame, False)[0].cpu().numpy()
-        res = {b: [out[i, :3].copy(), out[i, 3:].copy()] for i, b in enumerate(names)}
-        br.close()
-        dm.close()
-        return res
+        return {b: [out[i, :3].copy(), out[i, 3:].copy()] for i, b in enumerate(names)}

@@ -160,8 +160,10 @@ def frame_task_jacobian(m, k: Kin, body: int, tq, tp):
     return -jlog @ jb
 
 
-def configuration_limit(m, q, gain=0.95):
+def configuration_limit(m, q, gain=0.95, vmax=None, dt=None):
     """mink ConfigurationLimit (default limit set of solve_ik): box on limited hinge/slide dofs.
+    vmax [nv] (optional, not used by the reference - motion_retarget.py:147-149 passes no limits): mink
+    VelocityLimit, |dq| <= vmax * dt, intersected with the position box.
 
     Returns (lo[nv], hi[nv]) with +-inf where unconstrained:  lo <= dq <= hi.
     """
@@ -173,10 +175,13 @@ def configuration_limit(m, q, gain=0.95):
         qa, da = m.jnt_qposadr[j], m.jnt_dofadr[j]
         hi[da] = gain * (m.jnt_range[j, 1] - q[qa])
         lo[da] = -gain * (q[qa] - m.jnt_range[j, 0])
+    if vmax is not None:
+        hi = np.minimum(hi, np.asarray(vmax) * dt)
+        lo = np.maximum(lo, -np.asarray(vmax) * dt)
     return lo, hi
 
 
-def build_ik(m, k: Kin, q, tasks, damping):
+def build_ik(m, k: Kin, q, tasks, damping, vmax=None):
     """mink build_ik: H, c, lo, hi.  tasks = list of (body, wpos, wrot, tq, tp)."""
     H = np.eye(m.nv) * damping
     c = np.zeros(m.nv)
@@ -190,7 +195,7 @@ def build_ik(m, k: Kin, q, tasks, damping):
         mu = 1.0 * (We @ We)                  # lm_damping = 1 (motion_retarget.py:88,106)
         H += WJ.T @ WJ + mu * np.eye(m.nv)
         c += -We @ WJ
-    lo, hi = configuration_limit(m, q)
+    lo, hi = configuration_limit(m, q, vmax=vmax, dt=m.timestep)
     return H, c, lo, hi
 
 
@@ -236,8 +241,8 @@ def solve_box_qp(H, c, lo, hi, ptol=1e-10, dtol=1e-9, max_iter=200):
     raise RuntimeError("box QP did not terminate")
 
 
-def solve_ik(m, k: Kin, q, tasks, dt, damping):
-    H, c, lo, hi = build_ik(m, k, q, tasks, damping)
+def solve_ik(m, k: Kin, q, tasks, dt, damping, vmax=None):
+    H, c, lo, hi = build_ik(m, k, q, tasks, damping, vmax=vmax)
     dq, nfac = solve_box_qp(H, c, lo, hi)
     return dq / dt, nfac
 
@@ -250,12 +255,13 @@ class OracleRetargeter:
     flattened tables (gmr_b200.mjcf.RobotModel + gmr_b200.ik_config.RetargetTables)."""
 
     def __init__(self, model, tables, actual_human_height=None, solver="daqp", damping=5e-1,
-                 verbose=False):
+                 verbose=False, dof_vmax=None):
         self.m = model
         self.t = tables
         ratio = 1.0 if actual_human_height is None else actual_human_height / tables.human_height_assumption
         self.scale = tables.scale * ratio                       # :36-43
         self.damping = damping
+        self.dof_vmax = dof_vmax                                 # optional velocity box (None = the reference)
         self.max_iter = 10                                       # :56
         self.q = model.qpos0.copy()                              # mink.Configuration(model), :75
         self.kin = mj_kinematics(model, self.q)
@@ -305,7 +311,7 @@ class OracleRetargeter:
 
     def _step(self, tasks):
         dt = self.m.timestep
-        v, nfac = solve_ik(self.m, self.kin, self.q, tasks, dt, self.damping)
+        v, nfac = solve_ik(self.m, self.kin, self.q, tasks, dt, self.damping, vmax=self.dof_vmax)
         self.q = mj_integrate_pos(self.m, self.q, v, dt)
         self.kin = mj_kinematics(self.m, self.q)
         self.stats["solves"] += 1

@@ -16,19 +16,47 @@ def _clips(src, robot, lengths, seed=9):
     return m, t, [human[i, :n] for i, n in enumerate(lengths)], heights, names, human
 
 
-@pytest.mark.parametrize("adjust", [False, True])
-def test_motion_dicts_match_the_reference_tail(adjust, tmp_path):
-    import torch
-    from gmr_b200 import dataset, synth
+def _golden_tail(tag):
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"tail_{tag}.npz"), allow_pickle=False)
+    return {k: z[k] for k in z.files}
+
+
+@pytest.mark.parametrize("tag,adjust", [("bvh_unitree_g1", False), ("smplx_unitree_g1", True), ("smplx_booster_t1", True)])
+def test_driver_tail_matches_the_reference_lines(tag, adjust):
+    """dataset.driver_tail on known qpos against tests/golden/tail_*.npz = the reference drivers' OWN post-processing
+    lines executed on CPU (tools/make_golden_tail.py: scripts/bvh_to_robot_dataset.py:107-151 with HEIGHT_ADJUST
+    off, scripts/smplx_to_robot_dataset.py:93-141 with HEIGHT_ADJUST and ROOT_ORIGIN_OFFSET on)."""
+    from gmr_b200 import dataset
     from gmr_b200.engine import DeviceModel
-    from oracle import oracle as oc
-    lengths = [17, 5, 30, 1, 22]
+    g = _golden_tail(tag)
+    lengths = [int(n) for n in g["lengths"]]
+    dm = DeviceModel.load(str(g["source"]), str(g["robot"]))
+    qpos = np.concatenate([g[f"qpos_{i}"] for i in range(len(lengths))])
+    tail = dataset.driver_tail(dm, qpos, lengths, height_adjust=adjust, root_origin_offset=adjust)
+    assert list(g["link_body_list"]) == dataset.link_body_list(dm.desc.model)
+    o = 0
+    for i, n in enumerate(lengths):
+        np.testing.assert_array_equal(tail["root_rot"][o:o + n], g[f"root_rot_{i}"])            # a permutation: exact
+        np.testing.assert_array_equal(tail["dof_pos"][o:o + n], g[f"dof_pos_{i}"])
+        assert tail["local_body_pos"].dtype == np.float32 and g[f"local_body_pos_{i}"].dtype == np.float32
+        np.testing.assert_allclose(tail["local_body_pos"][o:o + n], g[f"local_body_pos_{i}"], atol=2e-6)   # float32 FK chain
+        np.testing.assert_allclose(tail["root_pos"][o:o + n], g[f"root_pos_{i}"], atol=2e-6 if adjust else 0)
+        if adjust:
+            assert tail["root_pos"][o, 0] == 0 and tail["root_pos"][o, 1] == 0
+        o += n
+    dm.close()
+
+
+def test_motion_dicts_match_the_reference_tail(tmp_path):
+    """Whole driver path (CSR host call + tail) on the clips the golden file was made from: qpos from the CUDA
+    path, tail from the reference's lines on the oracle's qpos; structural checks of the reference's smoke_test.py."""
+    from gmr_b200 import dataset
+    g = _golden_tail("bvh_unitree_g1")
+    lengths = [int(n) for n in g["lengths"]]
     m, t, clips, heights, names, human = _clips("bvh", "unitree_g1", lengths)
-    motions = dataset.retarget_clips("bvh", "unitree_g1", clips, heights=heights, human_names=names, fps=30,
-                                     height_adjust=adjust, root_origin_offset=adjust)
-    dm = DeviceModel.load("bvh", "unitree_g1", names)
-    ref = oc.run_clips(dm.desc, human, T_of=np.array(lengths, np.int32), scale=synth.clip_scales(t, heights), nthreads=4)["qpos"]
-    assert len(motions) == len(lengths)
+    motions, status = dataset.retarget_clips("bvh", "unitree_g1", clips, heights=heights, human_names=names, fps=30,
+                                             return_status=True)
+    assert len(motions) == len(lengths) and not (status & 28).any()
     for i, (mo, n) in enumerate(zip(motions, lengths)):
         # smoke_test.py:19-72 structural checks
         assert set(mo) == {"fps", "root_pos", "root_rot", "dof_pos", "local_body_pos", "link_body_list"}
@@ -37,25 +65,36 @@ def test_motion_dicts_match_the_reference_tail(adjust, tmp_path):
         assert len(mo["link_body_list"]) == m.nbody - 1 and mo["fps"] == 30
         norms = np.linalg.norm(mo["root_rot"], axis=-1)
         assert (norms > 0.5).all() and (norms < 1.5).all()
-        q = ref[i, :n]
-        np.testing.assert_allclose(mo["root_rot"], q[:, [4, 5, 6, 3]], atol=1e-7)           # xyzw
-        np.testing.assert_allclose(mo["dof_pos"], q[:, 7:], atol=1e-7)
-        # FK tail with identity root == golden-tested kernel on the oracle's dof_pos
-        ident = torch.zeros((n, 4), device="cuda"); ident[:, 3] = 1
-        lbp, _ = dm.fk_bodies_f32(torch.zeros((n, 3), device="cuda"), ident, torch.from_numpy(q[:, 7:]).cuda().float(), want_rot=False)
-        np.testing.assert_allclose(mo["local_body_pos"], lbp.cpu().numpy(), atol=1e-5)
-        rp = q[:, :3].copy()
-        if adjust:
-            bp, _ = dm.fk_bodies_f32(torch.from_numpy(q[:, :3]).cuda().float(), torch.from_numpy(q[:, [4, 5, 6, 3]]).cuda().float(),
-                                     torch.from_numpy(q[:, 7:]).cuda().float(), want_rot=False)
-            rp[:, 2] -= float(bp[..., 2].min().item())
-            rp[:, :2] -= rp[0, :2].copy()
-            assert abs(mo["root_pos"][0, 0]) < 1e-12 and abs(mo["root_pos"][0, 1]) < 1e-12
-        np.testing.assert_allclose(mo["root_pos"], rp, atol=2e-6)
+        np.testing.assert_allclose(mo["root_rot"], g[f"root_rot_{i}"], atol=1e-7)
+        np.testing.assert_allclose(mo["dof_pos"], g[f"dof_pos_{i}"], atol=1e-7)
+        np.testing.assert_allclose(mo["root_pos"], g[f"root_pos_{i}"], atol=1e-7)
+        np.testing.assert_allclose(mo["local_body_pos"], g[f"local_body_pos_{i}"], atol=1e-5)
     p = tmp_path / "a" / "b.pkl"
     dataset.save_motion(str(p), motions[0])
     back = pickle.load(open(p, "rb"))
     np.testing.assert_array_equal(back["dof_pos"], motions[0]["dof_pos"])
+    # .pt form (scripts/convert_motion_pkl_to_pt.py): tensors, xyzw kept, other fields verbatim
+    import torch
+    dataset.save_motion_pt(str(tmp_path / "a" / "b.pt"), motions[0])
+    pt = torch.load(tmp_path / "a" / "b.pt", weights_only=False)
+    assert isinstance(pt["root_rot"], torch.Tensor) and pt["link_body_list"] == motions[0]["link_body_list"] and pt["fps"] == 30
+    np.testing.assert_array_equal(dataset.load_motion(str(tmp_path / "a" / "b.pt"))["root_rot"], motions[0]["root_rot"])
+
+
+def test_failed_clip_is_flagged_and_skipped():
+    """A non-finite frame poisons its own clip only; the driver gets None for it and the status bits say why."""
+    from gmr_b200 import abi, dataset
+    lengths = [9, 12, 7]
+    m, t, clips, heights, names, human = _clips("bvh", "unitree_g1", lengths, seed=4)
+    ok = dataset.retarget_clips("bvh", "unitree_g1", clips, heights=heights, human_names=names)
+    bad = [c.copy() for c in clips]
+    bad[1][5, 3, 0] = np.nan
+    motions, status = dataset.retarget_clips("bvh", "unitree_g1", bad, heights=heights, human_names=names, return_status=True)
+    assert motions[1] is None and (status[1] & abi.STATUS_BAD_INPUT) and (status[1] & abi.STATUS_BAD_OUTPUT)
+    assert "non-finite" in dataset.describe_status(int(status[1]))
+    for i in (0, 2):
+        assert not status[i] & abi.STATUS_FAILED
+        np.testing.assert_array_equal(motions[i]["dof_pos"], ok[i]["dof_pos"])
 
 
 def test_pending_files_skip_logic(tmp_path):

@@ -393,3 +393,114 @@ def test_two_tasks_on_one_dof():
     ref = oc.run_clips(dm.desc, human, scale=synth.clip_scales(t2, heights), nthreads=8)
     assert _check_clip(qpos.cpu().numpy()[..., :m.nq], ref["qpos"], m, "merged tasks") < 1e-7
     np.testing.assert_array_equal(diag["iters"].cpu().numpy(), ref["iters"])
+
+
+def test_csr_stream_is_bit_identical_to_the_dense_layout():
+    """gmr_batch_run_csr / gmr_batch_run_host_csr (clips back to back, no padding) == gmr_batch_run on [B,T_max,h,7]."""
+    import torch
+    B, T = 21, 45
+    m, t, dm, br, human, heights = _setup("bvh", "unitree_g1", B, T, seed=8)
+    T_of = np.random.default_rng(2).integers(0, T + 1, size=B).astype(np.int32)
+    T_of[3], T_of[7] = T, 1                                          # longest, shortest, and (maybe) empty clips
+    T_of[11] = 0
+    br.set_order(np.argsort(-T_of, kind="stable").astype(np.int32))
+    dense, ddiag = br.run(human, T_of=T_of, diag=True)
+    dense = dense.cpu().numpy()
+    cs = np.concatenate([[0], np.cumsum(T_of)]).astype(np.int64)
+    flat = np.concatenate([human[b, :T_of[b]] for b in range(B)])
+    br.reset()
+    got, gdiag = br.run_csr(flat, cs, diag=True)
+    got = got.cpu().numpy()
+    for b in range(B):
+        np.testing.assert_array_equal(got[cs[b]:cs[b + 1]], dense[b, :T_of[b]])
+        np.testing.assert_array_equal(gdiag["iters"][cs[b]:cs[b + 1]].cpu().numpy(), ddiag["iters"][b, :T_of[b]].cpu().numpy())
+        np.testing.assert_array_equal(gdiag["status"][cs[b]:cs[b + 1]].cpu().numpy(), ddiag["status"][b, :T_of[b]].cpu().numpy())
+    for pinned in (True, False):                                     # zero-copy / staged host forms
+        hh = torch.from_numpy(flat)
+        q, st = br.retarget_clips_host_csr(hh.pin_memory() if pinned else hh,
+                                           cs, qpos_host=None if pinned else torch.zeros((len(flat), br.nq_max), dtype=torch.float64),
+                                           status_host=None if pinned else torch.zeros((len(flat),), dtype=torch.int32))
+        torch.cuda.synchronize()
+        np.testing.assert_array_equal(q.numpy(), got)
+        np.testing.assert_array_equal(st.numpy(), gdiag["status"].cpu().numpy())
+
+
+def test_status_flags():
+    """gmr_diag.status_dev: max_iter bits == the loop counters, bad input / output bits on a NaN frame only."""
+    from gmr_b200 import abi
+    B, T = 32, 30
+    m, t, dm, br, human, heights = _setup("bvh", "unitree_g1", B, T, seed=13)
+    h = human.copy()
+    h[5, 12, 2, 1] = np.inf
+    qpos, diag = br.run(h, diag=True)
+    st, it = diag["status"].cpu().numpy(), diag["iters"].cpu().numpy()
+    ok = np.ones((B, T), bool)
+    ok[5, 12:] = False                                               # the poisoned tail of clip 5
+    for k, bit in enumerate((abi.STATUS_MAX_ITER1, abi.STATUS_MAX_ITER2)):
+        hit = ((st & bit) != 0) & ok
+        assert (it[..., k][hit] == 11).all()                         # the counter ran out: 1 + max_iter solves
+        # 11 solves without the bit = the 11th solve converged; fewer solves never carry the bit
+        assert not (((st & bit) != 0) & ok & (it[..., k] < 11)).any()
+    assert ((st & abi.STATUS_MAX_ITER1) != 0)[:, 0].any()            # cold starts run out of iterations
+    bad_in = (st & abi.STATUS_BAD_INPUT) != 0
+    assert bad_in[5, 12] and bad_in.sum() == 1
+    bad_out = (st & abi.STATUS_BAD_OUTPUT) != 0
+    assert bad_out[5, 12:].all() and not bad_out[5, :12].any() and bad_out.sum() == T - 12
+    assert not (st & abi.STATUS_QP_CAP).any()
+    assert np.isfinite(qpos.cpu().numpy()[np.arange(B) != 5]).all()
+
+
+def test_velocity_limit_box():
+    """Optional |dq| <= vmax dt box (gmr_model_desc.dof_vmax; off by default = the reference): CUDA == oracle with the
+    same box, every step inside it, and NULL == +inf == the unlimited run bit for bit."""
+    import torch
+    from gmr_b200 import model_pack, synth
+    from gmr_b200.abi import ModelDesc
+    from gmr_b200.engine import BatchedRetargeter, DeviceModel
+    from oracle.gmr_oracle_np import OracleRetargeter
+    B, T = 4, 10
+    m, t = model_pack.build_tables("bvh", "unitree_g1")
+    human, heights, names = synth.synth_human_clips(m, t, "bvh", B=B, T=T, seed=17, dtype=np.float64)
+    idx = [names.index(b) for b in t.scaled_names]
+    vmax = 2.0                                                       # rad/s: 0.004 rad per solve at dt = 0.002
+    runs = {}
+    for key, vm in (("off", None), ("inf", np.full(m.nv, np.inf)), ("on", vmax)):
+        dm = DeviceModel(ModelDesc(m, t, names, dof_vmax=vm))
+        br = BatchedRetargeter(dm, B)
+        br.set_heights(heights)
+        runs[key] = br.run(human).cpu().numpy()[..., :m.nq]
+        if key == "on":
+            scaled = br.target_prep(human[:, 0])
+            br.reset()
+            dq, _ = br.solve_ik(0, scaled)
+            assert np.abs(dq.cpu().numpy()[:, 6:m.nv]).max() <= vmax * m.timestep + 1e-12
+            vfull = dm.desc.dof_vmax
+        br.close(); dm.close()
+    np.testing.assert_array_equal(runs["off"], runs["inf"])
+    assert np.abs(runs["on"] - runs["off"]).max() > 1e-3             # the box binds on a cold start
+    for b in range(B):
+        ref = OracleRetargeter(m, t, actual_human_height=float(heights[b]), dof_vmax=vfull)
+        for i in range(T):
+            np.testing.assert_allclose(runs["on"][b, i], ref.retarget(human[b, i][idx]), atol=1e-7)
+    with pytest.raises(Exception, match="free joint"):
+        DeviceModel(ModelDesc(m, t, names, dof_vmax=np.full(m.nv, 1.0)))
+
+
+def test_two_batches_of_different_footprint_alternate():
+    """The dynamic shared-memory opt-in of clip_kernel is per function and process-wide: creating a smaller batch
+    (other robot, narrower CTA) must not break the next launch of a larger one."""
+    mA, tA, dmA, brA, humanA, _ = _setup("smplx", "unitree_g1_with_hands", 64, 6, seed=1)
+    first = brA.run(humanA).cpu().numpy()
+    mB, tB, dmB, brB, humanB, _ = _setup("smplx", "galaxea_r1pro", 3, 6, seed=2)      # 3 warps per CTA, small blocks
+    small = brB.run(humanB).cpu().numpy()
+    brA.reset()
+    np.testing.assert_array_equal(brA.run(humanA).cpu().numpy(), first)
+    brB.reset()
+    np.testing.assert_array_equal(brB.run(humanB).cpu().numpy(), small)
+
+
+def test_set_order_rejects_non_permutations():
+    m, t, dm, br, human, heights = _setup("bvh", "unitree_g1", 6, 2)
+    with pytest.raises(ValueError):
+        br.set_order([0, 1, 1, 3, 4, 5])
+    br.set_order([5, 4, 3, 2, 1, 0])

@@ -95,3 +95,37 @@ def test_scale_and_offset_helpers():
     for b in t.scaled_names:
         np.testing.assert_allclose(off[b][0], gmr.scaled_human_data[b][0], atol=1e-12)
         np.testing.assert_allclose(off[b][1], gmr.scaled_human_data[b][1], atol=1e-12)
+
+
+def test_helpers_then_retarget_like_the_fbx_script():
+    """scripts/fbx_to_robot.py:1003-1041: scale_human_data / offset_human_data (helper batches of another footprint)
+    between retarget() calls; the helpers must not disturb the main batch's launches or its warm start."""
+    from gmr_b200.motion_retarget import GeneralMotionRetargeting
+    from oracle.gmr_oracle_np import OracleRetargeter
+    m, t, human, height, names, frames = _frames("bvh", "unitree_g1", 5)
+    gmr = GeneralMotionRetargeting("bvh", "unitree_g1", actual_human_height=height)
+    ref = OracleRetargeter(m, t, actual_human_height=height)
+    idx = [names.index(b) for b in t.scaled_names]
+    for i in range(5):
+        d = gmr.to_numpy(frames[i])
+        scaled = gmr.scale_human_data(d, gmr.human_root_name, gmr.human_scale_table)
+        gmr.offset_human_data(scaled, gmr.pos_offsets1, gmr.rot_offsets1)
+        np.testing.assert_allclose(gmr.retarget(frames[i]), ref.retarget(human[i][idx]), atol=1e-7)
+        np.testing.assert_allclose(gmr.error2(), ref.error(ref._tasks(1, ref.scaled_human_data)), atol=1e-9)
+
+
+def test_retarget_rate_of_one_object():
+    """The B = 1 shim keeps its buffers and uploads tables only when they change: thousands of frames/s per object
+    (the reference's README quotes 60-70 FPS for this loop)."""
+    import time
+    from gmr_b200.motion_retarget import GeneralMotionRetargeting
+    m, t, human, height, names, frames = _frames("bvh", "unitree_g1", 200)
+    gmr = GeneralMotionRetargeting("bvh", "unitree_g1", actual_human_height=height)
+    for f in frames[:20]:
+        gmr.retarget(f)
+    t0 = time.perf_counter()
+    for f in frames[20:]:
+        gmr.retarget(f)
+    rate = 180 / (time.perf_counter() - t0)
+    print(f"B=1 shim: {rate:.0f} frames/s")
+    assert rate > 1000

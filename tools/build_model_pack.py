@@ -47,6 +47,17 @@ def main():
     with open(params.PACK_PATH, "w") as f:
         json.dump(out, f, separators=(",", ":"))
     print("wrote", params.PACK_PATH, os.path.getsize(params.PACK_PATH), "bytes")
+    # motion names of the smplx driver's exclusion lists (scripts/smplx_to_robot_dataset.py:193-208), derived list
+    names = set()
+    for fn in ("0.txt", "1.txt"):
+        with open(os.path.join(args.gmr_root, "assets", "hard_motions", fn)) as f:
+            for line in f:
+                if "Motion:" in line:
+                    names.add(line.split(":")[1].strip().split(",")[0].strip().split(".")[0])
+    hm = os.path.join(os.path.dirname(params.PACK_PATH), "hard_motions.txt")
+    with open(hm, "w") as f:
+        f.write("\n".join(sorted(names)) + "\n")
+    print("wrote", hm, len(names), "names")
 
 
 if __name__ == "__main__":

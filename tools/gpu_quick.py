@@ -18,6 +18,7 @@ ap.add_argument("--robot", default="unitree_g1")
 ap.add_argument("--B", type=int, default=4096)
 ap.add_argument("--T", type=int, default=300)
 ap.add_argument("--reps", type=int, default=3)
+ap.add_argument("--seed", type=int, default=0)
 args = ap.parse_args()
 
 m, t = model_pack.build_tables(args.src, args.robot)
