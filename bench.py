@@ -53,6 +53,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the extra blocks (other configs, strong scaling, B=1 shim)")
+    ap.add_argument("--strong-clips", type=int, default=33334, help="clips of the strong-scaling block (configs[4])")
     ap.add_argument("--e2e-chunks", type=int, default=0,
                     help="gmr_batch_run_host mode: 0 = zero-copy on the pinned host buffers, k >= 1 = k staged frame ranges")
     return ap.parse_args()
@@ -156,9 +157,18 @@ def cpu_baseline(desc, human, scale, budget_s, cores):
     rate, _, _ = time_oracle(desc, human[:probe], scale[:probe], cores)
     n = int(min(human.shape[0], max(probe, (rate * budget_s / T) // cores * cores)))
     rate, dt, res = time_oracle(desc, human[:n], scale[:n], cores)
+    # configs[0] on the CPU side: ONE clip x 1000 frames on ONE thread (the reference's loop is single-threaded)
+    from gmr_b200 import model_pack, synth
+    m1, t1 = model_pack.build_tables(SRC, ROBOT)
+    h1, hg1, _ = synth.synth_human_clips(m1, t1, SRC, B=1, T=1000, seed=SEED - 1)
+    one, _, _ = time_oracle(desc, h1, synth.clip_scales(t1, hg1), 1)
     return {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": f"first {n} clips x {T} frames of the same workload, oracle/gmr_oracle.c with {cores} pthreads, {dt:.1f} s",
-            "iters_per_frame": float(res["iters"].sum(-1).mean())}
+            "iters_per_frame": float(res["iters"].sum(-1).mean()),
+            "single_thread_frames_per_s": one,
+            "single_thread_sample": "BASELINE.json configs[0]: 1 synthetic LAFAN1-shaped clip x 1000 frames, 1 thread",
+            "published_reference_fps": "60-70 FPS on a Threadripper 7960X, 35-45 FPS on an i9-13900K (README.md:615-621; the "
+                                       "real mink/mujoco/daqp loop incl. viewer, one thread; not runnable here)"}
 
 
 def run_reference(args):
@@ -170,14 +180,16 @@ def run_reference(args):
     cores = host_cores()
     T = args.frames
     n_steps = args.steps + args.warmup
-    per_step_s = max(2.0, min(10.0, 150.0 / max(1, n_steps)))
-    # size the sample from a short probe
-    desc, human, scale = build_cpu_case(min(args.clips, 64 * cores), T, cores)
+    per_step_s = max(2.0, min(25.0, 200.0 / max(1, n_steps)))
+    # the full config when one pass over it fits the per-step budget (same_config), else a prefix sized from a probe
+    desc, human, scale = build_cpu_case(args.clips, T, cores)
     from oracle import oracle as oc
     oc.build()
     probe = min(human.shape[0], 2 * cores)
     rate, _, _ = time_oracle(desc, human[:probe], scale[:probe], cores)
     n = int(min(human.shape[0], max(cores, (rate * per_step_s / T) // cores * cores)))
+    if n >= 0.9 * human.shape[0]:
+        n = human.shape[0]
     for _ in range(args.warmup):
         time_oracle(desc, human[:n], scale[:n], cores)
     t0 = time.perf_counter()
@@ -185,16 +197,20 @@ def run_reference(args):
         _, _, res = time_oracle(desc, human[:n], scale[:n], cores)
     dt = time.perf_counter() - t0
     value = n * T * args.steps / dt
-    sample = f"first {n} clips x {T} frames of the workload per step, oracle/gmr_oracle.c with {cores} pthreads"
+    full = n == human.shape[0]
+    sample = (f"all {n} clips x {T} frames of the workload per step (same config as the GPU arm)" if full else
+              f"first {n} clips x {T} frames of the workload per step (a rate: the prefix is the same seeded clips)") + \
+        f", oracle/gmr_oracle.c with {cores} pthreads"
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(args.clips, T), "robot": ROBOT, "source": SRC, "frames_per_clip": T,
-                       "clips_per_step_sample": n},
+                       "clips_per_step_sample": n, "same_config": full},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "iters_per_frame": float(res["iters"].sum(-1).mean()),
+            "published_reference_fps": "60-70 FPS (README.md:615-621: the real mink loop, one thread, Threadripper 7960X)",
             "note": "reference = Python over mink/mujoco/daqp (absent, no network); this arm times its C restatement"}
     print(json.dumps(line), flush=True)
 
@@ -296,6 +312,21 @@ def run_b200(args):
     e2e_value = world * B * T * K / (ms_e2e * 1e-3)
     checksum = float(qpos_host[:, -1, :3].sum().item())
 
+    # ---- extra blocks: strong scaling on every rank count, the other configs at N = 1
+    extras = {}
+    if not args.no_extras:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_extras
+        del qpos_dev
+        extras["strong"] = bench_extras.strong_block(lambda n: BatchedRetargeter(dm, n), human_dev, rank, world, maxr, barrier,
+                                                      total_clips=args.strong_clips)
+        if world == 1:
+            del human_dev
+            torch.cuda.empty_cache()
+            extras["configs0_shim"] = bench_extras.shim_block()
+            extras["configs2_hands"] = bench_extras.hands_block(local, cores)
+            extras["configs3_heterogeneous"] = bench_extras.hetero_block(local, cores)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -319,15 +350,34 @@ def run_b200(args):
     if os.path.exists(tpath):
         with open(tpath) as f:
             traffic = json.load(f).get("dram_bytes_per_launch")
-    roofline = {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
-                "traffic": traffic, "peak_source": peak_src, "kernel": "gmr::clip_kernel<float,true>",
-                "kernel_ms_per_launch": kernel_ms, "algorithmic_bytes_per_frame": bpf,
-                "note": "neither HBM nor tensor cores bind this path; the binding resource is the FP64 FMA pipe / "
-                        "dependent-chain latency - see `compute`",
-                "compute": {"pipe": "fp64_fma", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
-                            "frac": achieved_tf / fp64_peak if fp64_peak > 0 else None,
-                            "peak_source": "measured here (gmr_probe_fma_peak, DFMA chains on all SMs)",
-                            "algorithmic_flops_per_iteration": fpi, "iterations_per_frame": iters_per_frame}}
+    # executed work: ncu's per-opcode thread counts of one launch of this workload (profiles/clip_kernel_ops.json),
+    # turned into flops per frame and divided by the launch time measured here
+    executed = None
+    opath = os.path.join(ROOT, "profiles", "clip_kernel_ops.json")
+    if os.path.exists(opath):
+        with open(opath) as f:
+            ops = json.load(f)
+        fl_frame = (2.0 * ops["dfma"] + ops["dmul"] + ops["dadd"]) / ops["frames"]
+        ex_tf = fl_frame * frames_per_launch / (kernel_ms * 1e-3) / 1e12
+        executed = {"tflops": ex_tf, "frac_of_fp64_peak": ex_tf / fp64_peak if fp64_peak > 0 else None,
+                    "flops_per_frame": fl_frame, "warp_instructions_per_frame": ops["inst_executed"] / ops["frames"],
+                    "issue_active_pct": ops.get("issue_active_pct"), "pipe_fp64_pct": ops.get("pipe_fp64_pct"),
+                    "source": ops.get("source"),
+                    "note": "smsp__sass_thread_inst_executed_op_{dfma,dmul,dadd}_pred_on of one ncu-profiled launch of this "
+                            "workload / its frames, x frames per launch / the launch time measured in this run"}
+    roofline = {"bound": "fp64_fma", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+                "frac": achieved_tf / fp64_peak if fp64_peak > 0 else None, "traffic": traffic,
+                "peak_source": "measured here (gmr_probe_fma_peak, DFMA chains on all SMs; MEASURED_PEAKS.json has no FP64 entry)",
+                "kernel": "gmr::clip_kernel<float,true>", "kernel_ms_per_launch": kernel_ms,
+                "algorithmic_flops_per_iteration": fpi, "iterations_per_frame": iters_per_frame,
+                "note": "per-instance 6x6 contractions on a 35-dof tree: FP64 CUDA-core work on dependent chains, neither "
+                        "HBM nor tensor cores bind it.  `achieved` counts SURVEY.md 8d's DENSE algorithm (84x35 Jacobian, "
+                        "J'W2J, Cholesky) at the measured iteration count - the contract figure between rounds; the kernel "
+                        "runs an O(n) articulated-body recursion instead, so `executed` (ncu opcode counts) is what the "
+                        "FP64 pipe really does and issue_active / pipe_fp64 say how busy the SM is",
+                "executed": executed,
+                "hbm": {"achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
+                        "algorithmic_bytes_per_frame": bpf, "peak_source": peak_src}}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -346,6 +396,7 @@ def run_b200(args):
             "clocks": clk, "roofline": roofline,
             "convergence": {"iters_per_frame": iters_per_frame, "frames_hitting_max_iter": hit_max,
                             "qp_sweeps_per_solve": sweeps_per_solve}, "checksum": checksum}
+    line.update(extras)
     if not args.no_cpu_baseline and world == 1:
         desc = dm.desc
         hn = human_host.numpy()

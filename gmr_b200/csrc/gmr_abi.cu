@@ -230,6 +230,19 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
         if (((mk >> t) & 1u) && (tparent[t] < 0 || !((mk >> tparent[t]) & 1u))) topmask[k * nv + l] |= 1u << t;
     }
   }
+  // ---- dofs stage_integrate visits, box slots of the QP, constant spatial axes of a floating base
+  std::vector<short> integ_dof, box_dof;
+  std::vector<int> box_slot(nv, -1);
+  for (int i = 0; i < nv; i++) {
+    if (dof_kind[i] == DOF_SLIDE || dof_kind[i] == DOF_HINGE) {
+      integ_dof.push_back((short)i);
+      box_slot[i] = (int)box_dof.size();
+      box_dof.push_back((short)i);
+    } else if (dof_kind[i] == DOF_FREE_R && dof_qadr[i] >= 0) {
+      integ_dof.push_back((short)i);
+    }
+  }
+  const int fk_skip = (nv >= 6 && dof_kind[0] == DOF_FREE_T && dof_kind[1] == DOF_FREE_T && dof_kind[2] == DOF_FREE_T) ? 3 : 0;
   // ---- static schedule of the articulated-body solver (qp_solve_aba), per stage.
   // The scheduled dofs (those with a task below them) are cut into CHAINS: every dof continues into its tallest
   // child, its other children are the tops of side chains.  A chain runs bottom-up on one 8-lane group with the
@@ -316,7 +329,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
           const bool top = pos[g] + 1 == (int)chains[cur[g]].size();
           const int cb = (int)aba_ch.size() / 2;
           for (int kid : kids[c]) if (kid != cont[c]) { aba_ch.push_back(accoff(chain_of[kid])); aba_ch.push_back(kid * 64); }
-          const int flags = (pos[g] > 0 ? 1 : 0) | (top ? 2 : 0) | ((pos[g] > 0 ? cont[c] : 0) << 8);
+          const int flags = (pos[g] > 0 ? 1 : 0) | (top ? 2 : 0) | ((pos[g] > 0 ? cont[c] : 0) << 8) | ((box_slot[c] + 1) << 16);
           aba_up.push_back(c); aba_up.push_back(flags); aba_up.push_back(c * GMR_SS * 8); aba_up.push_back(c * 64);
           aba_up.push_back(own[c] >= 0 ? own[c] * GMR_KS * 8 : -1);
           aba_up.push_back(cb); aba_up.push_back((int)aba_ch.size() / 2); aba_up.push_back(accoff(cur[g]));
@@ -405,7 +418,8 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
          o_ro = bl.push(vec(d->rot_off, 4 * d->n_scaled)), o_ft = bl.push(vec(d->is_foot, d->n_scaled)),
          o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot),
          o_fj = bl.push(fk_jump), o_fb = bl.push(fk_body), o_ap1 = bl.push(aba_up), o_ach = bl.push(aba_ch), o_adn = bl.push(aba_dn), o_amg = bl.push(aba_merge),
-         o_atd = bl.push(task_dof), o_vm = bl.push(dof_vmax);
+         o_atd = bl.push(task_dof), o_vm = bl.push(dof_vmax),
+         o_ig = bl.push(integ_dof), o_bx = bl.push(box_dof);
   const size_t staged_bytes = (bl.bytes.size() + 15) & ~size_t(15);
   // tables only the stage kernels read (gmr_build_qp: the assembly of H), from global memory
   size_t o_lstart = bl.push(level_start), o_lbody = bl.push(level_body), o_dp = bl.push(dof_parent),
@@ -476,6 +490,8 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.jnt_axis = (const double*)(B0 + o_jaxis); h.qpos0 = (const double*)(B0 + o_q0);
   h.dof_kind = (const int*)(B0 + o_dk); h.dof_qadr = (const int*)(B0 + o_dq); h.dof_parent = (const int*)(B0 + o_dp);
   h.dof_body = (const int*)(B0 + o_db); h.blob = B0; h.blob_bytes = (int)staged_bytes;
+  h.fk_skip = fk_skip; h.n_integ = (int)integ_dof.size(); h.integ_dof = (const short*)(B0 + o_ig);
+  h.n_box = (int)box_dof.size(); h.box_dof = (const short*)(B0 + o_bx);
   h.has_vmax = d->dof_vmax ? 1 : 0; h.dof_vmax = (const double*)(B0 + o_vm);
   h.dof_limited = (const int*)(B0 + o_dl); h.dof_lo = (const double*)(B0 + o_dlo); h.dof_hi = (const double*)(B0 + o_dhi);
   h.dof_taskmask = (const unsigned*)(B0 + o_tm); h.scaled_index = (const int*)(B0 + o_si);
@@ -1179,6 +1195,25 @@ extern "C" int gmr_smplx_to_stream(int device, void* stream, const float* full_p
   else smplx_stream_kernel<double><<<(n_frames_out + tb - 1) / tb, tb, 0, (cudaStream_t)stream>>>(a);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(-3, cudaGetErrorString(e));
+  return 0;
+}
+
+// ---------------------------------------------------------------- short math probe (tests only)
+namespace {
+__global__ void math_probe_kernel(int n, const double* x, const double* y, double* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[3 * i] = rcp_pos(x[i]);
+  out[3 * i + 1] = rsqrt_pos(x[i]);
+  out[3 * i + 2] = atan_ratio(fmin(x[i], y[i]), fmax(x[i], y[i]));
+}
+}  // namespace
+
+extern "C" int gmr_probe_math(int device, int n, const double* x_dev, const double* y_dev, double* out_dev) {
+  if (n < 1 || !x_dev || !y_dev || !out_dev) return fail(-1, "bad argument");
+  DevGuard g(device);
+  math_probe_kernel<<<(n + 127) / 128, 128>>>(n, x_dev, y_dev, out_dev);
+  CU(cudaGetLastError());
   return 0;
 }
 

@@ -55,6 +55,11 @@ struct DevModel {
   const int* dof_limited;    // [nv]
   const double* dof_lo;      // [nv] joint range lower
   const double* dof_hi;      // [nv]
+  int fk_skip;               // leading translational dofs of a floating base (their spatial axes are constants): 3 or 0
+  int n_integ;               // dofs stage_integrate visits: hinges, slides and the first rotational dof of a free joint
+  const short* integ_dof;    // [n_integ]
+  int n_box;                 // dofs that can carry a box constraint (everything but a free joint's six), ascending
+  const short* box_dof;      // [n_box]: slot -> dof; the active-set masks of the box QP are indexed by slot
   int has_vmax;              // optional velocity box |dq| <= dof_vmax * timestep (off: the reference passes no velocity limit)
   const double* dof_vmax;    // [nv] (+inf: none)
   const unsigned* dof_taskmask;  // [2*nv] bit t set: task t of the stage is in the dof's subtree
@@ -84,7 +89,8 @@ struct DevModel {
   int aba_doubles;               // doubles of the block array a warp needs (max over stages)
   // upward sweep, per (pass, 8-lane group) two words:
   //   {dof (-1: idle), flags, S_dof, Ud_dof}  flags: 1 = X carried in registers from the previous dof of the chain
-  //                                                  (bits 8..: that dof), 2 = store X (the chain's top)
+  //                                                  (bits 8..15: that dof), 2 = store X (the chain's top),
+  //                                                  bits 16..23: box slot of the dof + 1 (0: none)
   //   {own task block (-1: none), side children [y,z) of aba_ch, X_dof (where a chain top stores)}
   const int4* aba_up;
   const int2* aba_ch;            // per side child: its accumulator, its Ud
@@ -156,19 +162,18 @@ __device__ __forceinline__ int tri(int i) { return i * (i + 1) / 2; }
 // ---------------------------------------------------------------- short reciprocal / root / arctangent
 // The library's double-precision 1/x, sqrt and atan2 carry slow paths for denormals, infinities and signed zeros
 // (20-150 instructions each, inlined at every call site of a kernel whose instruction footprint is what stalls it).
-// The arguments here are plain normal numbers far inside the float range, so a single-precision seed plus two
-// Newton steps (quadratic: 2^-23 -> 2^-46 -> 2^-92) gives the same result to the last bit or two in ~8 instructions.
+// The arguments here are plain normal numbers, so the hardware's approximate seed (MUFU.RCP64H / RSQ64H, ~20 bits)
+// plus two Newton steps (quadratic: 2^-20 -> 2^-40 -> 2^-80) gives the same result to the last bit or two in 5-7
+// instructions.
 __device__ __forceinline__ double rcp_pos(double D) {            // 1 / D, D > 0
-  float seed;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(seed) : "f"((float)D));
-  double inv = (double)seed;
+  double inv;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(inv) : "d"(D));        // MUFU.RCP64H: ~20 bits
   inv = fma(inv, fma(-D, inv, 1.0), inv);
   return fma(inv, fma(-D, inv, 1.0), inv);
 }
 __device__ __forceinline__ double rsqrt_pos(double x) {          // 1 / sqrt(x), x > 0
-  float seed;
-  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(seed) : "f"((float)x));
-  double y = (double)seed;
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));        // MUFU.RSQ64H
   const double hx = 0.5 * x;
   y = fma(y, fma(-hx * y, y, 0.5), y);
   return fma(y, fma(-hx * y, y, 0.5), y);

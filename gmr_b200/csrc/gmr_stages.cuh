@@ -191,7 +191,12 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
   // ---- pass C
   const int ref = M.ref_body;
   const double O[3] = {xpos[3 * ref], xpos[3 * ref + 1], xpos[3 * ref + 2]};    // world (body 0) has xpos = 0
-  for (int k = lane; k < M.nv; k += 32) {
+  const int skip = M.fk_skip;          // a floating base's translations: S = unit vectors, written by three lanes below
+  if (lane < skip) {
+    double* sk = S + GMR_SS * lane;
+    sk[0] = (lane == 0); sk[1] = (lane == 1); sk[2] = (lane == 2); sk[3] = sk[4] = sk[5] = 0;
+  }
+  for (int k = lane + skip; k < M.nv; k += 32) {
     const int kind = mv(M.dof_kind)[k], b = mv(M.dof_body)[k];
     double* sk = S + GMR_SS * k;
     if (kind == DOF_FREE_T) {
@@ -711,8 +716,12 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   int ra = 0, rb = 0;                       // lane e of the root block: M(ra, rb) for e < 21, r(ra) for 21 <= e < 27
   if (lane < 21) { while ((ra + 1) * (ra + 2) / 2 <= lane) ra++; rb = lane - ra * (ra + 1) / 2; }
   else if (lane < GMR_KS) ra = lane - 21;
-  const int i0 = lane, i1 = lane + 32;
-  const bool has0 = i0 < n, has1 = i1 < n;
+  // lane l owns the box of slots l and l + 32 (slot = index among the dofs that can carry a box: everything but a
+  // free joint's six; 29 slots for unitree_g1, so the second slot is skipped by a warp-uniform branch)
+  const int nbox = M.n_box;
+  const bool two = nbox > 32;
+  const bool has0 = lane < nbox, has1 = two && lane + 32 < nbox;
+  const int i0 = has0 ? mv(M.box_dof)[lane] : 0, i1 = has1 ? mv(M.box_dof)[lane + 32] : 0;
   // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs, intersected with the
   // optional velocity box |dq| <= vmax dt (off by default: the reference passes no velocity limit, motion_retarget.py:147-149)
   double lo0 = -INFINITY, hi0 = INFINITY, lo1 = -INFINITY, hi1 = INFINITY;
@@ -720,7 +729,7 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
     const double qv = q[mv(M.dof_qadr)[i0]];
     hi0 = M.limit_gain * (mv(M.dof_hi)[i0] - qv); lo0 = -M.limit_gain * (qv - mv(M.dof_lo)[i0]);
   }
-  if (has1 && mv(M.dof_limited)[i1]) {
+  if (two && has1 && mv(M.dof_limited)[i1]) {
     const double qv = q[mv(M.dof_qadr)[i1]];
     hi1 = M.limit_gain * (mv(M.dof_hi)[i1] - qv); lo1 = -M.limit_gain * (qv - mv(M.dof_lo)[i1]);
   }
@@ -738,9 +747,14 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
     }
   }
   int st0 = 0, st1 = 0;      // 0 free, -1 at lower, +1 at upper; a seed is only honoured where the bound is finite
-  if (has0) st0 = ((act_lo >> i0) & 1ull) && lo0 > -INFINITY ? -1 : (((act_hi >> i0) & 1ull) && hi0 < INFINITY ? 1 : 0);
-  if (has1) st1 = ((act_lo >> i1) & 1ull) && lo1 > -INFINITY ? -1 : (((act_hi >> i1) & 1ull) && hi1 < INFINITY ? 1 : 0);
-  unsigned long long act = (unsigned long long)__ballot_sync(GMR_FULL, st0 != 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 != 0) << 32);
+  if (has0) st0 = ((act_lo >> lane) & 1ull) && lo0 > -INFINITY ? -1 : (((act_hi >> lane) & 1ull) && hi0 < INFINITY ? 1 : 0);
+  if (has1) st1 = ((act_lo >> (lane + 32)) & 1ull) && lo1 > -INFINITY ? -1 : (((act_hi >> (lane + 32)) & 1ull) && hi1 < INFINITY ? 1 : 0);
+  unsigned long long act = (unsigned long long)__ballot_sync(GMR_FULL, st0 != 0);
+  if (two) act |= (unsigned long long)__ballot_sync(GMR_FULL, st1 != 0) << 32;
+  if (rootX < 0) {                          // no floating-base block: a free joint's dofs (if any) are not swept and stay at 0
+    for (int i = lane; i < n; i += 32) x[i] = 0.0;
+    __syncwarp();
+  }
   int best = n + 1, p = 3, nfact = 0;
   bool restarted = act == 0, capped = false;      // a warm-started search that hits its cap starts over cold once
   double r0 = 0, r1 = 0;
@@ -749,7 +763,7 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
     // dofs at a bound carry it; free dofs without a task below them stay at 0 (the sweeps skip them)
     const double xa0 = st0 < 0 ? lo0 : (st0 > 0 ? hi0 : 0.0), xa1 = st1 < 0 ? lo1 : (st1 > 0 ? hi1 : 0.0);
     if (has0) { x[i0] = xa0; if (st0) { Ud[8 * i0 + 6] = 0.0; Ud[8 * i0 + 7] = -xa0; } }      // locked joint: alpha = 0, beta = -bound
-    if (has1) { x[i1] = xa1; if (st1) { Ud[8 * i1 + 6] = 0.0; Ud[8 * i1 + 7] = -xa1; } }
+    if (two && has1) { x[i1] = xa1; if (st1) { Ud[8 * i1 + 6] = 0.0; Ud[8 * i1 + 7] = -xa1; } }
     __syncwarp();
     // ---- upward sweep
     const unsigned actw0 = (unsigned)act, actw1 = (unsigned)(act >> 32);
@@ -764,7 +778,7 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
         double t = 0.0, w = 0.0, U = 0.0;
         if (valid && i8 < 6) {
           if (en.y & 1) {                                      // the chain's previous dof: X -= [U U' alpha | U beta]
-            const double2* ud = (const double2*)(Udb + ((en.y >> 8) << 6));
+            const double2* ud = (const double2*)(Udb + (((en.y >> 8) & 0xff) << 6));
             const double2 u01 = ud[0], u23 = ud[1], u45 = ud[2], ab = ud[3];
             const double ua = -Uprev * ab.x;
             a0 = fma(ua, u01.x, a0); a1 = fma(ua, u01.y, a1); a2 = fma(ua, u23.x, a2);
@@ -807,7 +821,8 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
 #pragma unroll
         for (int o = 1; o < 8; o <<= 1) { t += __shfl_xor_sync(GMR_FULL, t, o); w += __shfl_xor_sync(GMR_FULL, w, o); }
         if (valid) {
-          const bool isact = ((en.x < 32 ? actw0 : actw1) >> (en.x & 31)) & 1u;
+          const int slot = (en.y >> 16) - 1;                       // box slot of the dof (-1: a free joint's dof)
+          const bool isact = slot >= 0 && (((slot < 32 ? actw0 : actw1) >> (slot & 31)) & 1u);
           const double inv = rcp_pos(t + diag);                  // D = S'U + d
           // lanes 0..5 store U, lane 6 alpha = 1/D, lane 7 beta = S'p / D (a locked dof keeps the pair its owner lane wrote)
           if (i8 < 6 || !isact) *(double*)(Udb + en.w + i8b) = i8 < 6 ? U : (i8 == 6 ? inv : w * inv);
@@ -884,42 +899,51 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
       __syncwarp();
     }
     nfact++;
-    // ---- downward sweep: the same chains top-down, v_i8 of the chain's current link in a register
+    // ---- downward sweep: the same chains top-down.  Every lane of a group carries the whole link velocity v (six
+    // registers) and forms U'v itself from three 128-bit loads of U: no shuffle rounds, a third of the dependent
+    // latency of a per-lane split - the sweep is a chain of depth `ndn`, so latency is what it costs.
     {
-      double vi = 0.0;
+      double v0 = 0, v1 = 0, v2 = 0, v3 = 0, v4 = 0, v5 = 0;
       const int4* e = dn0;
 #pragma unroll 1
       for (int ps = 0; ps < ndn; ps++, e += 4) {
         const int4 en = *e;                                      // dof (-1: idle), flags, byte offset of v_parent (-1: none)
-        const bool valid = en.x >= 0;
-        const char* ud = Udb + 64 * (valid ? en.x : 0);
-        double dot = 0.0;
-        if (valid && i8 < 6) {
-          if (!(en.y & 1)) vi = en.z >= 0 ? *(const double*)(vb + en.z + i8b) : 0.0;     // a chain's top: v_parent from shared memory
-          dot = *(const double*)(ud + i8b) * vi;
-        }
-#pragma unroll
-        for (int o = 1; o < 8; o <<= 1) dot += __shfl_xor_sync(GMR_FULL, dot, o);
-        if (valid) {
-          const double2 ab = *(const double2*)(ud + 48);
+        if (en.x >= 0) {
+          if (!(en.y & 1)) {                                     // a chain's top: v_parent from shared memory (0 at a tree root)
+            v0 = v1 = v2 = v3 = v4 = v5 = 0.0;
+            if (en.z >= 0) {
+              const double2* vp = (const double2*)(vb + en.z);
+              const double2 p01 = vp[0], p23 = vp[1], p45 = vp[2];
+              v0 = p01.x; v1 = p01.y; v2 = p23.x; v3 = p23.y; v4 = p45.x; v5 = p45.y;
+            }
+          }
+          const double2* ud = (const double2*)(Udb + 64 * en.x);
+          const double2* Sd = (const double2*)(Sb + GMR_SS * 8 * en.x);
+          const double2 u01 = ud[0], u23 = ud[1], u45 = ud[2], ab = ud[3], s01 = Sd[0], s23 = Sd[1], s45 = Sd[2];
+          const double dot = fma(u45.x, v4, fma(u23.x, v2, u01.x * v0)) + fma(u45.y, v5, fma(u23.y, v3, u01.y * v1));
           const double xc = fma(-dot, ab.x, -ab.y);
-          if (i8 < 6) {
-            vi = fma(*(const double*)(Sb + GMR_SS * 8 * en.x + i8b), xc, vi);
-            if (en.y & 2) *(double*)(vb + 48 * en.x + i8b) = vi;
-          } else if (i8 == 6) x[en.x] = xc;
+          v0 = fma(s01.x, xc, v0); v1 = fma(s01.y, xc, v1); v2 = fma(s23.x, xc, v2);
+          v3 = fma(s23.y, xc, v3); v4 = fma(s45.x, xc, v4); v5 = fma(s45.y, xc, v5);
+          if (i8 == 0) {
+            x[en.x] = xc;
+            if (en.y & 2) {
+              double2* vd = (double2*)(vb + 48 * en.x);
+              vd[0] = make_double2(v0, v1); vd[1] = make_double2(v2, v3); vd[2] = make_double2(v4, v5);
+            }
+          }
         }
         __syncwarp();
       }
     }
     r0 = has0 ? x[i0] : 0.0;
-    r1 = has1 ? x[i1] : 0.0;
+    r1 = (two && has1) ? x[i1] : 0.0;
     // exact bounds on the active set (the sweep reproduces them up to rounding)
     if (st0) r0 = xa0;
     if (st1) r1 = xa1;
     // ---- KKT check
     bool bad0 = false, bad1 = false;
     if (has0 && !st0) bad0 = (r0 < lo0 - QP_PTOL) || (r0 > hi0 + QP_PTOL);
-    if (has1 && !st1) bad1 = (r1 < lo1 - QP_PTOL) || (r1 > hi1 + QP_PTOL);
+    if (two && has1 && !st1) bad1 = (r1 < lo1 - QP_PTOL) || (r1 > hi1 + QP_PTOL);
     if (act) {
       const int* tdof = mv(M.task_dof) + stage * GMR_MAX_TASKS;
       for (int k = lane; k < 6 * m; k += 32) {                   // f_t = K_t v + g_t
@@ -938,6 +962,7 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
       const unsigned keep = M.aba_kktmask[stage];
 #pragma unroll
       for (int r = 0; r < 2; r++) {
+        if (r && !two) break;
         const int i = r ? i1 : i0;
         const int st = r ? st1 : st0;
         if ((r ? has1 : has0) && st) {
@@ -956,7 +981,7 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
       }
       __syncwarp();
     }
-    const unsigned b0 = __ballot_sync(GMR_FULL, bad0), b1 = __ballot_sync(GMR_FULL, bad1);
+    const unsigned b0 = __ballot_sync(GMR_FULL, bad0), b1 = two ? __ballot_sync(GMR_FULL, bad1) : 0u;
     const int nbad = __popc(b0) + __popc(b1);
     if (nbad == 0) break;
     if (it + 1 >= QP_MAX_SWEEPS) {
@@ -970,14 +995,19 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
     else if (p > 0) { p--; all = true; }
     else all = false;
     const int last = b1 ? 63 - __clz(b1) : 31 - __clz(b0);
-    if (bad0 && (all || i0 == last)) st0 = st0 ? 0 : (r0 < lo0 ? -1 : 1);
-    if (bad1 && (all || i1 == last)) st1 = st1 ? 0 : (r1 < lo1 ? -1 : 1);
-    act = (unsigned long long)__ballot_sync(GMR_FULL, st0 != 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 != 0) << 32);
+    if (bad0 && (all || lane == last)) st0 = st0 ? 0 : (r0 < lo0 ? -1 : 1);           // `last` is a slot: slots ascend with the dofs
+    if (bad1 && (all || lane + 32 == last)) st1 = st1 ? 0 : (r1 < lo1 ? -1 : 1);
+    act = (unsigned long long)__ballot_sync(GMR_FULL, st0 != 0);
+    if (two) act |= (unsigned long long)__ballot_sync(GMR_FULL, st1 != 0) << 32;
   }
   if (has0) x[i0] = r0;
-  if (has1) x[i1] = r1;
-  act_lo = (unsigned long long)__ballot_sync(GMR_FULL, st0 < 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 < 0) << 32);
-  act_hi = (unsigned long long)__ballot_sync(GMR_FULL, st0 > 0) | ((unsigned long long)__ballot_sync(GMR_FULL, st1 > 0) << 32);
+  if (two && has1) x[i1] = r1;
+  act_lo = (unsigned long long)__ballot_sync(GMR_FULL, st0 < 0);
+  act_hi = (unsigned long long)__ballot_sync(GMR_FULL, st0 > 0);
+  if (two) {
+    act_lo |= (unsigned long long)__ballot_sync(GMR_FULL, st1 < 0) << 32;
+    act_hi |= (unsigned long long)__ballot_sync(GMR_FULL, st1 > 0) << 32;
+  }
   __syncwarp();
   return capped ? -nfact : nfact;
 }
@@ -1001,10 +1031,14 @@ __device__ __forceinline__ void stage_integrate(const MV& mv, const Lay& lay, do
   double* q = sm + lay.q;
   const double* x = sm + lay.x;
   const double dt = M.timestep, idt = M.inv_timestep;
-  for (int i = lane; i < M.nv; i += 32) {
+  const short* idof = mv(M.integ_dof);
+  for (int j = lane; j < M.n_integ; j += 32) {       // hinges, slides, and one lane per free joint
+    const int i = idof[j];
     const int kind = mv(M.dof_kind)[i], qa = mv(M.dof_qadr)[i];
     if (kind == DOF_FREE_R) {
-      if (qa >= 0) {     // first rotational dof of the free joint updates the quaternion
+      {                  // first rotational dof of the free joint: its three translations, then the quaternion
+#pragma unroll
+        for (int k = 1; k <= 3; k++) q[qa - k] += dt * (x[i - k] * idt);
         double w[3] = {x[i] * idt, x[i + 1] * idt, x[i + 2] * idt};
         const double n2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
         double quat[4] = {q[qa], q[qa + 1], q[qa + 2], q[qa + 3]};

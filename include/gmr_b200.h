@@ -132,7 +132,8 @@ int gmr_model_destroy(gmr_model* m);
 #define GMR_TABLE_INFO       0   /* nv, n_task, n_up_passes, n_down_passes, n_merge, root block offset (-1: none), first base dof,
                                     kkt task mask, doubles of the block array, GMR_KS, GMR_XS, GMR_SS */
 #define GMR_TABLE_UP         2   /* per (pass, 8-lane group) 8 ints: dof (-1 idle), flags (1: X carried in registers from dof
-                                    flags >> 8, 2: store X), S, Ud offsets, own task block (-1), side children [b, e), X offset */
+                                    (flags >> 8) & 255, 2: store X, bits 16..23: box slot + 1), S, Ud offsets, own task block (-1),
+                                    side children [b, e), X offset */
 #define GMR_TABLE_CHILD      3   /* per side child: accumulator offset, Ud offset */
 #define GMR_TABLE_DN         5   /* per (pass, group) 4 ints: dof (-1 idle), flags (1: v carried, 2: store v), v_parent offset (-1: none), 0 */
 #define GMR_TABLE_MERGE      6   /* pairs (dst task, src task) hanging on one dof */
@@ -277,6 +278,10 @@ int gmr_smplx_to_stream(int device, void* stream, const float* full_pose_dev, co
  * TFLOP/s (fp64 != 0: DFMA, else FFMA) - the compute roofline denominator of bench.py.
  * Synchronous, default stream. */
 int gmr_probe_fma_peak(int device, int fp64, double* tflops_out);
+/* Test helper: the kernels' short reciprocal, reciprocal root and arctangent (csrc/gmr_device.cuh: hardware seed +
+ * two Newton steps; odd polynomial) evaluated on x, y > 0: out[3i] = 1/x, out[3i+1] = 1/sqrt(x),
+ * out[3i+2] = atan(min(x,y)/max(x,y)).  Device pointers, default stream. */
+int gmr_probe_math(int device, int n, const double* x_dev, const double* y_dev, double* out_dev);
 
 #ifdef __cplusplus
 }

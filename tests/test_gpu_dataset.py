@@ -88,7 +88,7 @@ def test_failed_clip_is_flagged_and_skipped():
     m, t, clips, heights, names, human = _clips("bvh", "unitree_g1", lengths, seed=4)
     ok = dataset.retarget_clips("bvh", "unitree_g1", clips, heights=heights, human_names=names)
     bad = [c.copy() for c in clips]
-    bad[1][5, 3, 0] = np.nan
+    bad[1][5, names.index(t.scaled_names[3]), 0] = np.nan      # a body the config reads (the others are dropped, :219-220)
     motions, status = dataset.retarget_clips("bvh", "unitree_g1", bad, heights=heights, human_names=names, return_status=True)
     assert motions[1] is None and (status[1] & abi.STATUS_BAD_INPUT) and (status[1] & abi.STATUS_BAD_OUTPUT)
     assert "non-finite" in dataset.describe_status(int(status[1]))

@@ -431,7 +431,7 @@ def test_status_flags():
     B, T = 32, 30
     m, t, dm, br, human, heights = _setup("bvh", "unitree_g1", B, T, seed=13)
     h = human.copy()
-    h[5, 12, 2, 1] = np.inf
+    h[5, 12, dm.desc.human_names.index(t.scaled_names[2]), 1] = np.inf      # a body the config reads
     qpos, diag = br.run(h, diag=True)
     st, it = diag["status"].cpu().numpy(), diag["iters"].cpu().numpy()
     ok = np.ones((B, T), bool)
@@ -504,3 +504,24 @@ def test_set_order_rejects_non_permutations():
     with pytest.raises(ValueError):
         br.set_order([0, 1, 1, 3, 4, 5])
     br.set_order([5, 4, 3, 2, 1, 0])
+
+
+def test_short_math_matches_libm():
+    """rcp_pos / rsqrt_pos / atan_ratio of csrc/gmr_device.cuh (hardware seed + two Newton steps; degree-39 odd
+    polynomial) against numpy over the ranges the kernels feed them: a few ulp."""
+    import ctypes as C
+    import torch
+    from gmr_b200 import _lib
+    rng = np.random.default_rng(0)
+    x = np.concatenate([10.0 ** rng.uniform(-12, 12, 20000), rng.uniform(0.5, 2.0, 20000), [1e-10, 1.0, 0.5, 4.0]])
+    y = np.concatenate([x[:20000] * 10.0 ** rng.uniform(-6, 6, 20000), rng.uniform(0.5, 2.0, 20000), [1e-10, 1.0, 3.0, 4.0]])
+    xd, yd = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    out = torch.zeros((len(x), 3), dtype=torch.float64, device="cuda")
+    _lib.check(_lib.lib().gmr_probe_math(0, len(x), C.c_void_p(xd.data_ptr()), C.c_void_p(yd.data_ptr()), C.c_void_p(out.data_ptr())),
+               "gmr_probe_math")
+    torch.cuda.synchronize()
+    o = out.cpu().numpy()
+    assert np.abs(o[:, 0] * x - 1.0).max() < 5e-16
+    assert np.abs(o[:, 1] * np.sqrt(x) - 1.0).max() < 5e-16
+    ref = np.arctan(np.minimum(x, y) / np.maximum(x, y))
+    assert np.abs(o[:, 2] - ref).max() < 4.5e-16

@@ -90,7 +90,7 @@ def _walk(hm, stage, S, K, g, d, locked, bound):
             seen.add(int(c))
             r = reg[grp]
             if flags & 1:
-                prev = flags >> 8
+                prev = (flags >> 8) & 0xff
                 assert r["dof"] == prev, "carried accumulator is not the previous dof of this group"
                 al, be = Ud[8 * prev + 6], Ud[8 * prev + 7]
                 Uc = Ud[8 * prev:8 * prev + 6]
