@@ -329,7 +329,9 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
           const bool top = pos[g] + 1 == (int)chains[cur[g]].size();
           const int cb = (int)aba_ch.size() / 2;
           for (int kid : kids[c]) if (kid != cont[c]) { aba_ch.push_back(accoff(chain_of[kid])); aba_ch.push_back(kid * 64); }
-          const int flags = (pos[g] > 0 ? 1 : 0) | (top ? 2 : 0) | ((pos[g] > 0 ? cont[c] : 0) << 8) | ((box_slot[c] + 1) << 16);
+          const bool is_root = fb >= 0 && c == fb + 5;       // the floating base's link: raw X for the 6x6 block
+          const bool side = top && !is_root && dof_parent[c] >= 0 && !skip_up(dof_parent[c]);
+          const int flags = (pos[g] > 0 ? 1 : 0) | (side ? 2 : 0) | (is_root ? 4 : 0) | ((box_slot[c] + 1) << 16);
           aba_up.push_back(c); aba_up.push_back(flags); aba_up.push_back(c * GMR_SS * 8); aba_up.push_back(c * 64);
           aba_up.push_back(own[c] >= 0 ? own[c] * GMR_KS * 8 : -1);
           aba_up.push_back(cb); aba_up.push_back((int)aba_ch.size() / 2); aba_up.push_back(accoff(cur[g]));

@@ -88,12 +88,12 @@ struct DevModel {
   unsigned aba_kktmask[2];       // tasks whose block is not merged into another task's (same dof)
   int aba_doubles;               // doubles of the block array a warp needs (max over stages)
   // upward sweep, per (pass, 8-lane group) two words:
-  //   {dof (-1: idle), flags, S_dof, Ud_dof}  flags: 1 = X carried in registers from the previous dof of the chain
-  //                                                  (bits 8..15: that dof), 2 = store X (the chain's top),
-  //                                                  bits 16..23: box slot of the dof + 1 (0: none)
-  //   {own task block (-1: none), side children [y,z) of aba_ch, X_dof (where a chain top stores)}
+  //   {dof (-1: idle), flags, S_dof, Ud_dof}  flags: 1 = X^a carried in registers from the previous dof of the chain,
+  //                                                  2 = store X^a (a side chain's top), 4 = store X before the dof's own
+  //                                                  rank-1 term (the floating base's link), bits 16..23: box slot + 1
+  //   {own task block (-1: none), side children [y,z) of aba_ch, X_dof (where a top stores)}
   const int4* aba_up;
-  const int2* aba_ch;            // per side child: its accumulator, its Ud
+  const int2* aba_ch;            // per side child: its accumulator (X^a, stored by its top), its Ud
   // downward sweep, per (pass, group): {dof (-1: idle), flags, v_parent (-1: none), -}
   //   flags: 1 = v carried in registers from the parent (previous dof of the chain), 2 = store v
   const int4* aba_dn;

@@ -714,7 +714,7 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   const int i8b = 8 * i8;
   const int rootX = M.aba_root[stage], rootdof = M.aba_rootdof[stage];
   int ra = 0, rb = 0;                       // lane e of the root block: M(ra, rb) for e < 21, r(ra) for 21 <= e < 27
-  if (lane < 21) { while ((ra + 1) * (ra + 2) / 2 <= lane) ra++; rb = lane - ra * (ra + 1) / 2; }
+  if (lane < 21) { ra = (int)((0x5b6db2491b6d2448ull >> (3 * lane)) & 7ull); rb = lane - ra * (ra + 1) / 2; }      // row of packed entry `lane`, 3 bits each
   else if (lane < GMR_KS) ra = lane - 21;
   // lane l owns the box of slots l and l + 32 (slot = index among the dofs that can carry a box: everything but a
   // free joint's six; 29 slots for unitree_g1, so the second slot is skipped by a warp-uniform branch)
@@ -762,31 +762,32 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   for (int it = 0;; it++) {
     // dofs at a bound carry it; free dofs without a task below them stay at 0 (the sweeps skip them)
     const double xa0 = st0 < 0 ? lo0 : (st0 > 0 ? hi0 : 0.0), xa1 = st1 < 0 ? lo1 : (st1 > 0 ? hi1 : 0.0);
-    if (has0) { x[i0] = xa0; if (st0) { Ud[8 * i0 + 6] = 0.0; Ud[8 * i0 + 7] = -xa0; } }      // locked joint: alpha = 0, beta = -bound
-    if (two && has1) { x[i1] = xa1; if (st1) { Ud[8 * i1 + 6] = 0.0; Ud[8 * i1 + 7] = -xa1; } }
+    if (has0) x[i0] = xa0;
+    if (two && has1) x[i1] = xa1;
     __syncwarp();
-    // ---- upward sweep
+    // ---- upward sweep.  A pass has two halves around one __syncwarp: (1) lane i < 6 completes row i of X_c (the chain's
+    // registers + own task block + side chains from shared memory) and writes U_i = X_i S and p_i; (2) every lane of
+    // the group reads the whole U and p back (six 128-bit loads), forms D = S'U + d, S'p, alpha, beta for itself - no
+    // shuffle rounds - and lanes < 6 subtract the dof's rank-1 term at once, so the registers carry the ARTICULATED
+    // X^a = [I - U U' alpha | p - U beta] into the next dof of the chain.
     const unsigned actw0 = (unsigned)act, actw1 = (unsigned)(act >> 32);
     {
-      double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0, a5 = 0, pi = 0, Uprev = 0;      // row i8 of the chain's X, U_i8 of its last dof
+      double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0, a5 = 0, pi = 0;      // row i8 of the chain's X^a
+      double* const pscr = fv + 8 * g8;                                  // the group's p, for the second half
       const int4* e = up0;
 #pragma unroll 1
       for (int ps = 0; ps < nup; ps++, e += 8) {
         // {dof (-1: idle), flags, S_c, Ud_c} {own task block (-1: none), side children [y, z), X_c}
         const int4 en = e[0], eb = e[1];
         const bool valid = en.x >= 0;
-        double t = 0.0, w = 0.0, U = 0.0;
+        double U = 0.0;
+        double2 s01 = make_double2(0, 0), s23 = s01, s45 = s01;
+        if (valid) {
+          const double2* Sd = (const double2*)(Sb + en.z);
+          s01 = Sd[0]; s23 = Sd[1]; s45 = Sd[2];
+        }
         if (valid && i8 < 6) {
-          if (en.y & 1) {                                      // the chain's previous dof: X -= [U U' alpha | U beta]
-            const double2* ud = (const double2*)(Udb + (((en.y >> 8) & 0xff) << 6));
-            const double2 u01 = ud[0], u23 = ud[1], u45 = ud[2], ab = ud[3];
-            const double ua = -Uprev * ab.x;
-            a0 = fma(ua, u01.x, a0); a1 = fma(ua, u01.y, a1); a2 = fma(ua, u23.x, a2);
-            a3 = fma(ua, u23.y, a3); a4 = fma(ua, u45.x, a4); a5 = fma(ua, u45.y, a5);
-            pi = fma(-Uprev, ab.y, pi);
-          } else {
-            a0 = a1 = a2 = a3 = a4 = a5 = pi = 0.0;
-          }
+          if (!(en.y & 1)) a0 = a1 = a2 = a3 = a4 = a5 = pi = 0.0;      // a chain's bottom
           if (eb.x >= 0) {                                     // own task block, packed symmetric
             const char* own = XAc + eb.x;
             a0 += *(const double*)(own + __byte_perm(row_lo, 0, 0x4440)); a1 += *(const double*)(own + __byte_perm(row_lo, 0, 0x4441));
@@ -795,37 +796,46 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
             pi += *(const double*)(own + 168 + i8b);
           }
 #pragma unroll 1
-          for (int ch = eb.y; ch < eb.z; ch++) {               // side chains that end here: X from shared memory
-            const int2 cd = chl[ch];                           // byte offsets of the child's accumulator and of its Ud
-            const double2* Xr = (const double2*)(XAc + cd.x + 6 * i8b);
-            const double2* ud = (const double2*)(Udb + cd.y);
-            const double2 x01 = Xr[0], x23 = Xr[1], x45 = Xr[2], u01 = ud[0], u23 = ud[1], u45 = ud[2], ab = ud[3];
-            const double ui = *(const double*)(Udb + cd.y + i8b), ua = -ui * ab.x;
-            a0 += fma(ua, u01.x, x01.x); a1 += fma(ua, u01.y, x01.y); a2 += fma(ua, u23.x, x23.x);
-            a3 += fma(ua, u23.y, x23.y); a4 += fma(ua, u45.x, x45.x); a5 += fma(ua, u45.y, x45.y);
-            pi += fma(-ui, ab.y, *(const double*)(XAc + cd.x + 288 + i8b));
+          for (int ch = eb.y; ch < eb.z; ch++) {               // side chains that end here: their X^a from shared memory
+            const char* Xc = XAc + chl[ch].x;
+            const double2* Xr = (const double2*)(Xc + 6 * i8b);
+            const double2 x01 = Xr[0], x23 = Xr[1], x45 = Xr[2];
+            a0 += x01.x; a1 += x01.y; a2 += x23.x; a3 += x23.y; a4 += x45.x; a5 += x45.y;
+            pi += *(const double*)(Xc + 288 + i8b);
           }
-          if (en.y & 2) {                                      // a chain's top: X to shared memory
+          if (en.y & 4) {                                      // the floating base's link: X as it is, for the 6x6 block
             double2* Xd = (double2*)(XAc + eb.w + 6 * i8b);
             Xd[0] = make_double2(a0, a1); Xd[1] = make_double2(a2, a3); Xd[2] = make_double2(a4, a5);
             *(double*)(XAc + eb.w + 288 + i8b) = pi;
           }
-          const double2* Sd = (const double2*)(Sb + en.z);
-          const double2 s01 = Sd[0], s23 = Sd[1], s45 = Sd[2];
           U = fma(a4, s45.x, fma(a2, s23.x, a0 * s01.x)) + fma(a5, s45.y, fma(a3, s23.y, a1 * s01.y));
-          const double si = *(const double*)(Sb + en.z + i8b);
-          t = si * U;
-          w = si * pi;
-          Uprev = U;
+          *(double*)(Udb + en.w + i8b) = U;
+          pscr[i8] = pi;
         }
-#pragma unroll
-        for (int o = 1; o < 8; o <<= 1) { t += __shfl_xor_sync(GMR_FULL, t, o); w += __shfl_xor_sync(GMR_FULL, w, o); }
+        __syncwarp();
         if (valid) {
+          const double2* ud = (const double2*)(Udb + en.w);
+          const double2* pp = (const double2*)pscr;
+          const double2 u01 = ud[0], u23 = ud[1], u45 = ud[2], p01 = pp[0], p23 = pp[1], p45 = pp[2];
+          const double D = fma(u45.x, s45.x, fma(u23.x, s23.x, u01.x * s01.x)) + fma(u45.y, s45.y, fma(u23.y, s23.y, fma(u01.y, s01.y, diag)));
+          const double sp = fma(p45.x, s45.x, fma(p23.x, s23.x, p01.x * s01.x)) + fma(p45.y, s45.y, fma(p23.y, s23.y, p01.y * s01.y));
           const int slot = (en.y >> 16) - 1;                       // box slot of the dof (-1: a free joint's dof)
           const bool isact = slot >= 0 && (((slot < 32 ? actw0 : actw1) >> (slot & 31)) & 1u);
-          const double inv = rcp_pos(t + diag);                  // D = S'U + d
-          // lanes 0..5 store U, lane 6 alpha = 1/D, lane 7 beta = S'p / D (a locked dof keeps the pair its owner lane wrote)
-          if (i8 < 6 || !isact) *(double*)(Udb + en.w + i8b) = i8 < 6 ? U : (i8 == 6 ? inv : w * inv);
+          const double inv = rcp_pos(D);
+          // a dof held at its bound is a locked joint: alpha = 0, beta = -bound (x[c] holds the bound)
+          const double alpha = isact ? 0.0 : inv, beta = isact ? -x[en.x] : sp * inv;
+          if (i8 == 6) *(double2*)(Udb + en.w + 48) = make_double2(alpha, beta);
+          if (i8 < 6) {
+            const double ua = -U * alpha;
+            a0 = fma(ua, u01.x, a0); a1 = fma(ua, u01.y, a1); a2 = fma(ua, u23.x, a2);
+            a3 = fma(ua, u23.y, a3); a4 = fma(ua, u45.x, a4); a5 = fma(ua, u45.y, a5);
+            pi = fma(-U, beta, pi);
+            if (en.y & 2) {                                    // a side chain's top: X^a to shared memory
+              double2* Xd = (double2*)(XAc + eb.w + 6 * i8b);
+              Xd[0] = make_double2(a0, a1); Xd[1] = make_double2(a2, a3); Xd[2] = make_double2(a4, a5);
+              *(double*)(XAc + eb.w + 288 + i8b) = pi;
+            }
+          }
         }
         __syncwarp();
       }

@@ -131,9 +131,9 @@ int gmr_model_destroy(gmr_model* m);
  * block array / Ud / v / S arrays as laid out in csrc/gmr_device.cuh (DevModel.aba_*). */
 #define GMR_TABLE_INFO       0   /* nv, n_task, n_up_passes, n_down_passes, n_merge, root block offset (-1: none), first base dof,
                                     kkt task mask, doubles of the block array, GMR_KS, GMR_XS, GMR_SS */
-#define GMR_TABLE_UP         2   /* per (pass, 8-lane group) 8 ints: dof (-1 idle), flags (1: X carried in registers from dof
-                                    (flags >> 8) & 255, 2: store X, bits 16..23: box slot + 1), S, Ud offsets, own task block (-1),
-                                    side children [b, e), X offset */
+#define GMR_TABLE_UP         2   /* per (pass, 8-lane group) 8 ints: dof (-1 idle), flags (1: X^a carried in registers from the
+                                    chain's previous dof, 2: store X^a, 4: store X before the dof's rank-1 term, bits 16..23: box
+                                    slot + 1), S, Ud offsets, own task block (-1), side children [b, e), X offset */
 #define GMR_TABLE_CHILD      3   /* per side child: accumulator offset, Ud offset */
 #define GMR_TABLE_DN         5   /* per (pass, group) 4 ints: dof (-1 idle), flags (1: v carried, 2: store v), v_parent offset (-1: none), 0 */
 #define GMR_TABLE_MERGE      6   /* pairs (dst task, src task) hanging on one dof */

@@ -71,7 +71,10 @@ def main():
     if args.device is None:
         args.device = local if local is not None else 0
     sdt = np.float32 if args.stream_f32 else np.float64
-    todo = dataset.shard_files(dataset.pending_files(args.src_folder, args.tgt_folder, (".bvh", ".npz"), args.override), rank, world)
+    # the partition is made on the whole file list, before the skip-if-exists filter: ranks that start at different
+    # moments (or a re-run after an interruption) must agree on who owns which file
+    mine = dataset.shard_files(dataset.pending_files(args.src_folder, args.tgt_folder, (".bvh", ".npz"), True), rank, world)
+    todo = [(s, t) for s, t in mine if args.override or not os.path.exists(t)]
     if not todo:
         print(f"[rank {rank}/{world}] Nothing to do.")
         return

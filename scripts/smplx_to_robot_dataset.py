@@ -54,8 +54,9 @@ def hard_motions() -> set:
     return names
 
 
-def select_files(src_folder, tgt_folder, override):
+def select_files(src_folder, tgt_folder, override, quiet=False):
     """The reference's walk (:210-234) -> [(src, tgt)]."""
+    say = (lambda *a: None) if quiet else print
     out = []
     for dirpath, _, filenames in os.walk(src_folder):
         for filename in sorted(filenames, key=natural_key):
@@ -66,7 +67,7 @@ def select_files(src_folder, tgt_folder, override):
                 tgt = src.replace(src_folder, tgt_folder).replace(".npz", ".pkl")
                 if not os.path.exists(tgt) or override:
                     out.append((src, tgt))
-    print("full args_list:", len(out))
+    say("full args_list:", len(out))
     hard = hard_motions()
     keep = []
     for src, tgt in out:
@@ -74,7 +75,7 @@ def select_files(src_folder, tgt_folder, override):
         if motion_name in hard or any(c in motion_name for c in EXCLUDE_FILE_CONTENT):
             continue
         keep.append((src, tgt))
-    print("new args_list:", len(keep))
+    say("new args_list:", len(keep))
     return keep
 
 
@@ -92,7 +93,12 @@ def main():
     rank, world, local = dataset.rank_info()
     if args.device is None:
         args.device = local if local is not None else 0
-    todo = dataset.shard_files(select_files(args.src_folder, args.tgt_folder, args.override), rank, world)
+    if rank == 0:
+        select_files(args.src_folder, args.tgt_folder, args.override)           # the reference's two counts
+    # the partition is made on the whole selection, before the skip-if-exists filter, so that ranks starting at
+    # different moments (or a re-run) agree on who owns which file
+    mine = dataset.shard_files(select_files(args.src_folder, args.tgt_folder, True, quiet=True), rank, world)
+    todo = [(s, t) for s, t in mine if args.override or not os.path.exists(t)]
     print(f"[rank {rank}/{world}] Total number of files to process: {len(todo)}")
     if not todo:
         return

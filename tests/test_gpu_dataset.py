@@ -219,3 +219,38 @@ def test_clip_diagnostics_match_the_per_frame_log(tmp_path):
     dm2 = DeviceModel.load("smplx", "booster_t1", n2)
     d2 = dataset.clip_diagnostics(dm2, h2[0], np.tile(m2.qpos0, (3, 1)), height=float(hg2[0]))
     assert np.isnan(d2["left_wrist_yaw_link"]).all() and np.isfinite(d2["error1"]).all()
+
+
+def test_bvh_driver_two_ranks_write_disjoint_halves(tmp_path):
+    """The driver under torchrun's environment (RANK / WORLD_SIZE / LOCAL_RANK): the ranks cut the file list between
+    them, each writes its own pickles (and .pt files), no communication; together they equal the one-process run."""
+    import pickle
+    import subprocess
+    import sys
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "bvh_lafan.npz"))
+    lines = str(z["bvh_text"]).rstrip("\n").split("\n")
+    src = tmp_path / "src"
+    src.mkdir()
+    for k, drop in enumerate((0, 3, 6, 9, 12)):
+        text = "\n".join(lines[:len(lines) - drop]).replace("Frames: 24", f"Frames: {24 - drop}") + "\n"
+        (src / f"clip{k}.bvh").write_text(text)
+    script = os.path.join(os.path.dirname(__file__), "..", "scripts", "bvh_to_robot_dataset.py")
+
+    def run(tgt, env_extra, extra=()):
+        env = dict(os.environ, **env_extra)
+        r = subprocess.run([sys.executable, script, "--src_folder", str(src), "--tgt_folder", str(tgt), "--robot", "unitree_g1", *extra],
+                           capture_output=True, text=True, timeout=600, env=env)
+        assert r.returncode == 0, r.stdout + r.stderr
+        return r.stdout
+    run(tmp_path / "one", {})
+    outs = [run(tmp_path / "two", {"RANK": str(r), "WORLD_SIZE": "2", "LOCAL_RANK": "0"}, ("--pt",)) for r in range(2)]
+    assert "[rank 0/2]" in outs[0] and "[rank 1/2]" in outs[1]
+    one = sorted(os.listdir(tmp_path / "one"))
+    assert one == [f"clip{k}.pkl" for k in range(5)]
+    assert sorted(f for f in os.listdir(tmp_path / "two") if f.endswith(".pkl")) == one
+    assert len([f for f in os.listdir(tmp_path / "two") if f.endswith(".pt")]) == 5
+    for f in one:
+        a = pickle.load(open(tmp_path / "one" / f, "rb"))
+        b = pickle.load(open(tmp_path / "two" / f, "rb"))
+        np.testing.assert_array_equal(a["dof_pos"], b["dof_pos"])
+        np.testing.assert_array_equal(a["local_body_pos"], b["local_body_pos"])

@@ -75,11 +75,11 @@ def _walk(hm, stage, S, K, g, d, locked, bound):
     Ud = np.full(8 * nv, np.nan)
     v = np.full(6 * nv, np.nan)
     x = np.where(locked, bound, 0.0)
-    for c in np.nonzero(locked)[0]:
-        Ud[8 * c + 6], Ud[8 * c + 7] = 0.0, -bound[c]
+    parent = hm.table(DOF_PARENT, stage)
     seen = set()
-    reg = [dict(rows=np.full((6, 6), np.nan), p=np.full(6, np.nan), U=np.full(6, np.nan), dof=-1) for _ in range(4)]
-    stored = set()
+    reg = [dict(rows=np.full((6, 6), np.nan), p=np.full(6, np.nan), dof=-1) for _ in range(4)]
+    stored, raw = set(), set()
+    child_of = {}
     for ps in range(nup):
         writes = []                                       # shared-memory stores become visible after the pass (__syncwarp)
         for grp in range(4):
@@ -89,40 +89,38 @@ def _walk(hm, stage, S, K, g, d, locked, bound):
             assert c not in seen and So == c * SS * 8 and Uo == c * 64 and Xo % 16 == 0
             seen.add(int(c))
             r = reg[grp]
-            if flags & 1:
-                prev = (flags >> 8) & 0xff
-                assert r["dof"] == prev, "carried accumulator is not the previous dof of this group"
-                al, be = Ud[8 * prev + 6], Ud[8 * prev + 7]
-                Uc = Ud[8 * prev:8 * prev + 6]
-                np.testing.assert_array_equal(Uc, r["U"])
-                rows = r["rows"] - np.outer(r["U"], Uc) * al
-                p = r["p"] - r["U"] * be
+            if flags & 1:                                 # the registers hold X^a of the chain's previous dof
+                assert r["dof"] >= 0 and parent[r["dof"]] == c, "carried accumulator is not a child of this dof"
+                rows, p = r["rows"].copy(), r["p"].copy()
             else:
                 rows, p = np.zeros((6, 6)), np.zeros(6)
             if own >= 0:
                 rows = rows + _sym_unpack(XA[own // 8:own // 8 + 21])
                 p = p + XA[own // 8 + 21:own // 8 + 27]
             for Xc, udc in ch[cb:ce]:
-                assert Xc in stored
-                U, al, be = Ud[udc // 8:udc // 8 + 6], Ud[udc // 8 + 6], Ud[udc // 8 + 7]
-                rows = rows + XA[Xc // 8:Xc // 8 + 36].reshape(6, 6) - np.outer(U, U) * al
-                p = p + XA[Xc // 8 + 36:Xc // 8 + 42] - U * be
-            if flags & 2:
-                writes.append((Xo // 8, np.concatenate([rows.ravel(), p])))
-                stored.add(int(Xo))
+                assert Xc in stored and parent[udc // 64] == c
+                rows = rows + XA[Xc // 8:Xc // 8 + 36].reshape(6, 6)
+                p = p + XA[Xc // 8 + 36:Xc // 8 + 42]
+            if flags & 4:
+                writes.append((XA, Xo // 8, np.concatenate([rows.ravel(), p])))
+                raw.add(int(Xo))
             Sc = Sarr[So // 8:So // 8 + 6]
             U = rows @ Sc
-            w = [(Uo // 8, U.copy())]
-            if not locked[c]:
+            if locked[c]:
+                al, be = 0.0, -x[c]
+            else:
                 D = Sc @ U + d
-                w.append((Uo // 8 + 6, np.array([1.0 / D, (Sc @ p) / D])))
-            writes += w
-            reg[grp] = dict(rows=rows, p=p, U=U, dof=int(c))
-        for off, val in writes:
-            tgt = Ud if val.size <= 6 else XA
+                al, be = 1.0 / D, (Sc @ p) / D
+            writes.append((Ud, Uo // 8, np.concatenate([U, [al, be]])))
+            rows, p = rows - np.outer(U, U) * al, p - U * be
+            if flags & 2:
+                writes.append((XA, Xo // 8, np.concatenate([rows.ravel(), p])))
+                stored.add(int(Xo))
+            reg[grp] = dict(rows=rows, p=p, dof=int(c))
+        for tgt, off, val in writes:
             tgt[off:off + val.size] = val
     if rootX >= 0:
-        assert rootX in stored
+        assert rootX in raw
         I = XA[rootX // 8:rootX // 8 + 36].reshape(6, 6)
         p = XA[rootX // 8 + 36:rootX // 8 + 42]
         Sb = np.stack([S[rootdof + b] for b in range(6)], 1)
