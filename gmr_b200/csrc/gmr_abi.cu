@@ -589,7 +589,7 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h, 
   Lay L{};
   int o = 0;
   auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };   // keep 16-byte alignment
-  L.q = take(nq); L.scaled = take(7 * s); L.x = take(nv);
+  L.q = take(nq); L.scaled = take(7 * s); L.x = take(nv); L.st = take(4);
   L.xpos = take(3 * nbody); L.xquat = take(GMR_QS * nbody);
   o = std::max(o, L.xpos + ((std::max(GMR_SS, 6) * nv + 1) & ~1));   // F_l (stride GMR_SS) and v (stride 6) alias the body poses
   L.F = L.xpos; L.v = L.xpos;

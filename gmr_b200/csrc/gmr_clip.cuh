@@ -61,8 +61,8 @@ struct Slot {
   int flags;                     // GMR_STATUS_* bits of the frame
   long long row0;                // row of the clip's frame 0 in the stream / the outputs
   bool new_frame, fresh, need_fk;
-  double curr;                   // curr_error of the reference loop
-  unsigned long long act_lo, act_hi;   // active set of the previous solve of this frame/stage
+  // curr_error of the reference loop and the active set of the previous solve of this frame / stage live in the warp's
+  // shared-memory block (Lay::st): the solver's sweeps need every register
 };
 
 __device__ __forceinline__ int next_stage(const DevModel& M, int stage) {
@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
   }
   __syncthreads();
   Slot s;
-  s.inst = -1; s.t = s.T = 0; s.stage = 2; s.it = 0; s.nfact = 0; s.flags = 0; s.row0 = 0; s.curr = 0; s.act_lo = s.act_hi = 0;
+  s.inst = -1; s.t = s.T = 0; s.stage = 2; s.it = 0; s.nfact = 0; s.flags = 0; s.row0 = 0;
   s.new_frame = s.fresh = s.need_fk = false;
   int range = 0;
   const int n_units = a.n_ranges * a.B;
@@ -140,6 +140,8 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
       s.new_frame = true; s.need_fk = true;
     }
     const DevModel& M = mv.M();
+    double* const curr = sm + lay.st;                                             // [0] curr_error
+    unsigned long long* const actp = (unsigned long long*)(sm + lay.st + 1);      // [1], [2] active set (lower, upper)
     // ---- Kernel 2: FK (q changed: integrate of the previous tick, or a new clip)
     if (s.need_fk) { stage_fk<false>(mv, lay, sm, lane); s.need_fk = false; }
     // ---- Kernel 4: control
@@ -156,7 +158,8 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
         }
         s.new_frame = false;
         s.stage = next_stage(M, -1);
-        s.fresh = true; s.it = 0; s.nfact = 0; s.act_lo = s.act_hi = 0;
+        s.fresh = true; s.it = 0; s.nfact = 0;
+        if (lane < 2) actp[lane] = 0ull;
         if (lane == 0) {      // stages that are switched off report zeros
           for (int k = 0; k < 2; k++)
             if (!M.use[k]) {
@@ -167,9 +170,9 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
       }
       if (s.stage < 2) {
         const double err = stage_errors(mv, lay, sm, s.stage, lane);
-        if (s.fresh) { s.curr = err; s.fresh = false; solve = true; break; }                           // :145 / :165
-        if (s.curr - err > M.converge_eps) {                                                                  // :153 / :172
-          if (s.it < M.max_iter) { s.curr = err; s.it++; solve = true; break; }
+        if (s.fresh) { if (lane == 0) *curr = err; s.fresh = false; solve = true; break; }              // :145 / :165
+        if (*curr - err > M.converge_eps) {                                                                   // :153 / :172
+          if (s.it < M.max_iter) { __syncwarp(); if (lane == 0) *curr = err; s.it++; solve = true; break; }
           s.flags |= GMR_STATUS_MAX_ITER1 << s.stage;        // the loop ended on its counter, not on the error test
         }
         if (lane == 0) {
@@ -177,7 +180,9 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
           if (a.iters_out) a.iters_out[2 * o + s.stage] = s.it + 1;
         }
         s.stage = next_stage(M, s.stage);
-        s.it = 0; s.act_lo = s.act_hi = 0;
+        s.it = 0;
+        __syncwarp();
+        if (lane < 2) actp[lane] = 0ull;
         if (s.stage < 2) { s.fresh = true; continue; }
       }
       // frame finished (:185)
@@ -208,7 +213,7 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
     // ---- Kernel 2+3: task stiffness, box QP of mink build_ik (never assembled: articulated-body sweeps over
     //      the task stiffnesses); Kernel 4: integrate
     const double mu = stage_stiffness(mv, lay, sm, s.stage, lane);
-    const int nf = qp_solve_aba(mv, lay, sm, s.stage, mu, lane, s.act_lo, s.act_hi);
+    const int nf = qp_solve_aba(mv, lay, sm, s.stage, mu, lane, actp);
     if (nf < 0) s.flags |= GMR_STATUS_QP_CAP;                // the active-set search hit its cap: last iterate used
     s.nfact += abs(nf);
     stage_integrate(mv, lay, sm, lane);
@@ -315,8 +320,10 @@ __global__ void solve_ik_kernel(const StageArgs a) {
   stage_fk<false>(mv, lay, sm, lane);
   stage_errors(mv, lay, sm, a.stage, lane);
   const double mu = stage_stiffness(mv, lay, sm, a.stage, lane);
-  unsigned long long act_lo = 0, act_hi = 0;
-  const int nf = qp_solve_aba(mv, lay, sm, a.stage, mu, lane, act_lo, act_hi);
+  unsigned long long* actp = (unsigned long long*)(sm + lay.st + 1);
+  if (lane < 2) actp[lane] = 0ull;
+  __syncwarp();
+  const int nf = qp_solve_aba(mv, lay, sm, a.stage, mu, lane, actp);
   for (int i = lane; i < M.nv; i += 32) a.dq_out[(size_t)inst * a.nv_max + i] = sm[lay.x + i];
   if (lane == 0 && a.nfact_out) a.nfact_out[inst] = nf;
 }

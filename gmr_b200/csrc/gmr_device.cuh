@@ -145,6 +145,7 @@ struct ModelView {
 // Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
 struct Lay {
   int q, scaled, x;                       // per-frame state: configuration, targets, the last solve's dq
+  int st;                                 // control state that would otherwise sit in registers: curr_error, active set (lo, hi)
   int H;                                  // gmr_build_qp only: nnz packed tree rows; aliases e/K (written once they are folded into F)
   int xpos, xquat, S;                     // kinematics: body poses, spatial axes (stride GMR_SS)
   int e, K;                               // task errors (stride GMR_ES), task blocks [K_t | g_t] (stride GMR_KS) + solver accumulators

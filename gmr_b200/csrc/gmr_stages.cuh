@@ -680,7 +680,7 @@ __device__ __noinline__ int qp_solve(int n, const double* __restrict__ H, const 
 #define QP_MAX_SWEEPS 100
 template <class MV>
 __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double* __restrict__ sm, int stage, double mu_sum,
-                                            int lane, unsigned long long& act_lo, unsigned long long& act_hi) {
+                                            int lane, unsigned long long* __restrict__ actp) {
   const DevModel& M = mv.M();
   const int n = M.nv, m = M.n_task[stage];
   const double diag = M.damping + M.lm_damping * mu_sum;
@@ -724,20 +724,16 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   const int i0 = has0 ? mv(M.box_dof)[lane] : 0, i1 = has1 ? mv(M.box_dof)[lane + 32] : 0;
   // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs, intersected with the
   // optional velocity box |dq| <= vmax dt (off by default: the reference passes no velocity limit, motion_retarget.py:147-149)
-  double lo0 = -INFINITY, hi0 = INFINITY, lo1 = -INFINITY, hi1 = INFINITY;
-  if (has0 && mv(M.dof_limited)[i0]) {
-    const double qv = q[mv(M.dof_qadr)[i0]];
-    hi0 = M.limit_gain * (mv(M.dof_hi)[i0] - qv); lo0 = -M.limit_gain * (qv - mv(M.dof_lo)[i0]);
-  }
-  if (two && has1 && mv(M.dof_limited)[i1]) {
-    const double qv = q[mv(M.dof_qadr)[i1]];
-    hi1 = M.limit_gain * (mv(M.dof_hi)[i1] - qv); lo1 = -M.limit_gain * (qv - mv(M.dof_lo)[i1]);
-  }
-  if (M.has_vmax) {
-    const double* vm = mv(M.dof_vmax);
-    if (has0) { const double b = vm[i0] * M.timestep; hi0 = fmin(hi0, b); lo0 = fmax(lo0, -b); }
-    if (has1) { const double b = vm[i1] * M.timestep; hi1 = fmin(hi1, b); lo1 = fmax(lo1, -b); }
-  }
+  // (recomputed from q after the sweeps instead of being carried through them: registers are what the sweeps lack)
+  auto box = [&](int i, bool has, double& lo, double& hi) {
+    lo = -INFINITY; hi = INFINITY;
+    if (!has) return;
+    if (mv(M.dof_limited)[i]) {
+      const double qv = q[mv(M.dof_qadr)[i]];
+      hi = M.limit_gain * (mv(M.dof_hi)[i] - qv); lo = -M.limit_gain * (qv - mv(M.dof_lo)[i]);
+    }
+    if (M.has_vmax) { const double bnd = mv(M.dof_vmax)[i] * M.timestep; hi = fmin(hi, bnd); lo = fmax(lo, -bnd); }
+  };
   // tasks that hang on the same dof are summed into the first of them
   {
     const int2* mg = mv(M.aba_merge) + stage * GMR_MAX_TASKS;
@@ -747,8 +743,16 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
     }
   }
   int st0 = 0, st1 = 0;      // 0 free, -1 at lower, +1 at upper; a seed is only honoured where the bound is finite
-  if (has0) st0 = ((act_lo >> lane) & 1ull) && lo0 > -INFINITY ? -1 : (((act_hi >> lane) & 1ull) && hi0 < INFINITY ? 1 : 0);
-  if (has1) st1 = ((act_lo >> (lane + 32)) & 1ull) && lo1 > -INFINITY ? -1 : (((act_hi >> (lane + 32)) & 1ull) && hi1 < INFINITY ? 1 : 0);
+  {
+    const unsigned long long act_lo = actp[0], act_hi = actp[1];
+    double lo, hi;
+    box(i0, has0, lo, hi);
+    if (has0) st0 = ((act_lo >> lane) & 1ull) && lo > -INFINITY ? -1 : (((act_hi >> lane) & 1ull) && hi < INFINITY ? 1 : 0);
+    if (two) {
+      box(i1, has1, lo, hi);
+      if (has1) st1 = ((act_lo >> (lane + 32)) & 1ull) && lo > -INFINITY ? -1 : (((act_hi >> (lane + 32)) & 1ull) && hi < INFINITY ? 1 : 0);
+    }
+  }
   unsigned long long act = (unsigned long long)__ballot_sync(GMR_FULL, st0 != 0);
   if (two) act |= (unsigned long long)__ballot_sync(GMR_FULL, st1 != 0) << 32;
   if (rootX < 0) {                          // no floating-base block: a free joint's dofs (if any) are not swept and stay at 0
@@ -761,9 +765,12 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
 #pragma unroll 1
   for (int it = 0;; it++) {
     // dofs at a bound carry it; free dofs without a task below them stay at 0 (the sweeps skip them)
-    const double xa0 = st0 < 0 ? lo0 : (st0 > 0 ? hi0 : 0.0), xa1 = st1 < 0 ? lo1 : (st1 > 0 ? hi1 : 0.0);
-    if (has0) x[i0] = xa0;
-    if (two && has1) x[i1] = xa1;
+    {
+      double lo, hi;
+      box(i0, has0, lo, hi);
+      if (has0) x[i0] = st0 < 0 ? lo : (st0 > 0 ? hi : 0.0);
+      if (two) { box(i1, has1, lo, hi); if (has1) x[i1] = st1 < 0 ? lo : (st1 > 0 ? hi : 0.0); }
+    }
     __syncwarp();
     // ---- upward sweep.  A pass has two halves around one __syncwarp: (1) lane i < 6 completes row i of X_c (the chain's
     // registers + own task block + side chains from shared memory) and writes U_i = X_i S and p_i; (2) every lane of
@@ -945,11 +952,13 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
         __syncwarp();
       }
     }
-    r0 = has0 ? x[i0] : 0.0;
-    r1 = (two && has1) ? x[i1] : 0.0;
-    // exact bounds on the active set (the sweep reproduces them up to rounding)
-    if (st0) r0 = xa0;
-    if (st1) r1 = xa1;
+    double lo0, hi0, lo1 = -INFINITY, hi1 = INFINITY;
+    box(i0, has0, lo0, hi0);
+    if (two) box(i1, has1, lo1, hi1);
+    // the sweeps reproduce the bounds of the active set up to rounding: x[] still holds them exactly for the dofs
+    // the sweeps skip, and the swept ones are overwritten with the exact bound here
+    r0 = has0 ? (st0 ? (st0 < 0 ? lo0 : hi0) : x[i0]) : 0.0;
+    r1 = (two && has1) ? (st1 ? (st1 < 0 ? lo1 : hi1) : x[i1]) : 0.0;
     // ---- KKT check
     bool bad0 = false, bad1 = false;
     if (has0 && !st0) bad0 = (r0 < lo0 - QP_PTOL) || (r0 > hi0 + QP_PTOL);
@@ -1012,12 +1021,13 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   }
   if (has0) x[i0] = r0;
   if (two && has1) x[i1] = r1;
-  act_lo = (unsigned long long)__ballot_sync(GMR_FULL, st0 < 0);
-  act_hi = (unsigned long long)__ballot_sync(GMR_FULL, st0 > 0);
+  unsigned long long act_lo = (unsigned long long)__ballot_sync(GMR_FULL, st0 < 0);
+  unsigned long long act_hi = (unsigned long long)__ballot_sync(GMR_FULL, st0 > 0);
   if (two) {
     act_lo |= (unsigned long long)__ballot_sync(GMR_FULL, st1 < 0) << 32;
     act_hi |= (unsigned long long)__ballot_sync(GMR_FULL, st1 > 0) << 32;
   }
+  if (lane == 0) { actp[0] = act_lo; actp[1] = act_hi; }
   __syncwarp();
   return capped ? -nfact : nfact;
 }
