@@ -19,7 +19,7 @@ EXPORTS = [
     "gmr_batch_set_order", "gmr_batch_launch_info", "gmr_batch_dims", "gmr_batch_step", "gmr_batch_run",
     "gmr_target_prep", "gmr_fk", "gmr_build_qp", "gmr_qp_solve", "gmr_fk_bodies_f32", "gmr_probe_fma_peak", "gmr_solve_ik", "gmr_batch_run_host",
     "gmr_bvh_to_stream", "gmr_smplx_to_stream", "gmr_model_table", "gmr_batch_run_csr", "gmr_batch_run_host_csr",
-    "gmr_batch_step_host", "gmr_probe_math",
+    "gmr_batch_step_host", "gmr_probe_math", "gmr_model_layout", "gmr_batch_layout_id",
 ]
 
 _lib = None
@@ -45,6 +45,8 @@ def lib():
     L.gmr_model_create.argtypes = [C.POINTER(gmr_model_desc), C.c_int, C.POINTER(vp)]
     L.gmr_model_destroy.argtypes = [vp]
     L.gmr_model_table.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int]
+    L.gmr_model_layout.argtypes = [vp, vp, C.c_int]
+    L.gmr_batch_layout_id.argtypes = [vp]
     L.gmr_batch_create.argtypes = [C.POINTER(vp), C.c_int, vp, C.c_int, vp, C.POINTER(vp)]
     L.gmr_batch_destroy.argtypes = [vp]
     L.gmr_batch_reset.argtypes = [vp, vp]

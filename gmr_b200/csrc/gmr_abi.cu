@@ -58,6 +58,7 @@ struct gmr_batch {
   cudaStream_t s_in = nullptr, s_out = nullptr;
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
   bool smem_model = false;
+  int layout_id = -1;            // index into gmr_layouts.cuh when the batch's layout is one of the compiled ones
 };
 
 extern "C" const char* gmr_last_error(void) { return g_err.c_str(); }
@@ -572,9 +573,19 @@ extern "C" int gmr_model_table(const gmr_model* m, int which, int stage, int32_t
 
 // ---------------------------------------------------------------- batch
 // the instantiation of the fused kernel for (stream dtype, model staged in shared memory)
-static const void* clip_kernel_ptr(int dtype, bool staged) {
-  if (dtype == GMR_F32) return staged ? (const void*)clip_kernel<float, true> : (const void*)clip_kernel<float, false>;
-  return staged ? (const void*)clip_kernel<double, true> : (const void*)clip_kernel<double, false>;
+// and the compile-time shared-memory layout (gmr_layouts.cuh; -1 = the run-time layout of RunArgs)
+template <int L>
+static const void* clip_kernel_of(int dtype, bool staged) {
+  if (dtype == GMR_F32) return staged ? (const void*)clip_kernel<float, true, L> : (const void*)clip_kernel<float, false, -1>;
+  return staged ? (const void*)clip_kernel<double, true, L> : (const void*)clip_kernel<double, false, -1>;
+}
+static const void* clip_kernel_ptr(int dtype, bool staged, int layout = -1) {
+  switch (staged ? layout : -1) {
+#define GMR_LAYOUT_CASE(k) case k: return clip_kernel_of<k>(dtype, staged);
+    GMR_FOR_EACH_FIXED_LAYOUT(GMR_LAYOUT_CASE)
+#undef GMR_LAYOUT_CASE
+    default: return clip_kernel_of<-1>(dtype, staged);
+  }
 }
 
 static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h, int blocks) {
@@ -606,6 +617,17 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h, 
   L.total = (o + 31) & ~31;
   L.maxt = GMR_MAX_TASKS;
   return L;
+}
+
+extern "C" int gmr_model_layout(const gmr_model* m, int32_t* out, int cap) {
+  if (!m) return fail(-1, "null model");
+  const DevModel& h = m->host;
+  const Lay L = make_layout(h.nq, h.n_scaled, h.nv, h.nbody, std::max(m->max_task, 1), h.nnz, h.n_human, std::max(h.aba_doubles, 1));
+  const int n = (int)(sizeof(Lay) / sizeof(int));
+  static_assert(sizeof(Lay) % sizeof(int) == 0, "Lay is a struct of ints");
+  const int* src = (const int*)&L;
+  if (out) for (int i = 0; i < n && i < cap; i++) out[i] = src[i];
+  return n;
 }
 
 extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const int32_t* model_of_instance,
@@ -663,6 +685,14 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
     const size_t fixed = stat + 1024;
     const size_t sm_total = 228 * 1024;
     b->smem_model = n_models == 1 && per_warp + blob + fixed <= (size_t)dev_smem && !getenv("GMR_DEBUG_GLOBAL_MODEL");
+    // a single-model batch whose layout is one of the generated ones runs the kernel compiled for it: every
+    // shared-memory offset is then an immediate instead of a constant-bank load rematerialised at each use
+    b->layout_id = -1;
+    if (b->smem_model && !getenv("GMR_DEBUG_RUNTIME_LAYOUT"))
+      for (int k = 0; k < GMR_NUM_FIXED_LAYOUTS; k++) {
+        const Lay f = fixed_layout(k);
+        if (memcmp(&f, &b->lay, sizeof(Lay)) == 0) { b->layout_id = k; break; }
+      }
     const size_t extra = fixed + (b->smem_model ? blob : 0);
     const int max_w = GMR_CTA_THREADS / 32;
     int best_w = 1, best_total = 0;
@@ -679,7 +709,7 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   }
   // The dynamic shared-memory opt-in is a per-function, process-wide attribute: another batch (another robot, a
   // narrower CTA) would lower it under this one, so launch_clips sets it again right before every launch.
-  const void* kf = clip_kernel_ptr(GMR_F32, b->smem_model);
+  const void* kf = clip_kernel_ptr(GMR_F32, b->smem_model, b->layout_id);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->clip_smem_bytes);
   int per_sm = 0;
   if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kf, 32 * b->warps_per_cta, b->clip_smem_bytes);
@@ -778,6 +808,8 @@ extern "C" int gmr_batch_dims(const gmr_batch* b, int32_t* B, int32_t* nq_max, i
   return 0;
 }
 
+extern "C" int gmr_batch_layout_id(const gmr_batch* b) { return b ? b->layout_id : -2; }
+
 extern "C" int gmr_batch_launch_info(const gmr_batch* b, int32_t* grid, int32_t* warps_per_cta, int32_t* smem_bytes, int32_t* smem_per_instance) {
   if (!b) return fail(-1, "null batch");
   if (grid) *grid = b->grid;
@@ -813,7 +845,7 @@ static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const in
   CU(cudaMemsetAsync(b->d_counter, 0, sizeof(int), b->stream));
   const dim3 grid(b->grid), block(32 * b->warps_per_cta);
   void* kargs[] = {(void*)&a};
-  const void* kern = clip_kernel_ptr(dtype, b->smem_model);
+  const void* kern = clip_kernel_ptr(dtype, b->smem_model, b->layout_id);
   CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->clip_smem_bytes));
   CU(cudaLaunchKernel(kern, grid, block, kargs, b->clip_smem_bytes, b->stream));
   CU(cudaGetLastError());

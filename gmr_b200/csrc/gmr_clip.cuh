@@ -9,6 +9,7 @@
 // DESIGN.md section 4 for the measured batch sizes from which the throughput bound takes over.
 #pragma once
 #include "gmr_stages.cuh"
+#include "gmr_layouts.cuh"
 
 namespace gmr {
 
@@ -79,12 +80,14 @@ __device__ __forceinline__ int next_stage(const DevModel& M, int stage) {
 // of the CTA therefore executes the same solver code in every tick, whatever frame, stage or
 // iteration its own instance is in, and each stage function has exactly one call site.
 // SM = true: single-model batch, model tables staged in shared memory.
-template <typename TIn, bool SM>
+// LAYOUT >= 0: the warp block's offsets are those of fixed_layout(LAYOUT) (gmr_layouts.cuh, generated for every
+// constructible (source, robot) pair) and fold into the addresses as immediates; -1: the layout comes in RunArgs.
+template <typename TIn, bool SM, int LAYOUT>
 __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs a) {
   extern __shared__ __align__(256) double smem[];
   __shared__ DevModel smodel;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const Lay lay = a.lay;
+  const Lay lay = LAYOUT >= 0 ? fixed_layout(LAYOUT < 0 ? 0 : LAYOUT) : a.lay;
   double* sm = smem + (size_t)warp * lay.total;
   ModelView<SM> mv;
   mv.m = a.models;

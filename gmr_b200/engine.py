@@ -114,7 +114,9 @@ class BatchedRetargeter:
     def launch_info(self) -> dict:
         d = [C.c_int32() for _ in range(4)]
         _lib.lib().gmr_batch_launch_info(self._h, *[C.byref(x) for x in d])
-        return dict(zip(("grid", "warps_per_cta", "smem_bytes_per_cta", "smem_bytes_per_instance"), [x.value for x in d]))
+        info = dict(zip(("grid", "warps_per_cta", "smem_bytes_per_cta", "smem_bytes_per_instance"), [x.value for x in d]))
+        info["layout_id"] = int(_lib.lib().gmr_batch_layout_id(self._h))
+        return info
 
     def reset(self, q0=None):
         q0 = None if q0 is None else self._dev(q0, torch.float64, (self.B, self.nq_max))

@@ -142,6 +142,11 @@ int gmr_model_destroy(gmr_model* m);
 #define GMR_TABLE_TASKMASK   9
 #define GMR_TABLE_FK_BODY   10   /* bodies the fused kernel's forward kinematics sweeps (world first) */
 int gmr_model_table(const gmr_model* m, int which, int stage, int32_t* out, int cap);
+/* Offsets (in doubles) of the per-instance shared-memory block a single-model batch of `m` uses, in the field order of
+ * csrc/gmr_device.cuh::Lay; returns the number of ints, copies at most `cap`.  tools/gen_layouts.py turns them into
+ * csrc/gmr_layouts.cuh (the fused kernel is compiled once per known layout, offsets as immediates); a batch whose layout
+ * is not in that file runs the generic kernel.  Host only, no CUDA call.  No counterpart in the reference. */
+int gmr_model_layout(const gmr_model* m, int32_t* out, int cap);
 
 /* B independent IK instances (clip x robot).  n_models > 1 = heterogeneous launch;
  * model_of_instance (host, [B]) may be NULL when n_models == 1.  State starts at qpos0. */
@@ -160,6 +165,9 @@ int gmr_batch_set_order(gmr_batch* b, const int32_t* order_dev);
 /* launch geometry chosen at create time (for reporting) */
 int gmr_batch_launch_info(const gmr_batch* b, int32_t* grid, int32_t* warps_per_cta,
                           int32_t* smem_bytes_per_cta, int32_t* smem_bytes_per_instance);
+/* index of the compile-time layout (csrc/gmr_layouts.cuh) the batch's fused kernel was compiled for; -1 = the generic
+ * kernel with the layout passed at run time (heterogeneous batch, unknown robot, or GMR_DEBUG_RUNTIME_LAYOUT set). */
+int gmr_batch_layout_id(const gmr_batch* b);
 int gmr_batch_dims(const gmr_batch* b, int32_t* B, int32_t* nq_max, int32_t* s_max,
                    int32_t* h_max, int32_t* nbody_max);
 

@@ -47,6 +47,17 @@ def test_struct_layout_matches_header():
     assert gmr_diag.status_dev.offset == off4
 
 
+def test_compile_time_layouts_are_current():
+    """csrc/gmr_layouts.cuh (generated) holds exactly the layouts the library's make_layout computes for the
+    constructible pairs; a stale file would silently send those robots to the generic kernel."""
+    import subprocess
+    import sys
+    from gmr_b200.build import build
+    build()
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gen_layouts.py"), "--check"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+
+
 def test_engine_fails_loudly_without_library(monkeypatch, tmp_path):
     import pytest
     from gmr_b200 import _lib

@@ -502,6 +502,25 @@ def test_two_batches_of_different_footprint_alternate():
     np.testing.assert_array_equal(brB.run(humanB).cpu().numpy(), small)
 
 
+@pytest.mark.parametrize("src,robot", [("bvh", "unitree_g1"), ("smplx", "unitree_g1_with_hands"), ("smplx", "galaxea_r1pro")])
+def test_compile_time_layout_kernels_equal_the_generic_one(src, robot, monkeypatch):
+    """A single-model batch of a known robot runs the kernel compiled for its layout (csrc/gmr_layouts.cuh); the
+    generic kernel (layout passed at run time) must give the same bits - same code, same arithmetic order."""
+    B, T = 40, 33
+    m, t, dm, br, human, heights = _setup(src, robot, B, T, seed=21)
+    assert br.launch_info()["layout_id"] >= 0, "known robot did not get its compile-time layout"
+    fixed, dfix = br.run(human, diag=True)
+    monkeypatch.setenv("GMR_DEBUG_RUNTIME_LAYOUT", "1")
+    from gmr_b200.engine import BatchedRetargeter
+    br2 = BatchedRetargeter(dm, B)
+    br2.set_heights(heights)
+    assert br2.launch_info()["layout_id"] == -1
+    generic, dgen = br2.run(human, diag=True)
+    np.testing.assert_array_equal(fixed.cpu().numpy(), generic.cpu().numpy())
+    np.testing.assert_array_equal(dfix["iters"].cpu().numpy(), dgen["iters"].cpu().numpy())
+    np.testing.assert_array_equal(dfix["err"].cpu().numpy(), dgen["err"].cpu().numpy())
+
+
 def test_set_order_rejects_non_permutations():
     m, t, dm, br, human, heights = _setup("bvh", "unitree_g1", 6, 2)
     with pytest.raises(ValueError):
