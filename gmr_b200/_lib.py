@@ -19,7 +19,7 @@ EXPORTS = [
     "gmr_batch_set_order", "gmr_batch_launch_info", "gmr_batch_dims", "gmr_batch_step", "gmr_batch_run",
     "gmr_target_prep", "gmr_fk", "gmr_build_qp", "gmr_qp_solve", "gmr_fk_bodies_f32", "gmr_probe_fma_peak", "gmr_solve_ik", "gmr_batch_run_host",
     "gmr_bvh_to_stream", "gmr_smplx_to_stream", "gmr_model_table", "gmr_batch_run_csr", "gmr_batch_run_host_csr",
-    "gmr_batch_step_host", "gmr_probe_math", "gmr_model_layout", "gmr_batch_layout_id",
+    "gmr_batch_step_host", "gmr_probe_math", "gmr_model_layout", "gmr_batch_layout_id", "gmr_bvh_to_stream_static",
 ]
 
 _lib = None
@@ -72,6 +72,7 @@ def lib():
     L.gmr_smplx_to_stream.argtypes = [C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, vp]
     L.gmr_bvh_to_stream.argtypes = [C.c_int, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, C.POINTER(i32), vp, vp, C.c_int,
                                     C.c_int, vp, C.c_int, C.POINTER(i32), vp]
+    L.gmr_bvh_to_stream_static.argtypes = L.gmr_bvh_to_stream.argtypes
     if L.gmr_abi_version() != ABI_VERSION:
         raise EngineError("ABI version mismatch between gmr_b200/abi.py and libgmr_b200.so")
     _lib = L

@@ -8,6 +8,7 @@
 #include <vector>
 #include <algorithm>
 #include <map>
+#include <mutex>
 
 #include "../../include/gmr_b200.h"
 #include "gmr_clip.cuh"
@@ -1204,6 +1205,77 @@ extern "C" int gmr_bvh_to_stream(int device, void* stream, const double* lpos_de
   e = cudaGetLastError();
   cudaFreeAsync(sign, st);
   cudaFreeAsync(G, st);
+  if (e != cudaSuccess) return fail(-3, cudaGetErrorString(e));
+  return 0;
+}
+
+// ---------------------------------------------------------------- the same without any allocation
+// Scratch of gmr_bvh_to_stream_static: [G: GMR_BVH_STATIC_MAX_ELEMS x 8 doubles | sign: GMR_BVH_STATIC_MAX_ELEMS bytes]
+// in the module's own global memory (32.5 MiB on every device that loads the library, until exit).  The name below is
+// a host-side stand-in in host code: the device address comes from cudaGetSymbolAddress, once per device.
+#define GMR_BVH_STATIC_G_BYTES ((size_t)GMR_BVH_STATIC_MAX_ELEMS * 8 * sizeof(double))
+static __device__ __align__(256) unsigned char g_bvh_static_scratch[GMR_BVH_STATIC_G_BYTES + GMR_BVH_STATIC_MAX_ELEMS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_bvh_static_mu;
+void* g_bvh_static_ptr[kMaxDevices] = {};
+}  // namespace
+
+extern "C" int gmr_bvh_to_stream_static(int device, void* stream, const double* lpos_dev, const double* euler_deg_dev,
+                                        const int32_t* clip_start_dev, int n_clips, int n_frames, int n_bones,
+                                        const int32_t* parents_dev, const int32_t* channel_axis, const int32_t* src_pos_dev,
+                                        const int32_t* src_rot_dev, int n_rows, int out_dtype, void* stream_out_dev,
+                                        int head_row, const int32_t* foot_rows, double* height_out_dev) {
+  if (!lpos_dev || !euler_deg_dev || !clip_start_dev || !parents_dev || !channel_axis || !src_pos_dev || !src_rot_dev ||
+      !stream_out_dev || n_clips < 0 || n_frames < 0 || n_bones < 1 || n_rows < 1)
+    return fail(-1, "gmr_bvh_to_stream_static: bad argument");
+  if (out_dtype != GMR_F32 && out_dtype != GMR_F64) return fail(-1, "gmr_bvh_to_stream_static: dtype must be GMR_F32 or GMR_F64");
+  for (int k = 0; k < 3; k++)
+    if (channel_axis[k] < 0 || channel_axis[k] > 2) return fail(-1, "gmr_bvh_to_stream_static: channel axis must be 0, 1 or 2");
+  if (head_row >= n_rows) return fail(-1, "gmr_bvh_to_stream_static: head row out of range");
+  if (device < 0 || device >= kMaxDevices) return fail(-1, "gmr_bvh_to_stream_static: device ordinal out of range");
+  const long long elems = (long long)n_frames * n_bones;
+  if (elems > (long long)GMR_BVH_STATIC_MAX_ELEMS)
+    return fail(-4, "gmr_bvh_to_stream_static: n_frames * n_bones = " + std::to_string(elems) + " exceeds the static scratch (GMR_BVH_STATIC_MAX_ELEMS = " +
+                        std::to_string((long long)GMR_BVH_STATIC_MAX_ELEMS) + "); split the call or use gmr_bvh_to_stream");
+  if (n_frames == 0 || n_clips == 0) return 0;
+  DevGuard g(device);
+  unsigned char* base = nullptr;
+  {   // set-up, once per device, with that device current
+    std::lock_guard<std::mutex> lk(g_bvh_static_mu);
+    if (!g_bvh_static_ptr[device]) {
+      void* p = nullptr;
+      cudaError_t e = cudaGetSymbolAddress(&p, g_bvh_static_scratch);
+      if (e != cudaSuccess || !p) return fail(-3, std::string("gmr_bvh_to_stream_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+      g_bvh_static_ptr[device] = p;
+    }
+    base = (unsigned char*)g_bvh_static_ptr[device];
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  BvhArgs a{};
+  a.lpos = lpos_dev; a.euler = euler_deg_dev; a.clip_start = clip_start_dev;
+  a.C = n_clips; a.N = n_frames; a.J = n_bones; a.parents = parents_dev;
+  a.ax0 = channel_axis[0]; a.ax1 = channel_axis[1]; a.ax2 = channel_axis[2];
+  a.src_pos = src_pos_dev; a.src_rot = src_rot_dev; a.h = n_rows; a.out = stream_out_dev;
+  a.head = head_row;
+  for (int k = 0; k < 4; k++) {
+    a.feet[k] = foot_rows ? foot_rows[k] : -1;
+    if (a.feet[k] >= n_rows) return fail(-1, "gmr_bvh_to_stream_static: foot row out of range");
+  }
+  a.height = height_out_dev;
+  a.G = (double*)base;
+  a.sign = (signed char*)(base + GMR_BVH_STATIC_G_BYTES);
+  // the array keeps the last call's contents: frames no clip covers must read "no flip", not a stale sign
+  CU(cudaMemsetAsync(a.sign, 0, (size_t)elems, st));
+  const int tb = 128;
+  bvh_sign_kernel<<<(n_clips * n_bones + tb - 1) / tb, tb, 0, st>>>(a);
+  bvh_fk_kernel<<<(n_frames + tb - 1) / tb, tb, 0, st>>>(a);
+  const long long ne = (long long)n_frames * n_rows;
+  if (out_dtype == GMR_F32) bvh_emit_kernel<float><<<(unsigned)((ne + 255) / 256), 256, 0, st>>>(a);
+  else bvh_emit_kernel<double><<<(unsigned)((ne + 255) / 256), 256, 0, st>>>(a);
+  if (height_out_dev) bvh_height_kernel<<<(n_clips + tb - 1) / tb, tb, 0, st>>>(a);
+  cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(-3, cudaGetErrorString(e));
   return 0;
 }

@@ -266,6 +266,26 @@ int gmr_bvh_to_stream(int device, void* stream, const double* lpos_dev, const do
                       const int32_t* src_rot_dev, int n_rows, int out_dtype, void* stream_out_dev,
                       int head_row, const int32_t* foot_rows, double* height_out_dev);
 
+/* gmr_bvh_to_stream for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, same kernels, same results; the per-(frame, bone) scratch (global transforms + sign bits, 65 bytes
+ * per element) lives in a fixed array in the library's device image instead of a stream-ordered allocation, so the
+ * call makes no cudaMalloc / cudaFree / cudaMallocAsync and calls no allocating library routine.
+ *   limit: n_frames * n_bones <= GMR_BVH_STATIC_MAX_ELEMS (22-bone LAFAN1 skeleton: 23 831 frames per call);
+ *          larger calls return -4 with a message in gmr_last_error() and launch nothing - split them or use
+ *          gmr_bvh_to_stream.  The array (32.5 MiB) is held by every device that loads the library, until exit.
+ *   sharing: every call on a device uses the same array, which keeps the previous call's contents (the part a call
+ *          reads without writing is cleared first).  Calls that overlap on the GPU - different streams, or graph
+ *          launches in flight at once - race on it; serialise them.
+ *   first call per device: looks the array's device address up (cudaGetSymbolAddress); make one call outside a
+ *          capture before capturing. */
+#define GMR_BVH_STATIC_MAX_ELEMS (1 << 19)
+int gmr_bvh_to_stream_static(int device, void* stream, const double* lpos_dev, const double* euler_deg_dev,
+                             const int32_t* clip_start_dev, int n_clips, int n_frames, int n_bones,
+                             const int32_t* parents_dev, const int32_t* channel_axis, const int32_t* src_pos_dev,
+                             const int32_t* src_rot_dev, int n_rows, int out_dtype, void* stream_out_dev,
+                             int head_row, const int32_t* foot_rows, double* height_out_dev);
+
 /* SMPL-X model output -> human frame stream, for all frames of all clips at once: what
  * get_smplx_data_offline_fast does (general_motion_retargeting/utils/smpl.py:109-198) - fps alignment
  * (SLERP of every joint's rotation vector between the two neighbouring source frames :78-107,133-160, linear
