@@ -368,7 +368,7 @@ def run_b200(args):
     roofline = {"bound": "fp64_fma", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                 "frac": achieved_tf / fp64_peak if fp64_peak > 0 else None, "traffic": traffic,
                 "peak_source": "measured here (gmr_probe_fma_peak, DFMA chains on all SMs; MEASURED_PEAKS.json has no FP64 entry)",
-                "kernel": f"gmr::clip_kernel<float, true, {launch.get('layout_id', -1)}>", "kernel_ms_per_launch": kernel_ms,
+                "kernel": f"gmr::clip_kernel<float, true, {br.launch_info().get('layout_id', -1)}>", "kernel_ms_per_launch": kernel_ms,
                 "algorithmic_flops_per_iteration": fpi, "iterations_per_frame": iters_per_frame,
                 "note": "per-instance 6x6 contractions on a 35-dof tree: FP64 CUDA-core work on dependent chains, neither "
                         "HBM nor tensor cores bind it.  `achieved` counts SURVEY.md 8d's DENSE algorithm (84x35 Jacobian, "
