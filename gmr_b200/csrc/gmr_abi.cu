@@ -400,14 +400,22 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   std::vector<double> body_quat_padded((size_t)GMR_QS * nb, 0.0);
   for (int b = 0; b < nb; b++)
     for (int i = 0; i < 4; i++) body_quat_padded[(size_t)GMR_QS * b + i] = d->body_quat[4 * b + i];
-  // bodies whose pose the IK reads: owners of joints, task frames, every ancestor of those, and the world
+  // bodies whose pose the IK reads: owners of scheduled joints, task frames, every ancestor of those, and the world
   std::vector<char> fk_need(nb, 0);
   fk_need[0] = 1;
-  for (int b = 1; b < nb; b++) if (d->body_jntnum[b] > 0) fk_need[b] = 1;
+  // a dof is "scheduled" when some task of some stage hangs below it; the others (fingers of a robot whose tasks
+  // end at the wrists) never move and nothing reads their axes, so their bodies stay out of the sweep
+  std::vector<short> cdof, udof;
+  for (int i = 0; i < nv; i++) {
+    const bool sched = (taskmask[i] | taskmask[nv + i]) != 0u;
+    if (sched) fk_need[dof_body[i]] = 1;
+    if (i < fk_skip) continue;                 // a floating base's translations: constant axes, written apart
+    if (sched) cdof.push_back((short)i); else udof.push_back((short)i);
+  }
   for (int v : task_body) if (v > 0 && v < nb) fk_need[v] = 1;
   for (int b = nb - 1; b > 0; b--) if (fk_need[b]) fk_need[d->body_parentid[b]] = 1;
   std::vector<short> fk_body;
-  for (int b = 0; b < nb; b++) if (fk_need[b]) fk_body.push_back((short)b);
+  for (int b = 1; b < nb; b++) if (fk_need[b]) fk_body.push_back((short)b);      // the world's pose is a constant (stage_fk writes it apart)
   Blob bl;
   // tables of the fused kernel first: a CTA stages exactly this leading part of the blob in shared memory
   size_t o_parent = bl.push(vec(d->body_parentid, nb)), o_bpos = bl.push(vec(d->body_pos, 3 * nb)),
@@ -423,7 +431,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
          o_tb = bl.push(task_body), o_ts = bl.push(task_src), o_wp = bl.push(task_wpos), o_wr = bl.push(task_wrot),
          o_fj = bl.push(fk_jump), o_fb = bl.push(fk_body), o_ap1 = bl.push(aba_up), o_ach = bl.push(aba_ch), o_adn = bl.push(aba_dn), o_amg = bl.push(aba_merge),
          o_atd = bl.push(task_dof), o_vm = bl.push(dof_vmax),
-         o_ig = bl.push(integ_dof), o_bx = bl.push(box_dof);
+         o_ig = bl.push(integ_dof), o_bx = bl.push(box_dof), o_cd = bl.push(cdof), o_ud = bl.push(udof);
   const size_t staged_bytes = (bl.bytes.size() + 15) & ~size_t(15);
   // tables only the stage kernels read (gmr_build_qp: the assembly of H), from global memory
   size_t o_lstart = bl.push(level_start), o_lbody = bl.push(level_body), o_dp = bl.push(dof_parent),
@@ -518,6 +526,7 @@ extern "C" int gmr_model_create(const gmr_model_desc* d, int device, gmr_model**
   h.task_dof = (const int*)(B0 + o_atd);
   h.fk_rounds = fk_rounds; h.fk_jump = (const short*)(B0 + o_fj);
   h.n_fk = (int)fk_body.size(); h.fk_body = (const short*)(B0 + o_fb);
+  h.n_cdof = (int)cdof.size(); h.cdof = (const short*)(B0 + o_cd); h.n_udof = (int)udof.size(); h.udof = (const short*)(B0 + o_ud);
   h.tasklev_task = (const int*)(B0 + o_tlt); h.n_tasklev[0] = n_tasklev[0]; h.n_tasklev[1] = n_tasklev[1];
   m->max_task = std::max(h.n_task[0], h.n_task[1]);
   char* T0 = m->tail_blob;

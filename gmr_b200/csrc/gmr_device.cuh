@@ -56,6 +56,9 @@ struct DevModel {
   const double* dof_lo;      // [nv] joint range lower
   const double* dof_hi;      // [nv]
   int fk_skip;               // leading translational dofs of a floating base (their spatial axes are constants): 3 or 0
+  int n_cdof, n_udof;        // FK pass C: scheduled dofs (a task below them) past fk_skip; unscheduled dofs (axes kept at zero)
+  const short* cdof;         // [n_cdof]
+  const short* udof;         // [n_udof]
   int n_integ;               // dofs stage_integrate visits: hinges, slides and the first rotational dof of a free joint
   const short* integ_dof;    // [n_integ]
   int n_box;                 // dofs that can carry a box constraint (everything but a free joint's six), ascending

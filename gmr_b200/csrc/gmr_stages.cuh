@@ -186,7 +186,11 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
   }
   // mju_normalize4 of every body quaternion, all bodies at once (the products above keep unit norm
   // to rounding, so normalising after the sweep instead of inside it changes results by ~1e-16)
-  for (int i = 1 + lane; i < nfk; i += 32) normalize4(xquat + GMR_QS * (ALL ? i : fkb[i]));      // entry 0 is the world
+  if (ALL) { for (int i = 1 + lane; i < nfk; i += 32) normalize4(xquat + GMR_QS * i); }          // body 0 is the world
+  else {
+    for (int i = lane; i < nfk; i += 32) normalize4(xquat + GMR_QS * fkb[i]);                    // the list leaves the world out
+    if (lane == 31) { xpos[0] = xpos[1] = xpos[2] = 0.0; xquat[0] = 1.0; xquat[1] = xquat[2] = xquat[3] = 0.0; }
+  }
   __syncwarp();
   // ---- pass C
   const int ref = M.ref_body;
@@ -196,7 +200,10 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
     double* sk = S + GMR_SS * lane;
     sk[0] = (lane == 0); sk[1] = (lane == 1); sk[2] = (lane == 2); sk[3] = sk[4] = sk[5] = 0;
   }
-  for (int k = lane + skip; k < M.nv; k += 32) {
+  for (int i = lane; i < 6 * M.n_udof; i += 32) S[GMR_SS * mv(M.udof)[i / 6] + i % 6] = 0.0;   // never scheduled: no axis
+  const short* cdof = mv(M.cdof);
+  for (int ci = lane; ci < M.n_cdof; ci += 32) {
+    const int k = cdof[ci];
     const int kind = mv(M.dof_kind)[k], b = mv(M.dof_body)[k];
     double* sk = S + GMR_SS * k;
     if (kind == DOF_FREE_T) {

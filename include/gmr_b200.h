@@ -140,7 +140,7 @@ int gmr_model_destroy(gmr_model* m);
 #define GMR_TABLE_TASK_DOF   7
 #define GMR_TABLE_DOF_PARENT 8
 #define GMR_TABLE_TASKMASK   9
-#define GMR_TABLE_FK_BODY   10   /* bodies the fused kernel's forward kinematics sweeps (world first) */
+#define GMR_TABLE_FK_BODY   10   /* bodies the fused kernel's forward kinematics sweeps (the world left out: its pose is a constant) */
 int gmr_model_table(const gmr_model* m, int which, int stage, int32_t* out, int cap);
 /* Offsets (in doubles) of the per-instance shared-memory block a single-model batch of `m` uses, in the field order of
  * csrc/gmr_device.cuh::Lay; returns the number of ints, copies at most `cap`.  tools/gen_layouts.py turns them into
