@@ -45,6 +45,7 @@ struct gmr_batch {
   double* d_scale = nullptr;    // [B, s_max]
   int* d_counter = nullptr;
   int* d_done = nullptr;        // [B] per-clip range flags of the current launch
+  unsigned long long* d_act = nullptr;   // [B,GMR_ACT_WORDS] remembered active sets of each instance (warm starts of its next solves)
   int* d_order = nullptr;
   int nq_max = 0, s_max = 0, h_max = 0, nbody_max = 0, nv_max = 0, m_max = 0, nnz_max = 0, blocks_max = 1;
   Lay lay{};
@@ -610,7 +611,7 @@ static Lay make_layout(int nq, int s, int nv, int nbody, int m, int nnz, int h, 
   Lay L{};
   int o = 0;
   auto take = [&](int n) { int r = o; o += (n + 1) & ~1; return r; };   // keep 16-byte alignment
-  L.q = take(nq); L.scaled = take(7 * s); L.x = take(nv); L.st = take(4);
+  L.q = take(nq); L.scaled = take(7 * s); L.x = take(nv); L.st = take(10);
   L.xpos = take(3 * nbody); L.xquat = take(GMR_QS * nbody);
   o = std::max(o, L.xpos + ((std::max(GMR_SS, 6) * nv + 1) & ~1));   // F_l (stride GMR_SS) and v (stride 6) alias the body poses
   L.F = L.xpos; L.v = L.xpos;
@@ -672,6 +673,7 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
   alloc((void**)&b->d_scale, sizeof(double) * (size_t)B * b->s_max);
   alloc((void**)&b->d_counter, sizeof(int));
   alloc((void**)&b->d_done, sizeof(int) * (size_t)B);
+  alloc((void**)&b->d_act, sizeof(unsigned long long) * GMR_ACT_WORDS * (size_t)B);
   if (model_of_instance) alloc((void**)&b->d_model_of, sizeof(int) * (size_t)B);
   if (e == cudaSuccess) e = cudaMemcpy(b->d_models, hm.data(), sizeof(DevModel) * n_models, cudaMemcpyHostToDevice);
   if (e == cudaSuccess && model_of_instance)
@@ -747,7 +749,7 @@ extern "C" int gmr_batch_destroy(gmr_batch* b) {
   int prev = 0;
   cudaGetDevice(&prev);
   cudaSetDevice(b->device);
-  cudaFree(b->d_models); cudaFree(b->d_q); cudaFree(b->d_scale); cudaFree(b->d_counter); cudaFree(b->d_done);
+  cudaFree(b->d_models); cudaFree(b->d_q); cudaFree(b->d_scale); cudaFree(b->d_counter); cudaFree(b->d_done); cudaFree(b->d_act);
   cudaFree(b->d_model_of); cudaFree(b->d_order);
   cudaFree(b->stage_in); cudaFree(b->stage_out); cudaFree(b->stage_T); cudaFree(b->stage_cs);
   if (b->s_in) { cudaStreamDestroy(b->s_in); cudaStreamDestroy(b->s_out); for (int i = 0; i < 3; i++) cudaEventDestroy(b->ev[i]); }
@@ -779,6 +781,7 @@ extern "C" int gmr_batch_reset(gmr_batch* b, const double* q0_dev) {
   if (q0_dev) CU(cudaMemcpyAsync(b->d_q, q0_dev, sizeof(double) * n, cudaMemcpyDeviceToDevice, b->stream));
   else fill_rows_kernel<<<(n + 255) / 256, 256, 0, b->stream>>>(b->d_q, b->B, b->nq_max, b->d_models, b->d_model_of, 0);
   CU(cudaGetLastError());
+  CU(cudaMemsetAsync(b->d_act, 0, sizeof(unsigned long long) * GMR_ACT_WORDS * (size_t)b->B, b->stream));      // cold start: empty active set
   return 0;
 }
 
@@ -850,7 +853,7 @@ static int launch_clips(gmr_batch* b, const void* human_dev, int dtype, const in
   a.unit_frames = 32;
   if (const char* ev = getenv("GMR_DEBUG_UNIT_FRAMES")) a.unit_frames = std::max(1, atoi(ev));
   a.n_ranges = std::max(1, (a.t_end - a.t_begin + a.unit_frames - 1) / a.unit_frames);
-  a.done = b->d_done;
+  a.done = b->d_done; a.act_state = b->d_act;
   CU(cudaMemsetAsync(b->d_done, 0, sizeof(int) * (size_t)b->B, b->stream));
   CU(cudaMemsetAsync(b->d_counter, 0, sizeof(int), b->stream));
   const dim3 grid(b->grid), block(32 * b->warps_per_cta);

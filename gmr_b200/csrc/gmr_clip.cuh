@@ -37,6 +37,7 @@ struct RunArgs {
   const double* scale;           // [B, s_max]
   int s_max;
   double* q_state;               // [B, nq_max] in/out
+  unsigned long long* act_state; // [B, GMR_ACT_WORDS] in/out: remembered active sets (first guesses of the next solves)
   int nq_max;
   double* qpos_out;              // [B, T_max, nq_max] or null
   double* scaled_out;            // [B, T_max, s_max, 7] or null
@@ -62,7 +63,8 @@ struct Slot {
   int flags;                     // GMR_STATUS_* bits of the frame
   long long row0;                // row of the clip's frame 0 in the stream / the outputs
   bool new_frame, fresh, need_fk;
-  // curr_error of the reference loop and the active set of the previous solve of this frame / stage live in the warp's
+  // curr_error of the reference loop and the active set of the instance's previous solve (whatever its frame or stage:
+  // a joint at its limit usually stays there; kept in RunArgs::act_state between units and launches) live in the warp's
   // shared-memory block (Lay::st): the solver's sweeps need every register
 };
 
@@ -139,12 +141,13 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
       s.inst = inst; s.t = t0; s.T = min(T_inst, t0 + a.unit_frames); s.row0 = r0;
       const double* qs = a.q_state + (size_t)inst * a.nq_max;
       for (int i = lane; i < mv.M().nq; i += 32) sm[lay.q + i] = __ldcg(qs + i);     // written by another SM: bypass L1
+      if (lane < GMR_ACT_WORDS) ((unsigned long long*)(sm + lay.st + 1))[lane] = __ldcg(a.act_state + GMR_ACT_WORDS * (size_t)inst + lane);
       __syncwarp();
       s.new_frame = true; s.need_fk = true;
     }
     const DevModel& M = mv.M();
     double* const curr = sm + lay.st;                                             // [0] curr_error
-    unsigned long long* const actp = (unsigned long long*)(sm + lay.st + 1);      // [1], [2] active set (lower, upper)
+    unsigned long long* const actm = (unsigned long long*)(sm + lay.st + 1);      // remembered active sets
     // ---- Kernel 2: FK (q changed: integrate of the previous tick, or a new clip)
     if (s.need_fk) { stage_fk<false>(mv, lay, sm, lane); s.need_fk = false; }
     // ---- Kernel 4: control
@@ -162,7 +165,6 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
         s.new_frame = false;
         s.stage = next_stage(M, -1);
         s.fresh = true; s.it = 0; s.nfact = 0;
-        if (lane < 2) actp[lane] = 0ull;
         if (lane == 0) {      // stages that are switched off report zeros
           for (int k = 0; k < 2; k++)
             if (!M.use[k]) {
@@ -184,8 +186,6 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
         }
         s.stage = next_stage(M, s.stage);
         s.it = 0;
-        __syncwarp();
-        if (lane < 2) actp[lane] = 0ull;
         if (s.stage < 2) { s.fresh = true; continue; }
       }
       // frame finished (:185)
@@ -206,6 +206,7 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
       if (++s.t < s.T) { s.new_frame = true; continue; }
       double* qs = a.q_state + (size_t)s.inst * a.nq_max;
       for (int i = lane; i < M.nq; i += 32) qs[i] = sm[lay.q + i];
+      if (lane < GMR_ACT_WORDS) a.act_state[GMR_ACT_WORDS * (size_t)s.inst + lane] = actm[lane];
       __threadfence();
       __syncwarp();
       if (lane == 0) *((volatile int*)a.done + s.inst) = range + 1;      // release the next range of this clip
@@ -216,6 +217,9 @@ __global__ void __launch_bounds__(GMR_CTA_THREADS, 1) clip_kernel(const RunArgs 
     // ---- Kernel 2+3: task stiffness, box QP of mink build_ik (never assembled: articulated-body sweeps over
     //      the task stiffnesses); Kernel 4: integrate
     const double mu = stage_stiffness(mv, lay, sm, s.stage, lane);
+    // first guess of the active set: what the same kind of solve ended with last time - the first solve of a frame
+    // (the targets just moved: joints run into their limits) or a later one (corrections: they come off again)
+    unsigned long long* const actp = actm + 4 * s.stage + 2 * (s.it > 0);
     const int nf = qp_solve_aba(mv, lay, sm, s.stage, mu, lane, actp);
     if (nf < 0) s.flags |= GMR_STATUS_QP_CAP;                // the active-set search hit its cap: last iterate used
     s.nfact += abs(nf);

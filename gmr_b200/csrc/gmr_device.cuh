@@ -146,9 +146,11 @@ struct ModelView {
 #define GMR_XS 42
 
 // Per-warp shared-memory layout, offsets in doubles (sized for the largest model of a batch).
+#define GMR_ACT_WORDS 8
 struct Lay {
   int q, scaled, x;                       // per-frame state: configuration, targets, the last solve's dq
-  int st;                                 // control state that would otherwise sit in registers: curr_error, active set (lo, hi)
+  int st;                                 // control state that would otherwise sit in registers: curr_error, then GMR_ACT_WORDS words of
+                                          // remembered active sets: [stage][first solve of a frame / later solves][lower, upper]
   int H;                                  // gmr_build_qp only: nnz packed tree rows; aliases e/K (written once they are folded into F)
   int xpos, xquat, S;                     // kinematics: body poses, spatial axes (stride GMR_SS)
   int e, K;                               // task errors (stride GMR_ES), task blocks [K_t | g_t] (stride GMR_KS) + solver accumulators

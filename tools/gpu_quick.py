@@ -44,3 +44,14 @@ for rep in range(args.reps):
     print(f"rep {rep}: {ms:.1f} ms  {args.B * args.T / ms * 1e3:.3e} frames/s  iters/frame {it}  "
           f"nfact/frame {diag['nfact'].double().mean().item():.2f}  maxiter-hit {(diag['iters'] == 11).double().mean().item():.4f}", flush=True)
 print("finite", torch.isfinite(qpos).all().item())
+# per clip: solves (= solve_ik calls) and box-QP sweeps; the slowest chains of the launch
+solves = diag["iters"].sum((1, 2)).cpu().numpy()
+sweeps = diag["nfact"].sum(1).cpu().numpy()
+order = np.argsort(-sweeps)
+print(f"clips: solves mean {solves.mean():.0f} max {solves.max()}  sweeps mean {sweeps.mean():.0f} max {sweeps.max()}  "
+      f"sweeps/solve overall {sweeps.sum() / solves.sum():.3f}")
+print("slowest by sweeps (clip, solves, sweeps, sweeps/solve):",
+      [(int(c), int(solves[c]), int(sweeps[c]), round(float(sweeps[c] / solves[c]), 3)) for c in order[:12]])
+nf = diag["nfact"].cpu().numpy()
+itf = diag["iters"].sum(-1).cpu().numpy()
+print("sweeps per frame histogram of (sweeps - solves):", np.bincount(np.clip(nf - itf, 0, 12).ravel())[:13].tolist())
