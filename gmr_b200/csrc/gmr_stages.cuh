@@ -838,17 +838,17 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
           const double inv = rcp_pos(D);
           // a dof held at its bound is a locked joint: alpha = 0, beta = -bound (x[c] holds the bound)
           const double alpha = isact ? 0.0 : inv, beta = isact ? -x[en.x] : sp * inv;
-          if (i8 == 6) *(double2*)(Udb + en.w + 48) = make_double2(alpha, beta);
-          if (i8 < 6) {
-            const double ua = -U * alpha;
-            a0 = fma(ua, u01.x, a0); a1 = fma(ua, u01.y, a1); a2 = fma(ua, u23.x, a2);
-            a3 = fma(ua, u23.y, a3); a4 = fma(ua, u45.x, a4); a5 = fma(ua, u45.y, a5);
-            pi = fma(-U, beta, pi);
-            if (en.y & 2) {                                    // a side chain's top: X^a to shared memory
-              double2* Xd = (double2*)(XAc + eb.w + 6 * i8b);
-              Xd[0] = make_double2(a0, a1); Xd[1] = make_double2(a2, a3); Xd[2] = make_double2(a4, a5);
-              *(double*)(XAc + eb.w + 288 + i8b) = pi;
-            }
+          // every lane of the group holds the same alpha, beta: all eight store them (one word, one value) and all
+          // eight run the update (lanes 6, 7 carry U = 0 and rows nobody reads) - branches cost more than the work
+          *(double2*)(Udb + en.w + 48) = make_double2(alpha, beta);
+          const double ua = -U * alpha;
+          a0 = fma(ua, u01.x, a0); a1 = fma(ua, u01.y, a1); a2 = fma(ua, u23.x, a2);
+          a3 = fma(ua, u23.y, a3); a4 = fma(ua, u45.x, a4); a5 = fma(ua, u45.y, a5);
+          pi = fma(-U, beta, pi);
+          if ((en.y & 2) && i8 < 6) {                            // a side chain's top: X^a to shared memory
+            double2* Xd = (double2*)(XAc + eb.w + 6 * i8b);
+            Xd[0] = make_double2(a0, a1); Xd[1] = make_double2(a2, a3); Xd[2] = make_double2(a4, a5);
+            *(double*)(XAc + eb.w + 288 + i8b) = pi;
           }
         }
         __syncwarp();
@@ -948,12 +948,10 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
           const double xc = fma(-dot, ab.x, -ab.y);
           v0 = fma(s01.x, xc, v0); v1 = fma(s01.y, xc, v1); v2 = fma(s23.x, xc, v2);
           v3 = fma(s23.y, xc, v3); v4 = fma(s45.x, xc, v4); v5 = fma(s45.y, xc, v5);
-          if (i8 == 0) {
-            x[en.x] = xc;
-            if (en.y & 2) {
-              double2* vd = (double2*)(vb + 48 * en.x);
-              vd[0] = make_double2(v0, v1); vd[1] = make_double2(v2, v3); vd[2] = make_double2(v4, v5);
-            }
+          x[en.x] = xc;                                          // all eight lanes hold the same xc and v: same word, same value
+          if (en.y & 2) {
+            double2* vd = (double2*)(vb + 48 * en.x);
+            vd[0] = make_double2(v0, v1); vd[1] = make_double2(v2, v3); vd[2] = make_double2(v4, v5);
           }
         }
         __syncwarp();
