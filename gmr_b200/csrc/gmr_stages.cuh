@@ -795,11 +795,8 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
         const int4 en = e[0], eb = e[1];
         const bool valid = en.x >= 0;
         double U = 0.0;
-        double2 s01 = make_double2(0, 0), s23 = s01, s45 = s01;
-        if (valid) {
-          const double2* Sd = (const double2*)(Sb + en.z);
-          s01 = Sd[0]; s23 = Sd[1]; s45 = Sd[2];
-        }
+        const double2* Sd = (const double2*)(Sb + en.z);       // an idle entry points at dof 0: loaded, not used
+        const double2 s01 = Sd[0], s23 = Sd[1], s45 = Sd[2];
         if (valid && i8 < 6) {
           if (!(en.y & 1)) a0 = a1 = a2 = a3 = a4 = a5 = pi = 0.0;      // a chain's bottom
           if (eb.x >= 0) {                                     // own task block, packed symmetric
