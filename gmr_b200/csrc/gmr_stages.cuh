@@ -93,9 +93,10 @@ __device__ __forceinline__ bool stage_prep(const MV& mv, const Lay& lay, double*
 //       column of ANY descendant frame at x is [v_O + w x (x - O); w].
 // Joint anchors are the body origin (jnt_pos = 0, checked at model creation) and slides precede
 // hinges inside a body, which is what makes the local transform independent of the parent.
-// ALL = false: only the bodies the IK needs are swept (M.fk_body: bodies with joints, task frames, their
-// ancestors and the world - 31 of 39 for unitree_g1, one pass of the warp instead of two); the poses of the other
-// bodies are then stale.  ALL = true (gmr_fk, diagnostics): every body.
+// ALL = false: only the bodies the IK needs are swept (M.fk_body: bodies of scheduled joints, task frames, their
+// ancestors - 30 of 39 for unitree_g1; at most 32 for every robot of the pack, so a lane keeps its body's transform
+// in registers from pass A to the normalisation); the poses of the other bodies are then stale.
+// ALL = true (gmr_fk, diagnostics): every body.
 template <bool ALL, class MV>
 __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* sm, int lane) {
   const DevModel& M = mv.M();
@@ -114,10 +115,8 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
   double* const Q_odd = (R & 1) ? xquat : ql;
   const int nfk = ALL ? nb : M.n_fk;
   const short* fkb = mv(M.fk_body);
-  // ---- pass A: local transform of every body (relative to its parent)
-  for (int i = lane; i < nfk; i += 32) {
-    const int b = ALL ? i : fkb[i];
-    double t[3] = {0, 0, 0}, qq[4] = {1, 0, 0, 0};
+  // local transform of body b (relative to its parent) with its joints folded in; the joint axes in the parent frame go to S
+  auto local_tf = [&](const int b, double (&t)[3], double (&qq)[4]) {
     if (b > 0) {
       const int jadr = mv(M.body_jntadr)[b], jnum = mv(M.body_jntnum)[b];
       if (jnum == 1 && mv(M.jnt_type)[jadr] == 0) {                     // free joint: pose straight from q
@@ -151,47 +150,93 @@ __device__ __forceinline__ void stage_fk(const MV& mv, const Lay& lay, double* s
         }
       }
     }
-    double* T0 = T_even + 3 * b;
-    double* Q0 = Q_even + GMR_QS * b;
-    T0[0] = t[0]; T0[1] = t[1]; T0[2] = t[2];
-    Q0[0] = qq[0]; Q0[1] = qq[1]; Q0[2] = qq[2]; Q0[3] = qq[3];
-  }
-  __syncwarp();
-  // ---- pass B: pointer jumping.  Before round r a body's transform is relative to its 2^r-th
-  // ancestor (or already to the world); composing it with that ancestor's transform doubles the
-  // reach, so ceil(log2(depth)) rounds over ALL bodies replace `depth` sequential levels.
+  };
   const short* jump = mv(M.fk_jump);
-  for (int r = 0; r < R; r++) {
-    const double* Ti = (r & 1) ? T_odd : T_even;
-    const double* Qi = (r & 1) ? Q_odd : Q_even;
-    double* To = (r & 1) ? T_even : T_odd;
-    double* Qo = (r & 1) ? Q_even : Q_odd;
+  if (!ALL && nfk <= 32) {
+    // ---- one body per lane (every robot of the pack): the body's transform stays in registers from pass A through the
+    // rounds of pass B to the normalisation; shared memory only carries it to the lanes that compose with it
+    const bool on = lane < nfk;
+    const int b = on ? fkb[lane] : 0;
+    double t[3] = {0, 0, 0}, qq[4] = {1, 0, 0, 0};
+    if (on) {
+      local_tf(b, t, qq);
+      if (R == 0) normalize4(qq);
+      double* T0 = T_even + 3 * b;
+      double* Q0 = Q_even + GMR_QS * b;
+      T0[0] = t[0]; T0[1] = t[1]; T0[2] = t[2];
+      Q0[0] = qq[0]; Q0[1] = qq[1]; Q0[2] = qq[2]; Q0[3] = qq[3];
+    }
+    __syncwarp();
+    for (int r = 0; r < R; r++) {
+      const double* Ti = (r & 1) ? T_odd : T_even;
+      const double* Qi = (r & 1) ? Q_odd : Q_even;
+      double* To = (r & 1) ? T_even : T_odd;
+      double* Qo = (r & 1) ? Q_even : Q_odd;
+      if (on) {
+        const int anc2 = jump[r * nb + b];                              // 2^r-th ancestor, -1: already in the world frame
+        if (anc2 >= 0) {
+          const double aq[4] = {Qi[GMR_QS * anc2], Qi[GMR_QS * anc2 + 1], Qi[GMR_QS * anc2 + 2], Qi[GMR_QS * anc2 + 3]};
+          double rt[3], nq[4];
+          qrot(aq, t, rt);
+          t[0] = Ti[3 * anc2] + rt[0]; t[1] = Ti[3 * anc2 + 1] + rt[1]; t[2] = Ti[3 * anc2 + 2] + rt[2];
+          qmul(aq, qq, nq);
+          qq[0] = nq[0]; qq[1] = nq[1]; qq[2] = nq[2]; qq[3] = nq[3];
+        }
+        if (r == R - 1) normalize4(qq);                                 // mju_normalize4, once, after the last composition
+        To[3 * b] = t[0]; To[3 * b + 1] = t[1]; To[3 * b + 2] = t[2];
+        Qo[GMR_QS * b] = qq[0]; Qo[GMR_QS * b + 1] = qq[1]; Qo[GMR_QS * b + 2] = qq[2]; Qo[GMR_QS * b + 3] = qq[3];
+      }
+      __syncwarp();
+    }
+    if (lane == 31) { xpos[0] = xpos[1] = xpos[2] = 0.0; xquat[0] = 1.0; xquat[1] = xquat[2] = xquat[3] = 0.0; }      // the world
+    __syncwarp();
+  } else {
+    // ---- pass A: local transform of every body (relative to its parent)
     for (int i = lane; i < nfk; i += 32) {
       const int b = ALL ? i : fkb[i];
-      const int anc2 = jump[r * nb + b];                                // 2^r-th ancestor, -1: already in the world frame
-      double t[3] = {Ti[3 * b], Ti[3 * b + 1], Ti[3 * b + 2]};
-      double qq[4] = {Qi[GMR_QS * b], Qi[GMR_QS * b + 1], Qi[GMR_QS * b + 2], Qi[GMR_QS * b + 3]};
-      if (anc2 >= 0) {
-        const double aq[4] = {Qi[GMR_QS * anc2], Qi[GMR_QS * anc2 + 1], Qi[GMR_QS * anc2 + 2], Qi[GMR_QS * anc2 + 3]};
-        double rt[3], nq[4];
-        qrot(aq, t, rt);
-        t[0] = Ti[3 * anc2] + rt[0]; t[1] = Ti[3 * anc2 + 1] + rt[1]; t[2] = Ti[3 * anc2 + 2] + rt[2];
-        qmul(aq, qq, nq);
-        qq[0] = nq[0]; qq[1] = nq[1]; qq[2] = nq[2]; qq[3] = nq[3];
+      double t[3] = {0, 0, 0}, qq[4] = {1, 0, 0, 0};
+      local_tf(b, t, qq);
+      double* T0 = T_even + 3 * b;
+      double* Q0 = Q_even + GMR_QS * b;
+      T0[0] = t[0]; T0[1] = t[1]; T0[2] = t[2];
+      Q0[0] = qq[0]; Q0[1] = qq[1]; Q0[2] = qq[2]; Q0[3] = qq[3];
+    }
+    __syncwarp();
+    // ---- pass B: pointer jumping.  Before round r a body's transform is relative to its 2^r-th
+    // ancestor (or already to the world); composing it with that ancestor's transform doubles the
+    // reach, so ceil(log2(depth)) rounds over ALL bodies replace `depth` sequential levels.
+    for (int r = 0; r < R; r++) {
+      const double* Ti = (r & 1) ? T_odd : T_even;
+      const double* Qi = (r & 1) ? Q_odd : Q_even;
+      double* To = (r & 1) ? T_even : T_odd;
+      double* Qo = (r & 1) ? Q_even : Q_odd;
+      for (int i = lane; i < nfk; i += 32) {
+        const int b = ALL ? i : fkb[i];
+        const int anc2 = jump[r * nb + b];                                // 2^r-th ancestor, -1: already in the world frame
+        double t[3] = {Ti[3 * b], Ti[3 * b + 1], Ti[3 * b + 2]};
+        double qq[4] = {Qi[GMR_QS * b], Qi[GMR_QS * b + 1], Qi[GMR_QS * b + 2], Qi[GMR_QS * b + 3]};
+        if (anc2 >= 0) {
+          const double aq[4] = {Qi[GMR_QS * anc2], Qi[GMR_QS * anc2 + 1], Qi[GMR_QS * anc2 + 2], Qi[GMR_QS * anc2 + 3]};
+          double rt[3], nq[4];
+          qrot(aq, t, rt);
+          t[0] = Ti[3 * anc2] + rt[0]; t[1] = Ti[3 * anc2 + 1] + rt[1]; t[2] = Ti[3 * anc2 + 2] + rt[2];
+          qmul(aq, qq, nq);
+          qq[0] = nq[0]; qq[1] = nq[1]; qq[2] = nq[2]; qq[3] = nq[3];
+        }
+        To[3 * b] = t[0]; To[3 * b + 1] = t[1]; To[3 * b + 2] = t[2];
+        Qo[GMR_QS * b] = qq[0]; Qo[GMR_QS * b + 1] = qq[1]; Qo[GMR_QS * b + 2] = qq[2]; Qo[GMR_QS * b + 3] = qq[3];
       }
-      To[3 * b] = t[0]; To[3 * b + 1] = t[1]; To[3 * b + 2] = t[2];
-      Qo[GMR_QS * b] = qq[0]; Qo[GMR_QS * b + 1] = qq[1]; Qo[GMR_QS * b + 2] = qq[2]; Qo[GMR_QS * b + 3] = qq[3];
+      __syncwarp();
+    }
+    // mju_normalize4 of every body quaternion, all bodies at once (the products above keep unit norm
+    // to rounding, so normalising after the sweep instead of inside it changes results by ~1e-16)
+    if (ALL) { for (int i = 1 + lane; i < nfk; i += 32) normalize4(xquat + GMR_QS * i); }          // body 0 is the world
+    else {
+      for (int i = lane; i < nfk; i += 32) normalize4(xquat + GMR_QS * fkb[i]);                    // the list leaves the world out
+      if (lane == 31) { xpos[0] = xpos[1] = xpos[2] = 0.0; xquat[0] = 1.0; xquat[1] = xquat[2] = xquat[3] = 0.0; }
     }
     __syncwarp();
   }
-  // mju_normalize4 of every body quaternion, all bodies at once (the products above keep unit norm
-  // to rounding, so normalising after the sweep instead of inside it changes results by ~1e-16)
-  if (ALL) { for (int i = 1 + lane; i < nfk; i += 32) normalize4(xquat + GMR_QS * i); }          // body 0 is the world
-  else {
-    for (int i = lane; i < nfk; i += 32) normalize4(xquat + GMR_QS * fkb[i]);                    // the list leaves the world out
-    if (lane == 31) { xpos[0] = xpos[1] = xpos[2] = 0.0; xquat[0] = 1.0; xquat[1] = xquat[2] = xquat[3] = 0.0; }
-  }
-  __syncwarp();
   // ---- pass C
   const int ref = M.ref_body;
   const double O[3] = {xpos[3 * ref], xpos[3 * ref + 1], xpos[3 * ref + 2]};    // world (body 0) has xpos = 0
