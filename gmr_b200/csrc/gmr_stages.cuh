@@ -795,10 +795,12 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
     }
   }
   int st0 = 0, st1 = 0;      // 0 free, -1 at lower, +1 at upper; a seed is only honoured where the bound is finite
+  double blo0, bhi0;         // the box of slot `lane`, kept for the whole solve (q does not move during it)
   {
     const unsigned long long act_lo = actp[0], act_hi = actp[1];
     double lo, hi;
     box(i0, has0, lo, hi);
+    blo0 = lo; bhi0 = hi;
     if (has0) st0 = ((act_lo >> lane) & 1ull) && lo > -INFINITY ? -1 : (((act_hi >> lane) & 1ull) && hi < INFINITY ? 1 : 0);
     if (two) {
       box(i1, has1, lo, hi);
@@ -818,10 +820,8 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   for (int it = 0;; it++) {
     // dofs at a bound carry it; free dofs without a task below them stay at 0 (the sweeps skip them)
     {
-      double lo, hi;
-      box(i0, has0, lo, hi);
-      if (has0) x[i0] = st0 < 0 ? lo : (st0 > 0 ? hi : 0.0);
-      if (two) { box(i1, has1, lo, hi); if (has1) x[i1] = st1 < 0 ? lo : (st1 > 0 ? hi : 0.0); }
+      if (has0) x[i0] = st0 < 0 ? blo0 : (st0 > 0 ? bhi0 : 0.0);
+      if (two) { double lo, hi; box(i1, has1, lo, hi); if (has1) x[i1] = st1 < 0 ? lo : (st1 > 0 ? hi : 0.0); }
     }
     __syncwarp();
     // ---- upward sweep.  A pass has two halves around one __syncwarp: (1) lane i < 6 completes row i of X_c (the chain's
@@ -1000,7 +1000,7 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
       }
     }
     double lo0, hi0, lo1 = -INFINITY, hi1 = INFINITY;
-    box(i0, has0, lo0, hi0);
+    lo0 = blo0; hi0 = bhi0;
     if (two) box(i1, has1, lo1, hi1);
     // the sweeps reproduce the bounds of the active set up to rounding: x[] still holds them exactly for the dofs
     // the sweeps skip, and the swept ones are overwritten with the exact bound here
