@@ -776,7 +776,7 @@ __device__ __forceinline__ int qp_solve_aba(const MV& mv, const Lay& lay, double
   const int i0 = has0 ? mv(M.box_dof)[lane] : 0, i1 = has1 ? mv(M.box_dof)[lane + 32] : 0;
   // mink ConfigurationLimit: -gain (q - lo) <= dq <= gain (hi - q) on limited hinge/slide dofs, intersected with the
   // optional velocity box |dq| <= vmax dt (off by default: the reference passes no velocity limit, motion_retarget.py:147-149)
-  // (recomputed from q after the sweeps instead of being carried through them: registers are what the sweeps lack)
+  // (the box of slot `lane` is computed once per solve and kept in registers; the second slot of robots with more than 32 slots is re-derived where needed)
   auto box = [&](int i, bool has, double& lo, double& hi) {
     lo = -INFINITY; hi = INFINITY;
     if (!has) return;
