@@ -158,6 +158,9 @@ int gmr_batch_reset(gmr_batch* b, const double* q0_dev);
 /* per-instance scale table [B,s_max] (human_scale_table * actual_height/assumption, :36-43);
  * NULL restores the model's table. */
 int gmr_batch_set_scale(gmr_batch* b, const double* scale_dev);
+/* The state that persists between calls is q plus the box QP's remembered active sets (the first guesses of the next
+ * solves, csrc/gmr_clip.cuh).  The sets only decide how many sweeps a solve takes, not its solution, so a clip that is
+ * carried over through get_state / reset(q0) (which clears the sets) continues with the same results to rounding. */
 int gmr_batch_get_state(gmr_batch* b, double* q_dev /* [B,nq_max] */);
 /* processing order of the work queue (device, [B], a permutation; longest clips first balances
  * ragged batches); NULL = instance order. */
