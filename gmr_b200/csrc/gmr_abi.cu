@@ -713,6 +713,9 @@ extern "C" int gmr_batch_create(gmr_model* const* models, int n_models, const in
       int ctas = (int)std::min<size_t>(sm_total / ((size_t)w * per_warp + extra), (size_t)(max_w / w));
       if (ctas * w >= best_total) { best_total = ctas * w; best_w = w; }
     }
+    // the four schedulers of an SM should hold the same number of warps: 13, 14 or 15 warps measured slower than 12
+    // (profiles/r02_warps_sweep.txt; a warp on a fuller scheduler is slower and the slowest chain sets the launch)
+    if (best_w >= 4) best_w -= best_w % 4;
     if (const char* ev = getenv("GMR_DEBUG_WARPS")) best_w = std::max(1, std::min(max_w, atoi(ev)));
     b->warps_per_cta = std::min(best_w, B);
     b->smem_bytes = per_warp * b->warps_per_cta;
